@@ -1,0 +1,188 @@
+"""Generate tests/golden/*.npz by RUNNING THE REFERENCE ITSELF (build container only).
+
+    python oracle/make_golden.py            # needs /root/reference; writes tests/golden/
+
+The reference (davdwan21/Silent-Speech) ships no tests or golden vectors, so
+the pin for this path is its own code executed here on seeded inputs:
+
+* train_model_official.BiGRUClassifier                (train_model_official.py:253-310)
+  forward, CE(label_smoothing=.05) backward, clip_grad_norm_(1.0), Adam(3e-4) step
+* live_infer_official.BiGRUClassifier                 (live_infer_official.py:101-138; no ROI standardise)
+* live_infer_official.extract_feature / mouth_width_px / crop_roi_gray / topk_from_logits
+* record_landmarks_official.extract_feature / crop_roi
+
+``mediapipe`` is absent; four empty stub modules let the two capture scripts
+import (their feature functions never touch it).  The reference cannot travel
+to the GPU box, hence fixtures.  Weights are NOT stored: they are regenerated
+from ``oracle.ref_model.synth_params(seed)`` (numpy PCG64, machine-independent)
+and loaded into the reference classes with ``load_state_dict``.  Large
+gradients are stored as (norm, sum, every-97th-element) summaries.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import tempfile
+import types
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF = "/root/reference"
+OUT = os.path.join(ROOT, "tests", "golden")
+sys.path.insert(0, ROOT)
+
+from oracle import ref_model  # noqa: E402
+from silent_speech_b200 import synth  # noqa: E402
+
+STRIDE = 97
+
+
+def import_reference():
+    for name in ("mediapipe", "mediapipe.tasks", "mediapipe.tasks.python", "mediapipe.tasks.python.vision"):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    sys.modules["mediapipe"].tasks = sys.modules["mediapipe.tasks"]
+    sys.modules["mediapipe.tasks"].python = sys.modules["mediapipe.tasks.python"]
+    sys.modules["mediapipe.tasks.python"].vision = sys.modules["mediapipe.tasks.python.vision"]
+    sys.path.insert(0, REF)
+    cwd = os.getcwd()
+    os.chdir(tempfile.mkdtemp())           # record_landmarks_official makedirs("clips_npz") at import
+    try:
+        import train_model_official as train
+        import live_infer_official as live
+        import record_landmarks_official as record
+    finally:
+        os.chdir(cwd)
+    return train, live, record
+
+
+class _Pt:
+    __slots__ = ("x", "y")
+
+    def __init__(self, x, y):
+        self.x, self.y = float(x), float(y)
+
+
+def as_face(lm_frame):
+    return [_Pt(p[0], p[1]) for p in lm_frame]
+
+
+def summarise(t: torch.Tensor):
+    f = t.detach().reshape(-1).double()
+    return np.array([f.norm().item(), f.sum().item()]), t.detach().reshape(-1)[::STRIDE].numpy().copy()
+
+
+def golden_features(live, record):
+    B, T = 3, 14
+    lm, present = synth.landmarks(B, T, seed=7, drop=0.15)
+    lm[1, 5, 291, 0] += 0.2          # one frame outside the 60..150 px band
+    out = {"lm": lm, "present": present, "w": np.int64(synth.FRAME_W), "h": np.int64(synth.FRAME_H),
+           "ids": np.array(live.FIXED_IDXS, np.int32)}
+    assert live.FIXED_IDXS == record.FIXED_IDXS and len(live.FIXED_IDXS) == 88
+    for tag, mod in (("live", live), ("record", record)):
+        X = np.zeros((B, T, 180), np.float32); C = np.zeros((B, T, 2), np.float32)
+        MW = np.zeros((B, T), np.float64); V = np.zeros((B, T), np.uint8)
+        for b in range(B):
+            prev = None
+            for t in range(T):
+                face = as_face(lm[b, t])
+                ok = bool(present[b, t])
+                if ok:
+                    mw = mod.mouth_width_px(face, synth.FRAME_W, synth.FRAME_H)
+                    ok = mod.MOUTH_W_MIN_PX <= mw <= mod.MOUTH_W_MAX_PX
+                if not ok:
+                    prev = None
+                    continue
+                feat, prev, center, mw = mod.extract_feature(face, synth.FRAME_W, synth.FRAME_H, mod.FIXED_IDXS, prev)
+                X[b, t] = feat; C[b, t] = center; MW[b, t] = mw; V[b, t] = 1
+        out[f"X_{tag}"] = X; out[f"center_{tag}"] = C; out[f"mouth_w_{tag}"] = MW; out[f"valid_{tag}"] = V
+    np.savez_compressed(os.path.join(OUT, "features.npz"), **out)
+    print("features.npz", {k: getattr(v, "shape", v) for k, v in out.items()})
+
+
+def golden_model(train, live, tag, use_roi, B, T, lens, seed, scale=1.0):
+    p = ref_model.synth_params(seed, use_roi=use_roi, scale=scale)
+    lens = np.asarray(lens, np.int64)
+    X = synth.point_features(B, T, lens, seed=seed)
+    R = synth.rois(B, T, lens, seed=seed) if use_roi else None
+    y = synth.labels(B, seed=seed)
+    tX, tL, ty = torch.from_numpy(X), torch.from_numpy(lens), torch.from_numpy(y)
+    tR = torch.from_numpy(R) if use_roi else None
+    out = {"param_seed": np.int64(seed), "param_scale": np.float64(scale), "use_roi": np.bool_(use_roi),
+           "X": X, "lengths": lens, "y": y}
+    if use_roi:
+        out["R"] = R
+
+    m = train.BiGRUClassifier(180, 10, use_roi=use_roi, roi_emb=32, hidden=192)
+    m.load_state_dict(p)
+    m.eval()
+    with torch.no_grad():
+        logits = m(tX, tL, tR)
+        out["logits_train_semantics"] = logits.numpy()
+        if use_roi:
+            r = (tR.float() / 255.0).unsqueeze(2)
+            mu = r.mean(dim=(2, 3, 4), keepdim=True); sd = r.std(dim=(2, 3, 4), keepdim=True).clamp_min(1e-6)
+            out["roi_emb"] = m.roi_cnn((r - mu) / sd).numpy()
+    ml = live.BiGRUClassifier(180, 10, use_roi=use_roi, roi_emb=32, hidden=192, gru_layers=2)
+    ml.load_state_dict(p)
+    ml.eval()
+    with torch.no_grad():
+        ll = ml(tX, tL, tR)
+        out["logits_live_semantics"] = ll.numpy()
+    top = live.topk_from_logits(ll[:1], {i: i for i in range(10)}, k=3)
+    out["top3_ids_clip0"] = np.array([t[0] for t in top], np.int64)
+    out["top3_probs_clip0"] = np.array([t[1] for t in top], np.float64)
+
+    # one train step exactly as train_model_official.py:402-405,433-439, dropout inactive (eval)
+    opt = torch.optim.Adam(m.parameters(), lr=train.LR)
+    loss_fn = torch.nn.CrossEntropyLoss(label_smoothing=0.05)
+    loss = loss_fn(m(tX, tL, tR), ty)
+    opt.zero_grad()
+    loss.backward()
+    out["loss"] = np.float64(loss.item())
+    for name, prm in m.named_parameters():
+        out[f"grad_stat/{name}"], out[f"grad_samp/{name}"] = summarise(prm.grad)
+    gn = torch.nn.utils.clip_grad_norm_(m.parameters(), 1.0)
+    out["grad_norm"] = np.float64(gn.item())
+    opt.step()
+    for name, prm in m.named_parameters():
+        out[f"step_stat/{name}"], out[f"step_samp/{name}"] = summarise(prm)
+    np.savez_compressed(os.path.join(OUT, f"model_{tag}.npz"), **out)
+    print(f"model_{tag}.npz loss={loss.item():.6f} gnorm={gn.item():.4f}")
+
+
+def golden_roi_crop(live, record):
+    rng = np.random.default_rng(11)
+    frame = rng.integers(0, 256, size=(360, 640, 3)).astype(np.uint8)
+    # smooth it a little so INTER_AREA / INTER_LINEAR differences are meaningful but bounded
+    import cv2
+    frame = cv2.GaussianBlur(frame, (7, 7), 2.0)
+    centers = np.array([[320.3, 200.7], [30.2, 20.9], [600.0, 340.0], [100.5, 180.25]], np.float32)
+    widths = np.array([80.0, 61.5, 120.0, 1.0], np.float32)
+    outs_live, outs_rec, ok_live, ok_rec = [], [], [], []
+    for c, mw in zip(centers, widths):
+        a = live.crop_roi_gray(frame, c, float(mw)); b = record.crop_roi(frame, c, float(mw))
+        ok_live.append(a is not None); ok_rec.append(b is not None)
+        outs_live.append(a if a is not None else np.zeros((48, 96), np.uint8))
+        outs_rec.append(b if b is not None else np.zeros((48, 96), np.uint8))
+    np.savez_compressed(os.path.join(OUT, "roi_crop.npz"), frame=frame, centers=centers, widths=widths,
+                        roi_live=np.stack(outs_live), roi_record=np.stack(outs_rec),
+                        ok_live=np.array(ok_live), ok_record=np.array(ok_rec))
+    print("roi_crop.npz", ok_live, ok_rec)
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    train, live, record = import_reference()
+    torch.set_num_threads(1)                 # deterministic reduction order for the fixtures
+    golden_features(live, record)
+    golden_model(train, live, "roi", True, B=4, T=12, lens=[12, 5, 1, 9], seed=101)
+    golden_model(train, live, "points", False, B=5, T=20, lens=[20, 6, 13, 1, 17], seed=102)
+    golden_model(train, live, "roi_hot", True, B=3, T=10, lens=[7, 10, 3], seed=103, scale=2.0)
+    golden_roi_crop(live, record)
+
+
+if __name__ == "__main__":
+    main()

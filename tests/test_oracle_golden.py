@@ -1,0 +1,81 @@
+"""The oracle against the committed outputs of the reference itself
+(tests/golden/*.npz, produced by oracle/make_golden.py from /root/reference)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_explicit, ref_features, ref_model
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def test_landmark_set_known_answers():
+    # record_landmarks_official.py:44-46 prints "should be 88 points"; x_dim = 2K+4 = 180
+    ids = ref_features.LANDMARK_IDS
+    assert len(ids) == 88 and ids.max() == 436 and list(ids) == sorted(set(ids.tolist()))
+    pos = {int(v): i for i, v in enumerate(ids)}
+    assert (pos[61], pos[291], pos[13], pos[14]) == (11, 50, 1, 2)
+
+
+@pytest.mark.parametrize("flavour", ["live", "record"])
+def test_features_match_reference(golden_dir, flavour):
+    g = _load(golden_dir, "features.npz")
+    assert np.array_equal(g["ids"], ref_features.LANDMARK_IDS)
+    lm, present = g["lm"], g["present"]
+    for b in range(lm.shape[0]):
+        o = ref_features.clip_features(lm[b], int(g["w"]), int(g["h"]), present=present[b], flavour=flavour)
+        assert np.array_equal(o["valid"], g[f"valid_{flavour}"][b])
+        assert np.array_equal(o["X"], g[f"X_{flavour}"][b])          # same numpy ops -> bit-exact
+        assert np.array_equal(o["center"], g[f"center_{flavour}"][b])
+    assert g["valid_live"].sum() < g["valid_live"].size              # gate / absent frames exercised
+
+
+def _inputs(g):
+    p = ref_model.synth_params(int(g["param_seed"]), use_roi=bool(g["use_roi"]), scale=float(g["param_scale"]))
+    X, L, y = torch.from_numpy(g["X"]), torch.from_numpy(g["lengths"]), torch.from_numpy(g["y"])
+    R = torch.from_numpy(g["R"]) if bool(g["use_roi"]) else None
+    return p, X, L, R, y
+
+
+@pytest.mark.parametrize("name", ["model_roi.npz", "model_points.npz", "model_roi_hot.npz"])
+def test_forward_matches_reference(golden_dir, name):
+    g = _load(golden_dir, name)
+    p, X, L, R, y = _inputs(g)
+    torch.set_num_threads(1)
+    out = ref_model.forward(p, X, L, R, standardize_roi=True, want_intermediates=True)
+    np.testing.assert_allclose(out["logits"].numpy(), g["logits_train_semantics"], rtol=0, atol=2e-6)
+    live = ref_model.forward(p, X, L, R, standardize_roi=False)
+    np.testing.assert_allclose(live.numpy(), g["logits_live_semantics"], rtol=0, atol=2e-6)
+    if R is not None:
+        np.testing.assert_allclose(out["roi_emb"].numpy(), g["roi_emb"], rtol=0, atol=2e-6)
+        assert np.abs(g["logits_train_semantics"] - g["logits_live_semantics"]).max() > 1e-4   # the skew is real
+    ids, probs = ref_model.topk(live[:1])
+    assert ids[0].tolist() == g["top3_ids_clip0"].tolist()
+    np.testing.assert_allclose(probs[0].numpy(), g["top3_probs_clip0"], atol=1e-6)
+    # float64 explicit math agrees with ATen fp32 to fp32 noise
+    ex = ref_explicit.forward(p, X, L, R)
+    np.testing.assert_allclose(ex["logits"].numpy(), g["logits_train_semantics"], rtol=0, atol=2e-5)
+
+
+@pytest.mark.parametrize("name", ["model_roi.npz", "model_points.npz", "model_roi_hot.npz"])
+def test_train_step_matches_reference(golden_dir, name):
+    g = _load(golden_dir, name)
+    p, X, L, R, y = _inputs(g)
+    torch.set_num_threads(1)
+    loss, _, grads = ref_model.loss_and_grads(p, X, L, R, y)
+    assert abs(loss.item() - float(g["loss"])) < 1e-6
+    for k, gr in grads.items():
+        samp = gr.reshape(-1)[::97].numpy()
+        ref = g[f"grad_samp/{k}"]
+        assert np.abs(samp - ref).max() <= 1e-6 + 1e-5 * np.abs(ref).max(), k
+        assert abs(gr.double().norm().item() - g[f"grad_stat/{k}"][0]) <= 1e-5 * max(1.0, g[f"grad_stat/{k}"][0]), k
+    st = ref_model.AdamState(p)
+    l2, _, gn = st.step(X, L, R, y)
+    assert abs(gn.item() - float(g["grad_norm"])) < 1e-4 * float(g["grad_norm"])
+    for k, v in st.params().items():
+        ref = g[f"step_samp/{k}"]
+        assert np.abs(v.reshape(-1)[::97].numpy() - ref).max() <= 1e-6, k
