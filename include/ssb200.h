@@ -1,0 +1,99 @@
+/* libssb200 -- C ABI of the B200-native Silent-Speech clip-classification hot path.
+ *
+ * The reference (davdwan21/Silent-Speech) is pure Python/PyTorch and has no FFI; the
+ * boundary it exposes for this path is the Python call contract of
+ *   BiGRUClassifier.forward(X, lengths, R)      train_model_official.py:279-310, live_infer_official.py:124-138
+ *   extract_feature(face, w, h, idxs, prev_xy)  live_infer_official.py:146-169, record_landmarks_official.py:62-100
+ *   the train step                              train_model_official.py:433-439
+ * This library is what a ctypes binding behind those calls loads (INTEGRATION.md shows it).
+ *
+ * Conventions
+ *  - Every pointer is a raw DEVICE pointer unless the name ends in _host; sizes are explicit.
+ *  - `stream` is a cudaStream_t; calls only enqueue work on it and return (asynchronous).
+ *  - Return value: 0 = ok, non-zero = error; ssb_last_error() gives the thread-local message.
+ *  - The caller owns every buffer (inputs, outputs, saved-for-backward, workspaces); the
+ *    library allocates nothing persistent.
+ *  - Built for sm_100a only.  There is no CPU fallback: without a B200 the calls fail.
+ *  - All floating point is fp32; ROI pixels are uint8; lengths/labels int64; landmark ids int32.
+ */
+#ifndef SSB200_H_
+#define SSB200_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int ssb_version(void);
+const char* ssb_last_error(void);
+int ssb_device_info(int32_t* sm_count, int32_t* cc_major, int32_t* cc_minor);
+
+/* K1: per-frame landmark features for a batch of clips.
+ * Replaces extract_feature + mouth_width_px + the capture loop's distance gate / velocity reset
+ * (live_infer_official.py:141-169, 275-296).
+ * landmarks [B,T,n_lm,lm_stride] (x,y first), ids [K<=128], anchor_ids = {left corner 61,
+ * right corner 291, upper inner 13, lower inner 14} as landmark ids, present [B,T] or NULL.
+ * X [B,T,2K+4]; center [B,T,2], mouth_w [B,T], valid [B,T], lengths [B] may be NULL.
+ * compact != 0 packs the used frames to the front of each clip (what the reference's bufX holds)
+ * and writes their count to lengths; otherwise skipped frames give zero rows in place. */
+int ssb_features_fwd(const float* landmarks, int64_t B, int64_t T, int64_t n_lm, int64_t lm_stride,
+                     const int32_t* ids, int32_t K, const int32_t anchor_ids_host[4],
+                     const uint8_t* present, float frame_w, float frame_h,
+                     float gate_min_px, float gate_max_px, int32_t compact,
+                     float* X, float* center, float* mouth_w, uint8_t* valid, int64_t* lengths,
+                     void* stream);
+
+/* K2: fused mouth-ROI CNN forward (normalise, per-frame standardise, TinyROICNN).
+ * Replaces train_model_official.py:286-294 (standardize=1) / live_infer_official.py:126-127 (0).
+ * R [B,T,48,96] u8; weights_host = 8 device pointers {net.0.w,b, net.3.w,b, net.6.w,b, fc.w,b};
+ * out[(b*T+t)*out_stride + 0..31] receives the embedding (zeros for t >= lengths[b]). */
+int ssb_roi_cnn_fwd(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
+                    int32_t roi_h, int32_t roi_w, const float* const* weights_host,
+                    int32_t standardize, float* out, int64_t out_stride, void* stream);
+
+/* fp32 strided GEMM: C[i,j] (+)= sum_k A[i*sai+k*sak] * B[k*sbk+j*sbj] (+ bias[j]).
+ * The ATen matmuls inside nn.GRU / nn.Linear of the reference (train_model_official.py:261-277)
+ * and their backward.  lengths/T (optional) skip 64-row tiles made only of padded frames. */
+int ssb_sgemm(const float* A, int64_t sai, int64_t sak, const float* B, int64_t sbk, int64_t sbj,
+              const float* bias, float* C, int64_t ldc, int64_t M, int64_t N, int64_t K,
+              int32_t accumulate, int32_t split_k, const int64_t* lengths, int64_t T, void* stream);
+
+/* K3b: one bidirectional GRU layer's time recurrence on packed-sequence semantics
+ * (nn.GRU, train_model_official.py:261-267, 301-305).  gi [B,T,gi_ld]: input projections incl.
+ * b_ih, forward direction at column 0, reverse at 576.  out [B,T,384] (zeros past lengths).
+ * gates (NULL for inference) [B,T,2,4,192] saves r, z, n, W_hn h + b_hn for the backward pass. */
+int ssb_gru_layer_fwd(const float* gi, int64_t gi_ld, const int64_t* lengths, int64_t B, int64_t T,
+                      int32_t hidden, const float* whh_f, const float* bhh_f,
+                      const float* whh_r, const float* bhh_r, float* out, float* gates, void* stream);
+
+/* K4: AttnPool + LayerNorm + Linear/ReLU/Dropout/Linear (+ softmax, top-k, label-smoothed CE).
+ * Replaces train_model_official.py:240-248, 271-277, 405 and live_infer_official.py:223-226.
+ * weights_host = 8 device pointers {pool.score.w,b, head.0.w,b, head.1.w,b, head.4.w,b};
+ * saved_host = NULL or 6 device pointers {attn[B,T], pooled[B,384], xhat[B,384], rstd[B],
+ * ln[B,384], hid[B,128]}.  probs, topk_*, y/loss may be NULL. loss[b] is the per-clip term. */
+int ssb_head_fwd(const float* seq, const int64_t* lengths, int64_t B, int64_t T, int32_t dim,
+                 const float* const* weights_host, int32_t num_classes, float* const* saved_host,
+                 float* logits, float* probs, int32_t* topk_ids, float* topk_probs, int32_t k_top,
+                 const int64_t* y, float label_smoothing, float* loss,
+                 float dropout_p, uint64_t seed, void* stream);
+
+/* K4-bwd part 1: gradient at the logits (fused CE when dlogits_in == NULL:
+ * grad_scale * (softmax - smoothed one-hot)) and back through head.4 / Dropout / ReLU. */
+int ssb_head_bwd_logits(const float* logits, const float* dlogits_in, const int64_t* y,
+                        float label_smoothing, float grad_scale, const float* w2, const float* hid,
+                        float dropout_p, int64_t B, int32_t num_classes,
+                        float* dlogits, float* dhid, void* stream);
+
+/* K4-bwd part 2: back through LayerNorm and AttnPool.  Overwrites dseq [B,T,384]; accumulates
+ * into d_ln_g[384], d_ln_b[384], d_ws[384], d_bs[1]. */
+int ssb_head_bwd_pool(const float* dln, const float* xhat, const float* rstd, const float* attn,
+                      const float* seq, const int64_t* lengths, int64_t B, int64_t T,
+                      const float* ln_g, const float* ws, float* dseq,
+                      float* d_ln_g, float* d_ln_b, float* d_ws, float* d_bs, void* stream);
+
+/* out[j] += sum_i A[i*lda + j]  (bias gradients). */
+int ssb_colsum(const float* A, int64_t lda, int64_t M, int64_t N, float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSB200_H_ */

@@ -1,0 +1,10 @@
+"""silent_speech_b200 -- B200-native (sm_100a) implementation of the Silent-Speech
+batched clip-classification hot path: landmark features, mouth-ROI CNN, 2-layer BiGRU,
+attention-pooled word head and its train step, behind the C ABI of include/ssb200.h.
+
+The package never falls back to eager PyTorch or the CPU: if libssb200.so is missing
+or the tensors are not on a B200 the calls raise."""
+from .landmarks import FIXED_IDXS, extract_feature, extract_features  # noqa: F401
+from .model import BiGRUClassifier, load_classifier  # noqa: F401
+
+__all__ = ["BiGRUClassifier", "load_classifier", "extract_features", "extract_feature", "FIXED_IDXS"]

@@ -1,0 +1,100 @@
+"""Forward / backward orchestration of the classifier over the C-ABI kernels.
+
+Stage order follows BiGRUClassifier.forward (train_model_official.py:279-310):
+  K2 ROI CNN -> K3a input projections (GEMM, both directions stacked into one [B,T,1152]
+  buffer; the concat of train:297 is never materialised -- X and the ROI embedding are two
+  K-slices of the same projection) -> K3b recurrence, layer 0 -> (dropout 0.1, train only)
+  -> K3a/K3b layer 1 -> K4 pooled head.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import ops
+
+H = ops.HIDDEN
+G3 = 3 * H
+
+
+class Workspace:
+    """Per-call buffers (allocated by PyTorch's caching allocator; the library owns nothing)."""
+
+    def __init__(self):
+        self.saved = {}
+
+
+def _project(A2d, w_pair, b_pair, gi2d, lengths, T, extra=None, x_dim=None):
+    """gi[:, d*576:(d+1)*576] = A @ W_ih_d^T + b_ih_d (+ E @ W_ih_d[:, x_dim:]^T) for d = fwd, rev."""
+    for d in (0, 1):
+        W, b = w_pair[d], b_pair[d]
+        k = A2d.shape[1]
+        ops.linear_nt(A2d, W, b, gi2d, lengths=lengths, T=T, k=k, c_col0=d * G3)
+        if extra is not None:
+            ops.linear_nt(extra, W, None, gi2d, accumulate=True, lengths=lengths, T=T,
+                          w_col0=k, k=extra.shape[1], c_col0=d * G3)
+
+
+def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 0, y=None,
+                 label_smoothing: float = 0.0):
+    dev = X.device
+    if not X.is_cuda:
+        raise ops._lib.SsbError("inputs must be CUDA tensors: this package has no CPU path")
+    X = X.contiguous().float()
+    lengths = lengths.to(device=dev, dtype=torch.int64).contiguous()
+    B, T, x_dim = X.shape
+    ctx = {"B": B, "T": T, "lengths": lengths, "X": X}
+    emb = None
+    if R is not None:
+        R = R.to(dev).contiguous()
+        emb = ops.roi_cnn_fwd(R, lengths, model.roi_cnn.tensors(), standardize=model.standardize_roi)
+        ctx["R"] = R
+        ctx["emb"] = emb
+    gi = torch.empty(B, T, 2 * G3, device=dev, dtype=torch.float32)
+    gi2d = gi.view(B * T, 2 * G3)
+    p0, p1 = model.gru.layer(0), model.gru.layer(1)
+
+    _project(X.view(B * T, x_dim), p0["weight_ih"], p0["bias_ih"], gi2d, lengths, T,
+             extra=None if emb is None else emb.view(B * T, -1))
+    gates0 = torch.empty(B, T, 2, 4, H, device=dev, dtype=torch.float32) if save else None
+    seq0 = ops.gru_layer_fwd(gi, lengths, p0["weight_hh"][0], p0["bias_hh"][0], p0["weight_hh"][1],
+                             p0["bias_hh"][1], gates=gates0)
+    seq0_in = seq0
+    drop_seed = 0
+    if training and model.gru_dropout > 0:
+        drop_seed = model._next_seed()
+        seq0_in = ops.dropout(seq0, model.gru_dropout, drop_seed)
+    _project(seq0_in.view(B * T, 2 * H), p1["weight_ih"], p1["bias_ih"], gi2d, lengths, T)
+    gates1 = torch.empty(B, T, 2, 4, H, device=dev, dtype=torch.float32) if save else None
+    seq1 = ops.gru_layer_fwd(gi, lengths, p1["weight_hh"][0], p1["bias_hh"][0], p1["weight_hh"][1],
+                             p1["bias_hh"][1], gates=gates1)
+    saved = None
+    if save:
+        saved = [torch.empty(B, T, device=dev), torch.empty(B, 2 * H, device=dev), torch.empty(B, 2 * H, device=dev),
+                 torch.empty(B, device=dev), torch.empty(B, 2 * H, device=dev), torch.empty(B, 128, device=dev)]
+    head_p = model.head_dropout if training else 0.0
+    head_seed = model._next_seed() if head_p > 0 else 0
+    out = ops.head_fwd(seq1, lengths, model.head_tensors(), model.num_classes, saved=saved,
+                       want_probs=k_top > 0, k_top=k_top, y=y, label_smoothing=label_smoothing,
+                       dropout_p=head_p, seed=head_seed)
+    ctx.update(seq0=seq0, seq0_in=seq0_in, seq1=seq1, gates0=gates0, gates1=gates1, head_saved=saved,
+               drop_seed=drop_seed, gru_p=model.gru_dropout if training else 0.0, head_p=head_p,
+               logits=out["logits"])
+    return out, ctx
+
+
+def classifier_forward(model, X, lengths, R=None, k_top: int = 0):
+    if not X.is_cuda:
+        raise ops._lib.SsbError("inputs must be CUDA tensors: this package has no CPU path")
+    needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in model.parameters())
+    if k_top or not needs_grad:
+        with torch.no_grad():
+            out, _ = forward_impl(model, X, lengths, R, training=model.training and needs_grad, save=False, k_top=k_top)
+        if k_top:
+            return out["topk_ids"], out["topk_probs"], out["logits"]
+        return out["logits"]
+    from .autograd import ClassifierFn
+    names = [n for n, _ in model.named_parameters()]
+    params = [p for _, p in model.named_parameters()]
+    return ClassifierFn.apply(model, names, X, lengths, R, *params)

@@ -1,0 +1,170 @@
+"""Thin tensor-level wrappers over the C ABI (one Python function per extern "C" entry).
+
+PyTorch is used for device memory and streams only: every function below checks
+shapes/dtypes, hands raw device pointers to libssb200.so and returns the output
+tensors it allocated.  All compute happens in the CUDA library; nothing here has an
+eager fallback (calls raise if the library is missing or the tensors are not CUDA)."""
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import check, f32, i32, i64, ptr, ptr_array, stream_ptr, u64
+
+HIDDEN = 192
+ROI_H, ROI_W, ROI_EMB = 48, 96, 32
+
+
+def _need(t: torch.Tensor, dtype, name: str):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda):
+        raise _lib.SsbError(f"{name} must be a CUDA tensor (this package has no CPU path)")
+    if t.dtype != dtype:
+        raise _lib.SsbError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise _lib.SsbError(f"{name} must be contiguous")
+    return t
+
+
+def device_info():
+    sm, major, minor = i32(), i32(), i32()
+    import ctypes
+    check(_lib.lib().ssb_device_info(ctypes.byref(sm), ctypes.byref(major), ctypes.byref(minor)))
+    return sm.value, major.value, minor.value
+
+
+# ----------------------------------------------------------------------------- K1
+def features_fwd(landmarks: torch.Tensor, ids: torch.Tensor, anchor_ids: Sequence[int],
+                 frame_w: float, frame_h: float, present: Optional[torch.Tensor] = None,
+                 gate=(60.0, 150.0), compact: bool = False):
+    """landmarks f32 [B,T,N,S>=2] -> dict(X [B,T,2K+4], center, mouth_w, valid, lengths)."""
+    _need(landmarks, torch.float32, "landmarks")
+    _need(ids, torch.int32, "ids")
+    B, T, N, S = landmarks.shape
+    K = ids.numel()
+    if present is not None:
+        _need(present, torch.uint8, "present")
+    dev = landmarks.device
+    X = torch.empty(B, T, 2 * K + 4, device=dev, dtype=torch.float32)
+    center = torch.empty(B, T, 2, device=dev, dtype=torch.float32)
+    mouth_w = torch.empty(B, T, device=dev, dtype=torch.float32)
+    valid = torch.empty(B, T, device=dev, dtype=torch.uint8)
+    lengths = torch.full((B,), T, device=dev, dtype=torch.int64)
+    lo, hi = (-float("inf"), float("inf")) if gate is None else gate
+    anchors = (i32 * 4)(*[int(a) for a in anchor_ids])
+    check(_lib.lib().ssb_features_fwd(ptr(landmarks), i64(B), i64(T), i64(N), i64(S), ptr(ids), i32(K), anchors,
+                                      ptr(present), f32(frame_w), f32(frame_h), f32(lo), f32(hi),
+                                      i32(1 if compact else 0), ptr(X), ptr(center), ptr(mouth_w), ptr(valid),
+                                      ptr(lengths), stream_ptr()))
+    if not compact:
+        lengths = valid.sum(dim=1, dtype=torch.int64)
+    return {"X": X, "center": center, "mouth_w": mouth_w, "valid": valid, "lengths": lengths}
+
+
+# ----------------------------------------------------------------------------- K2
+def roi_cnn_fwd(R: torch.Tensor, lengths: Optional[torch.Tensor], weights: Sequence[torch.Tensor],
+                standardize: bool = True, out: Optional[torch.Tensor] = None, out_col: int = 0) -> torch.Tensor:
+    """R u8 [B,T,48,96] -> embedding f32 [B,T,32] (or written into out[..., out_col:out_col+32])."""
+    _need(R, torch.uint8, "R")
+    B, T, Hh, Ww = R.shape
+    for w in weights:
+        _need(w, torch.float32, "roi weight")
+    if lengths is not None:
+        _need(lengths, torch.int64, "lengths")
+    if out is None:
+        out = torch.empty(B, T, ROI_EMB, device=R.device, dtype=torch.float32)
+        out_col = 0
+    _need(out, torch.float32, "out")
+    stride = out.shape[-1]
+    base = out.data_ptr() + 4 * out_col
+    import ctypes
+    check(_lib.lib().ssb_roi_cnn_fwd(ptr(R), ptr(lengths), i64(B), i64(T), i32(Hh), i32(Ww), ptr_array(weights),
+                                     i32(1 if standardize else 0), ctypes.c_void_p(base), i64(stride), stream_ptr()))
+    return out
+
+
+# ----------------------------------------------------------------------------- GEMM
+def sgemm(A: torch.Tensor, Bm: torch.Tensor, C: torch.Tensor, M: int, N: int, K: int,
+          sa=(None, None), sb=(None, None), ldc: Optional[int] = None, bias: Optional[torch.Tensor] = None,
+          accumulate: bool = False, split_k: int = 1, lengths: Optional[torch.Tensor] = None, T: int = 0,
+          a_off: int = 0, b_off: int = 0, c_off: int = 0):
+    """C[i,j] (+)= sum_k A[a_off + i*sai + k*sak] * B[b_off + k*sbk + j*sbj] (+ bias[j]); element offsets/strides."""
+    import ctypes
+    check(_lib.lib().ssb_sgemm(ctypes.c_void_p(A.data_ptr() + 4 * a_off), i64(sa[0]), i64(sa[1]),
+                               ctypes.c_void_p(Bm.data_ptr() + 4 * b_off), i64(sb[0]), i64(sb[1]), ptr(bias),
+                               ctypes.c_void_p(C.data_ptr() + 4 * c_off), i64(ldc), i64(M), i64(N), i64(K),
+                               i32(1 if accumulate else 0), i32(split_k), ptr(lengths), i64(T), stream_ptr()))
+    return C
+
+
+def linear_nt(A2d: torch.Tensor, W: torch.Tensor, bias, C2d: torch.Tensor, accumulate=False,
+              lengths=None, T=0, w_col0: int = 0, k: Optional[int] = None, c_col0: int = 0):
+    """C[:, c_col0:c_col0+N] (+)= A @ W[:, w_col0:w_col0+k]^T (+ bias).  A [M,k] rows contiguous."""
+    M, Ka = A2d.shape
+    N = W.shape[0]
+    k = Ka if k is None else k
+    return sgemm(A2d, W, C2d, M, N, k, sa=(A2d.stride(0), 1), sb=(1, W.stride(0)), ldc=C2d.stride(0), bias=bias,
+                 accumulate=accumulate, lengths=lengths, T=T, b_off=w_col0, c_off=c_col0)
+
+
+# ----------------------------------------------------------------------------- K3b
+def gru_layer_fwd(gi: torch.Tensor, lengths: torch.Tensor, whh_f, bhh_f, whh_r, bhh_r,
+                  out: Optional[torch.Tensor] = None, gates: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _need(gi, torch.float32, "gi")
+    _need(lengths, torch.int64, "lengths")
+    B, T, ld = gi.shape
+    if out is None:
+        out = torch.empty(B, T, 2 * HIDDEN, device=gi.device, dtype=torch.float32)
+    check(_lib.lib().ssb_gru_layer_fwd(ptr(gi), i64(ld), ptr(lengths), i64(B), i64(T), i32(HIDDEN),
+                                       ptr(whh_f), ptr(bhh_f), ptr(whh_r), ptr(bhh_r), ptr(out), ptr(gates),
+                                       stream_ptr()))
+    return out
+
+
+# ----------------------------------------------------------------------------- K4
+def head_fwd(seq: torch.Tensor, lengths: torch.Tensor, weights: Sequence[torch.Tensor], num_classes: int,
+             saved: Optional[Sequence[torch.Tensor]] = None, want_probs: bool = False, k_top: int = 0,
+             y: Optional[torch.Tensor] = None, label_smoothing: float = 0.0, dropout_p: float = 0.0,
+             seed: int = 0):
+    _need(seq, torch.float32, "seq")
+    _need(lengths, torch.int64, "lengths")
+    B, T, D = seq.shape
+    dev = seq.device
+    logits = torch.empty(B, num_classes, device=dev, dtype=torch.float32)
+    probs = torch.empty(B, num_classes, device=dev, dtype=torch.float32) if want_probs else None
+    ids = torch.empty(B, k_top, device=dev, dtype=torch.int32) if k_top else None
+    tp = torch.empty(B, k_top, device=dev, dtype=torch.float32) if k_top else None
+    loss = torch.empty(B, device=dev, dtype=torch.float32) if y is not None else None
+    check(_lib.lib().ssb_head_fwd(ptr(seq), ptr(lengths), i64(B), i64(T), i32(D), ptr_array(weights),
+                                  i32(num_classes), ptr_array(saved) if saved is not None else None,
+                                  ptr(logits), ptr(probs), ptr(ids), ptr(tp), i32(k_top), ptr(y),
+                                  f32(label_smoothing), ptr(loss), f32(dropout_p), u64(seed), stream_ptr()))
+    return {"logits": logits, "probs": probs, "topk_ids": ids, "topk_probs": tp, "loss": loss}
+
+
+def head_bwd_logits(logits, dlogits_in, y, label_smoothing, grad_scale, w2, hid, dropout_p):
+    B, C = (logits if logits is not None else dlogits_in).shape
+    dev = hid.device
+    dlogits = torch.empty(B, C, device=dev, dtype=torch.float32)
+    dhid = torch.empty(B, 128, device=dev, dtype=torch.float32)
+    check(_lib.lib().ssb_head_bwd_logits(ptr(logits), ptr(dlogits_in), ptr(y), f32(label_smoothing), f32(grad_scale),
+                                         ptr(w2), ptr(hid), f32(dropout_p), i64(B), i32(C), ptr(dlogits), ptr(dhid),
+                                         stream_ptr()))
+    return dlogits, dhid
+
+
+def head_bwd_pool(dln, xhat, rstd, attn, seq, lengths, ln_g, ws, d_ln_g, d_ln_b, d_ws, d_bs, dseq=None):
+    B, T, D = seq.shape
+    if dseq is None:
+        dseq = torch.empty_like(seq)
+    check(_lib.lib().ssb_head_bwd_pool(ptr(dln), ptr(xhat), ptr(rstd), ptr(attn), ptr(seq), ptr(lengths), i64(B), i64(T),
+                                       ptr(ln_g), ptr(ws), ptr(dseq), ptr(d_ln_g), ptr(d_ln_b), ptr(d_ws), ptr(d_bs),
+                                       stream_ptr()))
+    return dseq
+
+
+def colsum(A2d: torch.Tensor, out: torch.Tensor):
+    M, N = A2d.shape
+    check(_lib.lib().ssb_colsum(ptr(A2d), i64(A2d.stride(0)), i64(M), i64(N), ptr(out), stream_ptr()))
+    return out

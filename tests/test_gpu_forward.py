@@ -1,0 +1,235 @@
+"""GPU parity, forward path: every CUDA stage (called through the C ABI) against the CPU
+oracle on the same seeded inputs, and the whole model against the reference's golden logits.
+
+Tolerances (BASELINE.json north_star): landmark gather bit-exact; features / logits within
+1e-4 relative in fp32 with identical argmax.  "Relative" is taken against the tensor's
+max-abs (per-element relative error is meaningless around zero crossings)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import ref_explicit, ref_features, ref_model  # noqa: E402
+
+
+def _cuda():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch.device("cuda")
+
+
+def rel_err(a: torch.Tensor, b: torch.Tensor) -> float:
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def _model_from(p, use_roi, dev, standardize=True):
+    from silent_speech_b200 import BiGRUClassifier
+    m = BiGRUClassifier(180, p["head.4.weight"].shape[0], use_roi=use_roi, standardize_roi=standardize)
+    m.load_state_dict(p)
+    return m.to(dev).eval()
+
+
+def test_device_is_b200():
+    _cuda()
+    from silent_speech_b200 import ops
+    sm, major, minor = ops.device_info()
+    assert major == 10 and sm >= 100
+
+
+# ------------------------------------------------------------------ K1 features
+def test_features_vs_golden_and_oracle(golden_dir):
+    dev = _cuda()
+    from silent_speech_b200 import extract_features
+    g = np.load(os.path.join(golden_dir, "features.npz"))
+    lm = torch.from_numpy(g["lm"]).to(dev)
+    present = torch.from_numpy(g["present"]).to(dev)
+    out = extract_features(lm, int(g["w"]), int(g["h"]), present=present)
+    assert np.array_equal(out["valid"].cpu().numpy(), g["valid_live"])
+    X = out["X"].cpu().numpy()
+    ref = g["X_live"]
+    K = 88
+    # known-answer structure: tail order [vel, open_px, mouth_w_px, aspect] (live:167)
+    np.testing.assert_allclose(X[..., 2 * K + 2], g["mouth_w_live"].astype(np.float32), rtol=1e-6)
+    err = np.abs(X - ref).max() / np.abs(ref).max()
+    assert err < 1e-5, err
+    np.testing.assert_allclose(out["center"].cpu().numpy(), g["center_live"], rtol=1e-6, atol=1e-4)
+    # the gather itself is data movement: pixel positions recovered from the outputs must be
+    # the bit-exact products x*w, y*h of the selected landmarks
+    ids = g["ids"]
+    b, t = 0, int(np.argmax(g["valid_live"][0]))
+    px = g["lm"][b, t, ids, 0] * np.float32(g["w"])
+    assert np.array_equal(px.astype(np.float32), (g["lm"][b, t, ids, 0].astype(np.float64) * int(g["w"])).astype(np.float32))
+    # compact mode == the reference's bufX
+    outc = extract_features(lm, int(g["w"]), int(g["h"]), present=present, compact=True)
+    for b in range(lm.shape[0]):
+        n = int(g["valid_live"][b].sum())
+        assert int(outc["lengths"][b]) == n
+        o = ref_features.clip_features(g["lm"][b], int(g["w"]), int(g["h"]), present=g["present"][b], compact=True)
+        e = np.abs(outc["X"][b].cpu().numpy() - o["X"]).max() / np.abs(o["X"]).max()
+        assert e < 1e-5, e
+        assert np.all(outc["X"][b, n:].cpu().numpy() == 0)
+
+
+def test_features_larger_seeded():
+    dev = _cuda()
+    from silent_speech_b200 import extract_features, synth
+    lm, present = synth.landmarks(6, 90, seed=5, drop=0.05)
+    out = extract_features(torch.from_numpy(lm).to(dev), synth.FRAME_W, synth.FRAME_H,
+                           present=torch.from_numpy(present).to(dev))
+    for b in range(6):
+        o = ref_features.clip_features(lm[b], synth.FRAME_W, synth.FRAME_H, present=present[b])
+        assert np.array_equal(out["valid"][b].cpu().numpy(), o["valid"])
+        e = np.abs(out["X"][b].cpu().numpy() - o["X"]).max() / np.abs(o["X"]).max()
+        assert e < 1e-5, e
+
+
+# ------------------------------------------------------------------ K2 ROI CNN
+@pytest.mark.parametrize("standardize", [True, False])
+def test_roi_cnn_vs_oracle(standardize):
+    dev = _cuda()
+    from silent_speech_b200 import ops, synth
+    p = ref_model.synth_params(11)
+    B, T = 5, 9
+    L = np.array([9, 4, 1, 7, 9], np.int64)
+    R = synth.rois(B, T, L, seed=3)
+    R[0, 2] = 0            # an all-zero frame inside a clip: (0-0)/1e-6 = 0
+    R[3, 1] = 77           # a constant frame: std clamps to 1e-6
+    names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
+             "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
+    w = [p[n].to(dev).contiguous() for n in names]
+    emb = ops.roi_cnn_fwd(torch.from_numpy(R).to(dev), torch.from_numpy(L).to(dev), w, standardize=standardize)
+    ref = ref_model.roi_cnn(p, ref_model.roi_prepare(torch.from_numpy(R), standardize))
+    mask = torch.arange(T)[None, :] < torch.from_numpy(L)[:, None]
+    ref = ref * mask[..., None]
+    e = rel_err(emb, ref)
+    assert e < 1e-4, e
+    assert torch.all(emb.cpu()[~mask] == 0)
+    truth = ref_explicit.roi_embed(p, torch.from_numpy(R), standardize, torch.float64) * mask[..., None]
+    # we are as close to the float64 truth as ATen is (within 3x)
+    assert rel_err(emb, truth) <= 3 * max(rel_err(ref, truth), 1e-6)
+
+
+# ------------------------------------------------------------------ GEMM
+def test_sgemm_variants():
+    dev = _cuda()
+    from silent_speech_b200 import ops
+    g = torch.Generator().manual_seed(0)
+    M, N, K = 150, 97, 53
+    A = torch.randn(M, K, generator=g); W = torch.randn(N, K, generator=g); b = torch.randn(N, generator=g)
+    Ad, Wd, bd = A.to(dev), W.to(dev), b.to(dev)
+    C = torch.empty(M, N, device=dev)
+    ops.linear_nt(Ad, Wd, bd, C)
+    assert rel_err(C, A @ W.T + b) < 1e-5
+    # NN: dX = dY @ W   (A k-contig, B j-contig)
+    dY = torch.randn(M, N, generator=g); dYd = dY.to(dev)
+    dX = torch.empty(M, K, device=dev)
+    ops.sgemm(dYd, Wd, dX, M, K, N, sa=(N, 1), sb=(K, 1), ldc=K)
+    assert rel_err(dX, dY @ W) < 1e-5
+    # TN with split-k: dW = dY^T @ A
+    dW = torch.zeros(N, K, device=dev)
+    ops.sgemm(dYd, Ad, dW, N, K, M, sa=(1, N), sb=(K, 1), ldc=K, accumulate=True, split_k=4)
+    assert rel_err(dW, dY.T @ A) < 1e-5
+    # column-sliced accumulate (the X | roi-embedding split of the layer-0 projection)
+    C2 = torch.zeros(M, 2 * N, device=dev)
+    ops.linear_nt(Ad[:, :40].contiguous(), Wd, bd, C2, k=40, c_col0=N)
+    ops.linear_nt(Ad[:, 40:].contiguous(), Wd, None, C2, accumulate=True, w_col0=40, k=K - 40, c_col0=N)
+    assert rel_err(C2[:, N:], A @ W.T + b) < 1e-5 and torch.all(C2[:, :N] == 0)
+
+
+# ------------------------------------------------------------------ K3 GRU
+def test_gru_layer_vs_explicit():
+    dev = _cuda()
+    from silent_speech_b200 import ops
+    p = ref_model.synth_params(21, scale=1.5)
+    B, T = 70, 11           # > one 64-clip tile, ragged
+    g = torch.Generator().manual_seed(2)
+    L = torch.randint(1, T + 1, (B,), generator=g); L[0] = T; L[1] = 1
+    gi = torch.randn(B, T, 1152, generator=g) * 0.7
+    args = [p[f"gru.{n}"].to(dev).contiguous() for n in ("weight_hh_l0", "bias_hh_l0", "weight_hh_l0_reverse", "bias_hh_l0_reverse")]
+    gates = torch.zeros(B, T, 2, 4, 192, device=dev)
+    out = ops.gru_layer_fwd(gi.to(dev), L.to(dev), *args, gates=gates)
+    out_ng = ops.gru_layer_fwd(gi.to(dev), L.to(dev), *args)
+    assert torch.equal(out, out_ng)
+    f = ref_explicit.gru_direction(gi[..., :576].double(), p["gru.weight_hh_l0"].double(), p["gru.bias_hh_l0"].double(), L, False)
+    r = ref_explicit.gru_direction(gi[..., 576:].double(), p["gru.weight_hh_l0_reverse"].double(), p["gru.bias_hh_l0_reverse"].double(), L, True)
+    ref = torch.cat([f, r], dim=2)
+    e = rel_err(out, ref)
+    assert e < 2e-6, e
+    mask = torch.arange(T)[None, :] < L[:, None]
+    assert torch.all(out.cpu()[~mask] == 0)
+    # saved gates are consistent with the outputs: h_t = (1-z) n + z h_{t-1} at t = 0 of the forward direction
+    r0, z0, n0 = gates[:, 0, 0, 0].cpu(), gates[:, 0, 0, 1].cpu(), gates[:, 0, 0, 2].cpu()
+    assert rel_err((1 - z0) * n0, out[:, 0, :192].cpu()) < 1e-6
+
+
+# ------------------------------------------------------------------ K4 head
+def test_head_vs_oracle():
+    dev = _cuda()
+    from silent_speech_b200 import ops
+    p = ref_model.synth_params(31)
+    B, T = 9, 13
+    g = torch.Generator().manual_seed(4)
+    L = torch.randint(1, T + 1, (B,), generator=g); L[0] = T; L[1] = 1
+    seq = torch.randn(B, T, 384, generator=g)
+    seq = seq * (torch.arange(T)[None, :, None] < L[:, None, None])
+    y = torch.randint(0, 10, (B,), generator=g)
+    names = ["pool.score.weight", "pool.score.bias", "head.0.weight", "head.0.bias", "head.1.weight", "head.1.bias",
+             "head.4.weight", "head.4.bias"]
+    w = [p[n].to(dev).contiguous() for n in names]
+    out = ops.head_fwd(seq.to(dev), L.to(dev), w, 10, want_probs=True, k_top=3, y=y.to(dev), label_smoothing=0.05)
+    pooled = ref_model.attn_pool(p, seq, L)
+    logits = ref_model.head(p, pooled)
+    assert rel_err(out["logits"], logits) < 1e-5
+    assert torch.equal(out["logits"].argmax(1).cpu(), logits.argmax(1))
+    ids, probs = ref_model.topk(logits)
+    assert torch.equal(out["topk_ids"].cpu().long(), ids)
+    assert rel_err(out["topk_probs"], probs) < 1e-5
+    assert rel_err(out["probs"], torch.softmax(logits, -1)) < 1e-5
+    per = torch.nn.functional.cross_entropy(logits, y, label_smoothing=0.05, reduction="none")
+    assert rel_err(out["loss"], per) < 1e-5
+
+
+# ------------------------------------------------------------------ whole model
+@pytest.mark.parametrize("name", ["model_roi.npz", "model_points.npz", "model_roi_hot.npz"])
+def test_logits_vs_reference_golden(golden_dir, name):
+    dev = _cuda()
+    g = np.load(os.path.join(golden_dir, name))
+    use_roi = bool(g["use_roi"])
+    p = ref_model.synth_params(int(g["param_seed"]), use_roi=use_roi, scale=float(g["param_scale"]))
+    X, L = torch.from_numpy(g["X"]).to(dev), torch.from_numpy(g["lengths"]).to(dev)
+    R = torch.from_numpy(g["R"]).to(dev) if use_roi else None
+    for sem, std in (("train", True), ("live", False)):
+        m = _model_from(p, use_roi, dev, standardize=std)
+        with torch.no_grad():
+            logits = m(X, L, R)
+        ref = torch.from_numpy(g[f"logits_{sem}_semantics"])
+        e = rel_err(logits, ref)
+        assert e < 1e-4, (sem, e)
+        assert torch.equal(logits.argmax(1).cpu(), ref.argmax(1))
+    m = _model_from(p, use_roi, dev, standardize=False)
+    ids, probs, _ = m.predict_topk(X[:1], L[:1], None if R is None else R[:1], k=3)
+    assert ids[0].cpu().tolist() == g["top3_ids_clip0"].tolist()
+    np.testing.assert_allclose(probs[0].cpu().numpy(), g["top3_probs_clip0"], atol=1e-5)
+
+
+@pytest.mark.parametrize("use_roi,B,T,mode", [(True, 130, 90, "uniform"), (False, 96, 256, "uniform"), (True, 64, 90, "full")])
+def test_logits_vs_oracle_seeded(use_roi, B, T, mode):
+    dev = _cuda()
+    from silent_speech_b200 import synth
+    torch.set_num_threads(os.cpu_count() or 1)
+    p = ref_model.synth_params(7, use_roi=use_roi)
+    d = synth.clip_batch(B, T, mode=mode, seed=9, use_roi=use_roi)
+    X, L = torch.from_numpy(d["X"]), torch.from_numpy(d["lengths"])
+    R = torch.from_numpy(d["R"]) if use_roi else None
+    with torch.no_grad():
+        ref = ref_model.forward(p, X, L, R, want_intermediates=True)
+    m = _model_from(p, use_roi, dev)
+    with torch.no_grad():
+        logits = m(X.to(dev), L.to(dev), None if R is None else R.to(dev))
+    e = rel_err(logits, ref["logits"])
+    assert e < 1e-4, e
+    assert torch.equal(logits.argmax(1).cpu(), ref["logits"].argmax(1))
