@@ -1,0 +1,304 @@
+#!/usr/bin/env python
+"""Benchmark of the Silent-Speech clip-classification hot path on B200 (contract in DESIGN.md).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload infer|train]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A step = one pass of the hot path over one batch of synthetic clips of the reference's shape
+(T=90 frames, 180 point features, 48x96 u8 mouth ROI; train_model_official.py:34,38).  Workload at
+N=1: BASELINE.json configs[1] -- batched inference of the points+ROI model, 4096 clips per GPU,
+weak scaling (clips are independent: each rank gets its own 4096, no data-path collective).
+One JSON line is printed by rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+T_FRAMES, X_DIM, NUM_CLASSES = 90, 180, 10
+CNN_FLOP_PER_FRAME = 5_309_952
+GRU_FLOP_PER_FRAME = 2_257_920
+FWD_FLOP_PER_FRAME = CNN_FLOP_PER_FRAME + GRU_FLOP_PER_FRAME
+
+
+def env_int(name, default):
+    return int(os.environ.get(name, default))
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return {"hbm": d["hbm_gbs"], "tensor_burst": d["bf16_tflops"], "tensor_sustained": d["bf16_tflops_sustained"],
+                "src": "measured"}
+    return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor_sustained": 1400.0, "src": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.15)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def make_batch(B, T, mode, use_roi=True, unique=64, seed=42):
+    """Host batch in the collate_fn layout; `unique` distinct clips tiled to B (values do not affect timing)."""
+    from silent_speech_b200 import synth
+    u = min(unique, B)
+    d = synth.clip_batch(u, T, mode=mode, seed=seed, use_roi=use_roi, x_dim=X_DIM, num_classes=NUM_CLASSES)
+    reps = (B + u - 1) // u
+    out = {}
+    for k, v in d.items():
+        out[k] = None if v is None else np.concatenate([v] * reps, axis=0)[:B]
+    return out
+
+
+def cpu_reference_rate(workload, threads, budget_s=12.0, B=64):
+    """The reference's CPU path (oracle port = same ATen call sites) on a bounded sample."""
+    from oracle import ref_model
+    torch.set_num_threads(threads)
+    p = ref_model.synth_params(42)
+    d = make_batch(B, T_FRAMES, "full", unique=B)
+    X, L, R, y = (torch.from_numpy(d["X"]), torch.from_numpy(d["lengths"]), torch.from_numpy(d["R"]),
+                  torch.from_numpy(d["y"]))
+    times = []
+    if workload == "train":
+        st = ref_model.AdamState(p)
+        fn = lambda: st.step(X, L, R, y, training=True)
+    else:
+        def fn():
+            with torch.no_grad():
+                ref_model.forward(p, X, L, R)
+    fn()                                  # warm-up
+    t_end = time.perf_counter() + budget_s
+    while len(times) < 3 or (time.perf_counter() < t_end and len(times) < 10):
+        t0 = time.perf_counter(); fn(); times.append(time.perf_counter() - t0)
+    return B / min(times), f"B={B} clips x T={T_FRAMES}, full lengths, best of {len(times)}"
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    from oracle import ref_model
+    torch.set_num_threads(threads)
+    B = 64
+    p = ref_model.synth_params(42)
+    d = make_batch(B, T_FRAMES, "full", unique=B)
+    X, L, R, y = (torch.from_numpy(d["X"]), torch.from_numpy(d["lengths"]), torch.from_numpy(d["R"]),
+                  torch.from_numpy(d["y"]))
+    if args.workload == "train":
+        st = ref_model.AdamState(p)
+        step = lambda: st.step(X, L, R, y, training=True)
+    else:
+        def step():
+            with torch.no_grad():
+                ref_model.forward(p, X, L, R)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    val = B * args.steps / dt
+    sample = f"each step = {B} clips x T={T_FRAMES} (bounded sample of the 4096-clip batch), {threads} threads"
+    line = {"impl": "reference", "metric": metric_name(args.workload), "value": val, "unit": "clips/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args.workload, B),
+            "cpu_baseline": {"value": val, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def metric_name(workload):
+    return "train_step_samples_per_sec" if workload == "train" else "inference_clips_per_sec"
+
+
+def workload_config(workload, B):
+    if workload == "train":
+        return {"workload": "configs[2]: full train step (fwd+bwd+clip+Adam) points+ROI model", "clips_per_gpu": B,
+                "frames": T_FRAMES, "lengths": "all=T", "l2": "inputs larger than L2"}
+    return {"workload": "configs[1]: batched inference word_model_points_roi, fp32", "clips_per_gpu": B,
+            "frames": T_FRAMES, "lengths": "all=T", "l2": "inputs (1.96 GB/step) larger than L2"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="infer", choices=["infer", "train"])
+    ap.add_argument("--batch", type=int, default=0, help="clips per GPU (default 4096 infer / 128 train)")
+    ap.add_argument("--lengths", default="full", choices=["full", "uniform"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch.distributed as dist
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    from silent_speech_b200 import BiGRUClassifier
+    from oracle import ref_model
+
+    B = args.batch or (4096 if args.workload == "infer" else 128)
+    peaks = load_peaks()
+    p = ref_model.synth_params(42)         # seed-42 weights of the reference's init magnitudes (no ckpt is shipped)
+    model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=True)
+    model.load_state_dict(p)
+    model = model.to(dev)
+    d = make_batch(B, T_FRAMES, args.lengths, seed=42 + rank)
+    hX = torch.from_numpy(d["X"]).pin_memory(); hL = torch.from_numpy(d["lengths"]).pin_memory()
+    hR = torch.from_numpy(d["R"]).pin_memory(); hy = torch.from_numpy(d["y"]).pin_memory()
+    X, L, R, y = hX.to(dev), hL.to(dev), hR.to(dev), hy.to(dev)
+    frames = int(d["lengths"].sum())
+
+    if args.workload == "train":
+        from silent_speech_b200.train import Trainer
+        trainer = Trainer(model, lr=3e-4, world_size=world)
+        step = lambda: trainer.step(X, L, R, y)
+        launches_per_step = trainer.launches_per_step
+    else:
+        model.eval()
+
+        def step():
+            with torch.no_grad():
+                return model(X, L, R)
+        launches_per_step = None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    from silent_speech_b200 import _lib as ssb_lib
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    c0 = ssb_lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+        barrier()
+    launches = ssb_lib.launch_count() - c0
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = B * world * args.steps / (ms / 1e3)
+
+    # ---- end to end through the public API with host buffers (H2D + D2H inside the timed region)
+    def e2e_step():
+        Xd, Ld, Rd = hX.to(dev, non_blocking=True), hL.to(dev, non_blocking=True), hR.to(dev, non_blocking=True)
+        if args.workload == "train":
+            return trainer.step(Xd, Ld, Rd, hy.to(dev, non_blocking=True)).cpu()
+        with torch.no_grad():
+            return model(Xd, Ld, Rd).cpu()
+    e2e_step()
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_e2e = max(2, min(args.steps, 5))
+    e2.record()
+    for _ in range(n_e2e):
+        res = e2e_step()
+    e3.record()
+    barrier()
+    t = torch.tensor([e2.elapsed_time(e3)], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_val = B * world * n_e2e / (float(t.item()) / 1e3)
+    h2d = hX.numel() * 4 + hL.numel() * 8 + hR.numel() + (hy.numel() * 8 if args.workload == "train" else 0)
+    d2h = res.numel() * res.element_size()
+
+    # ---- dominant kernel (fused ROI CNN) timed alone for the roofline line
+    from silent_speech_b200 import ops
+    w = model.roi_cnn.tensors()
+    for _ in range(2):
+        ops.roi_cnn_fwd(R, L, w)
+    torch.cuda.synchronize()
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0.record()
+    for _ in range(5):
+        ops.roi_cnn_fwd(R, L, w)
+    k1.record()
+    torch.cuda.synchronize()
+    cnn_ms = k0.elapsed_time(k1) / 5
+    achieved = CNN_FLOP_PER_FRAME * frames / (cnn_ms / 1e3) / 1e12
+    roofline = {"kernel": "roi_cnn_fwd_kernel", "bound": "tensor", "achieved": achieved, "peak": peaks["tensor_burst"],
+                "unit": "TFLOP/s", "frac": achieved / peaks["tensor_burst"], "traffic": None,
+                "peak_src": f"{peaks['src']} bf16 burst", "ms_per_launch": cnn_ms,
+                "note": "fp32 CUDA-core build of K2; step-level: %.1f TFLOP/s over %.0f MFLOP/clip" % (
+                    FWD_FLOP_PER_FRAME * frames * world * args.steps / (ms / 1e3) / 1e12, FWD_FLOP_PER_FRAME * T_FRAMES / 1e6)}
+
+    if rank == 0:
+        cpu = None
+        if not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            v, sample = cpu_reference_rate(args.workload, threads)
+            cpu = {"value": v, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample}
+        line = {"metric": metric_name(args.workload), "value": value, "unit": "clips/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": workload_config(args.workload, B) | {"lengths": "all=T" if args.lengths == "full" else "uniform[6,T]"},
+                "clocks": clk.summary(),
+                "e2e": {"value": e2e_val, "unit": "clips/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+                "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -93,6 +93,35 @@ int ssb_head_bwd_pool(const float* dln, const float* xhat, const float* rstd, co
 /* out[j] += sum_i A[i*lda + j]  (bias gradients). */
 int ssb_colsum(const float* A, int64_t lda, int64_t M, int64_t N, float* out, void* stream);
 
+/* K2-bwd: weight gradients of the fused ROI CNN (backward of train_model_official.py:209-229 as run by
+ * loss.backward(), train:437).  The forward is recomputed per frame in shared memory.  grads_host =
+ * 8 device pointers in the order of weights_host; they are accumulated into (+=). */
+int ssb_roi_cnn_bwd(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
+                    int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
+                    const float* d_out, int64_t d_out_stride, float* const* grads_host, void* stream);
+
+/* K3-bwd: back-propagation through time of one bidirectional GRU layer (ATen's GRU backward under
+ * train:437).  dout/out [B,T,384]; gates from ssb_gru_layer_fwd; whhT_* = W_hh^T [192,576].
+ * Writes dgi [B,T,1152] (gradient at the input projections), dghn [B,T,2,192] (n-gate part of the
+ * hidden-projection gradient) and hprev [B,T,2,192]; dW_ih, dW_hh, biases and d(input) follow as GEMMs. */
+int ssb_gru_layer_bwd(const float* dout, const float* out, const float* gates,
+                      const float* whhT_f, const float* whhT_r, const int64_t* lengths,
+                      int64_t B, int64_t T, int32_t hidden,
+                      float* dgi, float* dghn, float* hprev, void* stream);
+
+/* out[cols][rows] = in[rows][cols]^T. */
+int ssb_transpose(const float* in, float* out, int64_t rows, int64_t cols, void* stream);
+
+/* K5: joint-norm clip + Adam over a flat bucket (train_model_official.py:403, 438-439).
+ * ssb_grad_sqnorm adds sum(g^2) to *sqnorm (double, zeroed by the caller once per step). */
+int ssb_grad_sqnorm(const float* g, int64_t n, double* sqnorm, void* stream);
+int ssb_clip_adam_step(float* p, float* g, float* m, float* v, int64_t n, const double* sqnorm,
+                       float max_norm, float lr, float beta1, float beta2, float eps, int64_t step,
+                       int32_t write_back_grad, float* norm_out, void* stream);
+
+/* Counter-based dropout: y = x * keep(seed, i) / (1-p)  (nn.GRU inter-layer dropout, train:266). */
+int ssb_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

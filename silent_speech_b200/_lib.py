@@ -27,7 +27,17 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
+_launches = 0
+
+
+def launch_count() -> int:
+    """Number of C-ABI compute calls made so far; every one of them enqueues exactly one kernel."""
+    return _launches
+
+
 def check(code: int) -> None:
+    global _launches
+    _launches += 1
     if code != 0:
         raise SsbError(f"libssb200 error {code}: {lib().ssb_last_error().decode()}")
 

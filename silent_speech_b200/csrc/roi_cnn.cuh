@@ -26,7 +26,10 @@ constexpr int NPIX = H0 * W0;
 constexpr int IN_LD = 100, IN_ROWS = H0 + 2;         // [50][100]
 constexpr int A1_LD = 52, A1_ROWS = H1 + 2;          // [8][26][52]
 constexpr int A2_LD = 28, A2_ROWS = H2 + 2;          // [16][14][28]
-constexpr int A1_PLANE = A1_ROWS * A1_LD, A2_PLANE = A2_ROWS * A2_LD;
+// plane strides: a1 = 1352+4 (== 12 mod 32), a2 = 392+26 (== 2 mod 32) so that threads that differ only
+// in the input channel hit different banks in the weight-gradient passes of the backward kernel
+constexpr int A1_PLANE = A1_ROWS * A1_LD + 4, A2_PLANE = A2_ROWS * A2_LD + 26;
+constexpr int A3_LD = A2_LD, A3_PLANE = A2_ROWS * A2_LD;      // conv3 output kept padded [24][14][28] when saved
 
 struct Weights {            // device pointers in the reference's state-dict layout
   const float *w1, *b1;     // roi_cnn.net.0  [8,1,3,3],  [8]
@@ -205,7 +208,7 @@ __device__ __forceinline__ void conv2_pool(const float* __restrict__ s_a1, float
 
 // ---- stage 3: conv(16->24)+ReLU, mean over the 288 positions, Linear(24->32).
 // One thread = a vertical pair of positions x 12 channels.  s_part: >= 18*12 floats,
-// s_mean: >= 24 floats.  kSave keeps the ReLU output a3 [24][12][24] for the backward pass.
+// s_mean: >= 24 floats.  kSave keeps the ReLU output a3 (padded [24][14][28]) for the backward pass.
 template <bool kSave>
 __device__ __forceinline__ void conv3_mean(const float* __restrict__ s_a2, const SmemWeights& w,
                                            float* __restrict__ s_part, float* __restrict__ s_mean,
@@ -241,7 +244,7 @@ __device__ __forceinline__ void conv3_mean(const float* __restrict__ s_a2, const
   for (int co = 0; co < 12; ++co) {
     const int c = half * 12 + co;
     const float r0 = fmaxf(acc[co][0] + w.b3[c], 0.f), r1 = fmaxf(acc[co][1] + w.b3[c], 0.f);
-    if (kSave) { a3[c * (H2 * W2) + y * W2 + x] = r0; a3[c * (H2 * W2) + (y + 1) * W2 + x] = r1; }
+    if (kSave) { a3[c * A3_PLANE + (y + 1) * A3_LD + x + 1] = r0; a3[c * A3_PLANE + (y + 2) * A3_LD + x + 1] = r1; }
     float v = r0 + r1;
 #pragma unroll
     for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);     // 16-lane segments

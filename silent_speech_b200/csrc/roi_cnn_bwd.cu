@@ -1,0 +1,313 @@
+// K2-bwd (fp32 build) -- weight gradients of the fused mouth-ROI CNN.
+//
+// What loss.backward() (train_model_official.py:437) does through TinyROICNN
+// (train_model_official.py:209-229) and the standardise of 289-291, per frame and entirely
+// in shared memory: the forward pass is recomputed (keeping the two max-pool argmax maps and
+// the conv3 ReLU output), then
+//   B0  Linear(24->32) and the mean:      dWfc, dbfc, g3 = relu'(a3) * dmean/288, db3
+//   B1  conv3 weight gradient             dW3[co,ci,tap] += sum_pos g3[co,pos] a2[ci,pos+tap]
+//   B2  conv3 data gradient (gather)      da2, masked by relu'(a2)
+//   B3  conv2 weight gradient through the pool argmax     dW2, db2
+//   B4  conv2 data gradient (gather through the argmax)   da1, masked by relu'(a1)
+//   B5  conv1 weight gradient through the pool argmax     dW1, db1
+// The ROI pixels are inputs, not parameters, so nothing flows past conv1.  Every thread keeps
+// its slice of the weight gradients in registers across all frames its CTA visits and adds
+// them to the global gradient once, at the end.
+#include "roi_cnn.cuh"
+
+namespace ssb {
+namespace cnn {
+
+constexpr int A3_COL0 = 2;     // interior of the saved conv3 plane starts at column 2 (float2-aligned pairs)
+
+struct BwdSmem {
+  SmemWeights w;
+  float in[IN_ROWS * IN_LD];
+  float a1[C1 * A1_PLANE];
+  float a2[C2 * A2_PLANE];
+  float g3[C3 * A3_PLANE];
+  float da2m[C2 * H2 * W2];
+  float da1m[C1 * H1 * W1];
+  uint8_t idx1[C1 * H1 * W1];
+  uint8_t idx2[C2 * H2 * W2];
+  float part[18 * 12];
+  float mean[C3];
+  float red[16];
+  float dE[E];
+  float dmean[C3];
+  int cnt[C3];
+};
+
+// conv3 forward that keeps the ReLU output in the padded, column-shifted plane used by B1/B2
+__device__ __forceinline__ void conv3_save(const float* __restrict__ s_a2, const SmemWeights& w,
+                                           float* __restrict__ s_part, float* __restrict__ s_mean,
+                                           float* __restrict__ g3, int tid) {
+  // a3 is written through conv3_mean<true> at [c][y+1][x+1]; shift the base by one column
+  conv3_mean<true>(s_a2, w, s_part, s_mean, g3 + (A3_COL0 - 1), tid);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ lengths, int B, int T,
+                   Weights gw, int standardize, const float* __restrict__ d_out, int64_t d_out_stride,
+                   float* __restrict__ gW1, float* __restrict__ gb1, float* __restrict__ gW2, float* __restrict__ gb2,
+                   float* __restrict__ gW3, float* __restrict__ gb3, float* __restrict__ gWfc, float* __restrict__ gbfc) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BwdSmem& s = *reinterpret_cast<BwdSmem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31;
+  load_weights(s.w, gw, tid);
+  for (int i = tid; i < IN_ROWS * IN_LD; i += kThreads) s.in[i] = 0.f;
+  for (int i = tid; i < C1 * A1_PLANE; i += kThreads) s.a1[i] = 0.f;
+  for (int i = tid; i < C2 * A2_PLANE; i += kThreads) s.a2[i] = 0.f;
+  for (int i = tid; i < C3 * A3_PLANE; i += kThreads) s.g3[i] = 0.f;
+  __syncthreads();
+
+  // ---- per-thread slices of the weight gradients
+  const int b1_third = tid / 96, b1_cog = (tid % 96) / 16, b1_ci = tid % 16;          // dW3
+  float acc3[4][9];
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+#pragma unroll
+    for (int t = 0; t < 9; ++t) acc3[k][t] = 0.f;
+  const int b3_half = tid >> 7, b3_co = (tid & 127) >> 3, b3_ci = tid & 7;            // dW2 (tid < 256)
+  float acc2[9], accb2 = 0.f;
+#pragma unroll
+  for (int t = 0; t < 9; ++t) acc2[t] = 0.f;
+  const int b5_q = tid / 72, b5_co = (tid % 72) / 9, b5_tap = tid % 9;                // dW1
+  float acc1 = 0.f, accb1 = 0.f, accb3 = 0.f, accfc[3] = {0.f, 0.f, 0.f};
+
+  const int64_t frames = (int64_t)B * T;
+  for (int64_t f = blockIdx.x; f < frames; f += gridDim.x) {
+    const int b = (int)(f / T), t = (int)(f % T);
+    if (lengths && t >= (int)lengths[b]) continue;
+
+    // ================= forward recompute
+    load_frame(R + f * NPIX, s.in, s.red, tid, standardize != 0);
+    __syncthreads();
+    conv1_pool<true>(s.in, s.a1, s.w, s.idx1, tid);
+    __syncthreads();
+    conv2_pool<true>(s.a1, s.a2, s.w, s.idx2, tid);
+    __syncthreads();
+    conv3_save(s.a2, s.w, s.part, s.mean, s.g3, tid);          // ends with a barrier; s.mean valid
+
+    // ================= B0: fc, mean, relu mask of conv3
+    if (tid < E) s.dE[tid] = d_out[f * d_out_stride + tid];
+    __syncthreads();
+    if (tid < C3) {
+      float a = 0.f;
+#pragma unroll
+      for (int e = 0; e < E; ++e) a = fmaf(s.w.wfc[e][tid], s.dE[e], a);
+      s.dmean[tid] = a / (float)(H2 * W2);
+      s.cnt[tid] = 0;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int i = tid + k * kThreads;
+      if (i < E * C3) accfc[k] = fmaf(s.dE[i / C3], s.mean[i % C3], accfc[k]);
+      else if (i < E * C3 + E) accfc[k] += s.dE[i - E * C3];
+    }
+    __syncthreads();
+    {
+      const int y = tid / W2, x = tid % W2;
+      float* g = s.g3 + (y + 1) * A3_LD + x + A3_COL0;
+#pragma unroll 4
+      for (int c = 0; c < C3; ++c) {
+        const bool on = g[c * A3_PLANE] > 0.f;
+        g[c * A3_PLANE] = on ? s.dmean[c] : 0.f;
+        const unsigned bal = __ballot_sync(0xffffffffu, on);
+        if (lane == 0) atomicAdd(&s.cnt[c], __popc(bal));
+      }
+    }
+    __syncthreads();
+    if (tid < C3) accb3 = fmaf(s.dmean[tid], (float)s.cnt[tid], accb3);
+
+    // ================= B1: dW3
+    {
+      const float* gbase = s.g3 + (b1_cog * 4) * A3_PLANE + A3_COL0;
+      const float* abase = s.a2 + b1_ci * A2_PLANE;
+#pragma unroll 1
+      for (int yy = 0; yy < 4; ++yy) {
+        const int y = b1_third * 4 + yy;
+#pragma unroll 2
+        for (int xp = 0; xp < W2 / 2; ++xp) {
+          const int x = 2 * xp;
+          float2 g[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) g[k] = *reinterpret_cast<const float2*>(gbase + k * A3_PLANE + (y + 1) * A3_LD + x);
+          float P[3][4];
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+            const float2 p0 = *reinterpret_cast<const float2*>(abase + (y + r) * A2_LD + x);
+            const float2 p1 = *reinterpret_cast<const float2*>(abase + (y + r) * A2_LD + x + 2);
+            P[r][0] = p0.x; P[r][1] = p0.y; P[r][2] = p1.x; P[r][3] = p1.y;
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+              for (int dx = 0; dx < 3; ++dx)
+                acc3[k][dy * 3 + dx] = fmaf(g[k].y, P[dy][dx + 1], fmaf(g[k].x, P[dy][dx], acc3[k][dy * 3 + dx]));
+        }
+      }
+    }
+
+    // ================= B2: da2 = conv3^T(g3), masked by relu'(a2)
+    {
+      const int q = tid % 144, half = tid / 144;
+      const int y = 2 * (q / W2), x = q % W2;
+      float acc[8][2];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) acc[c][0] = acc[c][1] = 0.f;
+#pragma unroll 1
+      for (int tap = 0; tap < 9; ++tap) {
+        const int dy = tap / 3, dx = tap % 3;
+        // position (y,x) receives from conv3 output (y-dy+1, x-dx+1): padded row +1, col +A3_COL0
+        const float* gp = s.g3 + (y - dy + 2) * A3_LD + (x - dx + 1 + A3_COL0);
+        float g0[C3], g1[C3];
+#pragma unroll
+        for (int co = 0; co < C3; ++co) { g0[co] = gp[co * A3_PLANE]; g1[co] = gp[co * A3_PLANE + A3_LD]; }
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const float4* wp = reinterpret_cast<const float4*>(&s.w.w3[half * 8 + c][tap][0]);
+          float a0 = acc[c][0], a1v = acc[c][1];
+#pragma unroll
+          for (int v = 0; v < C3 / 4; ++v) {
+            const float4 wv = wp[v];
+            a0 = fmaf(wv.x, g0[4 * v], a0); a0 = fmaf(wv.y, g0[4 * v + 1], a0);
+            a0 = fmaf(wv.z, g0[4 * v + 2], a0); a0 = fmaf(wv.w, g0[4 * v + 3], a0);
+            a1v = fmaf(wv.x, g1[4 * v], a1v); a1v = fmaf(wv.y, g1[4 * v + 1], a1v);
+            a1v = fmaf(wv.z, g1[4 * v + 2], a1v); a1v = fmaf(wv.w, g1[4 * v + 3], a1v);
+          }
+          acc[c][0] = a0; acc[c][1] = a1v;
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const int ci = half * 8 + c;
+        const float v0 = s.a2[ci * A2_PLANE + (y + 1) * A2_LD + x + 1], v1 = s.a2[ci * A2_PLANE + (y + 2) * A2_LD + x + 1];
+        s.da2m[ci * (H2 * W2) + y * W2 + x] = v0 > 0.f ? acc[c][0] : 0.f;
+        s.da2m[ci * (H2 * W2) + (y + 1) * W2 + x] = v1 > 0.f ? acc[c][1] : 0.f;
+      }
+    }
+    __syncthreads();
+
+    // ================= B3: dW2, db2 (gradient sits at the pooled cell's argmax position)
+    if (tid < 256) {
+      const float* dptr = s.da2m + b3_co * (H2 * W2);
+      const uint8_t* iptr = s.idx2 + b3_co * (H2 * W2);
+      const float* abase = s.a1 + b3_ci * A1_PLANE;
+#pragma unroll 2
+      for (int cell = b3_half * 144; cell < b3_half * 144 + 144; ++cell) {
+        const float d = dptr[cell];
+        const int id = iptr[cell];
+        const int py = cell / W2, px = cell % W2;
+        const float* p = abase + (2 * py + (id >> 1)) * A1_LD + 2 * px + (id & 1);
+#pragma unroll
+        for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+          for (int dx = 0; dx < 3; ++dx) acc2[dy * 3 + dx] = fmaf(d, p[dy * A1_LD + dx], acc2[dy * 3 + dx]);
+        accb2 += d;
+      }
+    }
+
+    // ================= B4: da1 = conv2^T(dc2) gathered through the argmax, masked by relu'(a1)
+#pragma unroll 1
+    for (int k = 0; k < 4; ++k) {
+      const int pos = tid + k * kThreads;
+      const int y = pos / W1, x = pos % W1;
+      float acc[C1];
+#pragma unroll
+      for (int c = 0; c < C1; ++c) acc[c] = 0.f;
+#pragma unroll 1
+      for (int tap = 0; tap < 9; ++tap) {
+        const int dy = tap / 3, dx = tap % 3;
+        const int yy = y + 1 - dy, xx = x + 1 - dx;            // conv2 output position feeding (y,x) through this tap
+        if (yy < 0 || yy >= H1 || xx < 0 || xx >= W1) continue;
+        const int cell = (yy >> 1) * W2 + (xx >> 1), sub = ((yy & 1) << 1) | (xx & 1);
+        float dv[C2];
+#pragma unroll
+        for (int co = 0; co < C2; ++co)
+          dv[co] = s.idx2[co * (H2 * W2) + cell] == sub ? s.da2m[co * (H2 * W2) + cell] : 0.f;
+#pragma unroll
+        for (int c = 0; c < C1; ++c) {
+          const float4* wp = reinterpret_cast<const float4*>(&s.w.w2[c][tap][0]);
+          float a = acc[c];
+#pragma unroll
+          for (int v = 0; v < C2 / 4; ++v) {
+            const float4 wv = wp[v];
+            a = fmaf(wv.x, dv[4 * v], a); a = fmaf(wv.y, dv[4 * v + 1], a);
+            a = fmaf(wv.z, dv[4 * v + 2], a); a = fmaf(wv.w, dv[4 * v + 3], a);
+          }
+          acc[c] = a;
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < C1; ++c)
+        s.da1m[c * (H1 * W1) + pos] = s.a1[c * A1_PLANE + (y + 1) * A1_LD + x + 1] > 0.f ? acc[c] : 0.f;
+    }
+    __syncthreads();
+
+    // ================= B5: dW1, db1
+    {
+      const float* dptr = s.da1m + b5_co * (H1 * W1);
+      const uint8_t* iptr = s.idx1 + b5_co * (H1 * W1);
+      const int dy = b5_tap / 3, dx = b5_tap % 3;
+#pragma unroll 4
+      for (int cell = b5_q * 288; cell < b5_q * 288 + 288; ++cell) {
+        const float d = dptr[cell];
+        const int id = iptr[cell];
+        const int py = cell / W1, px = cell % W1;
+        acc1 = fmaf(d, s.in[(2 * py + (id >> 1) + dy) * IN_LD + 2 * px + (id & 1) + dx], acc1);
+        accb1 += d;
+      }
+    }
+    __syncthreads();      // all reads of this frame's planes are done before the next frame overwrites them
+  }
+
+  // ---- one global accumulation per CTA
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+#pragma unroll
+    for (int t = 0; t < 9; ++t) atomicAdd(gW3 + ((b1_cog * 4 + k) * C2 + b1_ci) * 9 + t, acc3[k][t]);
+  if (tid < 256) {
+#pragma unroll
+    for (int t = 0; t < 9; ++t) atomicAdd(gW2 + (b3_co * C1 + b3_ci) * 9 + t, acc2[t]);
+    if (b3_ci == 0) atomicAdd(gb2 + b3_co, accb2);
+  }
+  atomicAdd(gW1 + b5_co * 9 + b5_tap, acc1);
+  if (b5_tap == 0) atomicAdd(gb1 + b5_co, accb1);
+  if (tid < C3) atomicAdd(gb3 + tid, accb3);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int i = tid + k * kThreads;
+    if (i < E * C3) atomicAdd(gWfc + i, accfc[k]);
+    else if (i < E * C3 + E) atomicAdd(gbfc + (i - E * C3), accfc[k]);
+  }
+}
+
+}  // namespace cnn
+}  // namespace ssb
+
+// Accumulates (+=) the 8 parameter gradients {net.0.w,b, net.3.w,b, net.6.w,b, fc.w,b} of the fused
+// ROI CNN given d_out[(b*T+t)*d_out_stride + 0..31] = dL/d(embedding).  R is re-read and the forward
+// recomputed in shared memory; nothing is saved by the forward call.
+extern "C" int ssb_roi_cnn_bwd(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
+                               int32_t roi_h, int32_t roi_w, const float* const* weights, int32_t standardize,
+                               const float* d_out, int64_t d_out_stride, float* const* grads, void* stream) {
+  using namespace ssb;
+  using namespace ssb::cnn;
+  SSB_REQUIRE(R && weights && d_out && grads, "null pointer");
+  SSB_REQUIRE(roi_h == H0 && roi_w == W0, "ROI must be 48x96");
+  SSB_REQUIRE(d_out_stride >= E, "d_out_stride < 32");
+  for (int i = 0; i < 8; ++i) SSB_REQUIRE(weights[i] && grads[i], "null weight/grad pointer");
+  if (B * T == 0) return SSB_OK;
+  Weights gw{weights[0], weights[1], weights[2], weights[3], weights[4], weights[5], weights[6], weights[7]};
+  SSB_CUDA(cudaFuncSetAttribute(roi_cnn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));
+  const int64_t frames = B * T;
+  const int grid = (int)(frames < kSMs ? frames : kSMs);
+  roi_cnn_bwd_kernel<<<grid, kThreads, sizeof(BwdSmem), (cudaStream_t)stream>>>(
+      R, lengths, (int)B, (int)T, gw, standardize, d_out, d_out_stride,
+      grads[0], grads[1], grads[2], grads[3], grads[4], grads[5], grads[6], grads[7]);
+  SSB_LAUNCH_CHECK();
+  return SSB_OK;
+}

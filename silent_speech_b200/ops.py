@@ -31,6 +31,7 @@ def device_info():
     sm, major, minor = i32(), i32(), i32()
     import ctypes
     check(_lib.lib().ssb_device_info(ctypes.byref(sm), ctypes.byref(major), ctypes.byref(minor)))
+    _lib._launches -= 1          # a probe, not a kernel launch
     return sm.value, major.value, minor.value
 
 
@@ -168,3 +169,49 @@ def colsum(A2d: torch.Tensor, out: torch.Tensor):
     M, N = A2d.shape
     check(_lib.lib().ssb_colsum(ptr(A2d), i64(A2d.stride(0)), i64(M), i64(N), ptr(out), stream_ptr()))
     return out
+
+
+# ----------------------------------------------------------------------------- backward / optimiser
+def roi_cnn_bwd(R, lengths, weights, standardize, d_out: torch.Tensor, d_col: int, grads):
+    """Accumulates the 8 ROI-CNN parameter gradients from d_out[..., d_col:d_col+32]."""
+    import ctypes
+    B, T, Hh, Ww = R.shape
+    base = d_out.data_ptr() + 4 * d_col
+    check(_lib.lib().ssb_roi_cnn_bwd(ptr(R), ptr(lengths), i64(B), i64(T), i32(Hh), i32(Ww), ptr_array(weights),
+                                     i32(1 if standardize else 0), ctypes.c_void_p(base), i64(d_out.shape[-1]),
+                                     ptr_array(grads), stream_ptr()))
+
+
+def transpose(x2d: torch.Tensor) -> torch.Tensor:
+    r, c = x2d.shape
+    out = torch.empty(c, r, device=x2d.device, dtype=torch.float32)
+    check(_lib.lib().ssb_transpose(ptr(x2d), ptr(out), i64(r), i64(c), stream_ptr()))
+    return out
+
+
+def gru_layer_bwd(dout, out, gates, whhT_f, whhT_r, lengths):
+    B, T, _ = out.shape
+    dev = out.device
+    dgi = torch.empty(B, T, 2 * 3 * HIDDEN, device=dev, dtype=torch.float32)
+    dghn = torch.empty(B, T, 2, HIDDEN, device=dev, dtype=torch.float32)
+    hprev = torch.empty(B, T, 2, HIDDEN, device=dev, dtype=torch.float32)
+    check(_lib.lib().ssb_gru_layer_bwd(ptr(dout), ptr(out), ptr(gates), ptr(whhT_f), ptr(whhT_r), ptr(lengths),
+                                       i64(B), i64(T), i32(HIDDEN), ptr(dgi), ptr(dghn), ptr(hprev), stream_ptr()))
+    return dgi, dghn, hprev
+
+
+def dropout(x: torch.Tensor, p: float, seed: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _need(x, torch.float32, "x")
+    y = torch.empty_like(x) if out is None else out
+    check(_lib.lib().ssb_dropout(ptr(x), ptr(y), i64(x.numel()), f32(p), u64(seed), stream_ptr()))
+    return y
+
+
+def grad_sqnorm(g: torch.Tensor, sqnorm: torch.Tensor):
+    check(_lib.lib().ssb_grad_sqnorm(ptr(g), i64(g.numel()), ptr(sqnorm), stream_ptr()))
+
+
+def clip_adam_step(p, g, m, v, sqnorm, max_norm, lr, beta1, beta2, eps, step, write_back_grad=False, norm_out=None):
+    check(_lib.lib().ssb_clip_adam_step(ptr(p), ptr(g), ptr(m), ptr(v), i64(p.numel()), ptr(sqnorm), f32(max_norm),
+                                        f32(lr), f32(beta1), f32(beta2), f32(eps), i64(step),
+                                        i32(1 if write_back_grad else 0), ptr(norm_out), stream_ptr()))

@@ -1,0 +1,151 @@
+"""GPU parity, backward path and train step: gradients of every parameter, the joint-norm clip
+and the Adam update against the reference's golden values and against the CPU oracle (ATen
+autograd) on seeded inputs.  Dropout is inactive for gradient parity and is
+checked statistically on its own.
+
+Tolerance: |g - g_ref|_inf <= 1e-4 * |g_ref|_inf per tensor (fp32, different summation order)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import ref_model  # noqa: E402
+
+
+def _cuda():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch.device("cuda")
+
+
+def rel_err(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def _model(p, use_roi, dev):
+    from silent_speech_b200 import BiGRUClassifier
+    m = BiGRUClassifier(180, p["head.4.weight"].shape[0], use_roi=use_roi)
+    m.load_state_dict(p)
+    return m.to(dev)
+
+
+def _golden_inputs(g):
+    use_roi = bool(g["use_roi"])
+    p = ref_model.synth_params(int(g["param_seed"]), use_roi=use_roi, scale=float(g["param_scale"]))
+    X, L, y = torch.from_numpy(g["X"]), torch.from_numpy(g["lengths"]), torch.from_numpy(g["y"])
+    R = torch.from_numpy(g["R"]) if use_roi else None
+    return p, use_roi, X, L, R, y
+
+
+@pytest.mark.parametrize("name", ["model_roi.npz", "model_points.npz", "model_roi_hot.npz"])
+def test_autograd_grads_vs_reference_golden(golden_dir, name):
+    """The reference's own loop: logits = model(X, lengths, R); CE(ls=.05); loss.backward()."""
+    dev = _cuda()
+    g = np.load(os.path.join(golden_dir, name))
+    p, use_roi, X, L, R, y = _golden_inputs(g)
+    m = _model(p, use_roi, dev).eval()              # eval: dropout off, backward still defined
+    logits = m(X.to(dev), L.to(dev), None if R is None else R.to(dev))
+    loss = torch.nn.CrossEntropyLoss(label_smoothing=0.05)(logits, y.to(dev))
+    loss.backward()
+    assert abs(loss.item() - float(g["loss"])) < 1e-5
+    worst = {}
+    for n, prm in m.named_parameters():
+        ref = g[f"grad_samp/{n}"]
+        got = prm.grad.reshape(-1)[::97].cpu().numpy()
+        scale = max(np.abs(ref).max(), g[f"grad_stat/{n}"][0] / np.sqrt(prm.numel()))
+        worst[n] = float(np.abs(got - ref).max() / scale)
+        nrm = prm.grad.double().norm().item()
+        assert abs(nrm - g[f"grad_stat/{n}"][0]) <= 1e-4 * g[f"grad_stat/{n}"][0] + 1e-9, n
+    bad = {k: v for k, v in worst.items() if v > 1e-4}
+    assert not bad, bad
+
+
+@pytest.mark.parametrize("use_roi,B,T", [(True, 37, 30), (False, 70, 50)])
+def test_grads_vs_oracle_seeded(use_roi, B, T):
+    dev = _cuda()
+    from silent_speech_b200 import synth
+    torch.set_num_threads(os.cpu_count() or 1)
+    p = ref_model.synth_params(13, use_roi=use_roi)
+    d = synth.clip_batch(B, T, mode="uniform", seed=17, use_roi=use_roi)
+    X, L, y = torch.from_numpy(d["X"]), torch.from_numpy(d["lengths"]), torch.from_numpy(d["y"])
+    L[0] = 1
+    X[0, 1:] = 0
+    R = torch.from_numpy(d["R"]) if use_roi else None
+    loss_ref, logits_ref, grads_ref = ref_model.loss_and_grads(p, X, L, R, y)
+    m = _model(p, use_roi, dev).eval()
+    logits = m(X.to(dev), L.to(dev), None if R is None else R.to(dev))
+    loss = torch.nn.functional.cross_entropy(logits, y.to(dev), label_smoothing=0.05)
+    loss.backward()
+    assert abs(loss.item() - loss_ref.item()) < 1e-5
+    errs = {n: rel_err(prm.grad, grads_ref[n]) for n, prm in m.named_parameters()}
+    bad = {k: v for k, v in errs.items() if v > 1e-4}
+    assert not bad, bad
+
+
+@pytest.mark.parametrize("name", ["model_roi.npz", "model_points.npz"])
+def test_train_step_vs_reference_golden(golden_dir, name):
+    """forward + fused CE + backward + joint clip + Adam, against the reference's post-step weights."""
+    dev = _cuda()
+    from silent_speech_b200.train import Trainer
+    g = np.load(os.path.join(golden_dir, name))
+    p, use_roi, X, L, R, y = _golden_inputs(g)
+    m = _model(p, use_roi, dev).eval()
+    tr = Trainer(m, lr=3e-4, dropout=False)
+    loss = tr.step(X.to(dev), L.to(dev), None if R is None else R.to(dev), y.to(dev))
+    assert abs(loss.mean().item() - float(g["loss"])) < 1e-5
+    assert abs(tr.grad_norm.item() - float(g["grad_norm"])) < 1e-4 * float(g["grad_norm"])
+    sd = m.state_dict()
+    assert list(sd.keys()) == list(p.keys())
+    for n, v in sd.items():
+        ref = g[f"step_samp/{n}"]
+        got = v.reshape(-1)[::97].cpu().numpy()
+        # one Adam step moves every weight by ~lr; agree to 1% of that step
+        assert np.abs(got - ref).max() <= 3e-6, (n, np.abs(got - ref).max())
+
+
+def test_three_train_steps_vs_oracle():
+    dev = _cuda()
+    from silent_speech_b200 import synth
+    from silent_speech_b200.train import Trainer
+    p = ref_model.synth_params(23)
+    d = synth.clip_batch(12, 20, mode="uniform", seed=3)
+    X, L, R, y = (torch.from_numpy(d[k]) for k in ("X", "lengths", "R", "y"))
+    st = ref_model.AdamState(p)
+    m = _model(p, True, dev).eval()
+    tr = Trainer(m, dropout=False)
+    for _ in range(3):
+        l_ref, _, gn_ref = st.step(X, L, R, y)
+        l = tr.step(X.to(dev), L.to(dev), R.to(dev), y.to(dev))
+        assert abs(l.mean().item() - l_ref.item()) < 2e-5
+        assert abs(tr.grad_norm.item() - gn_ref.item()) < 2e-4 * gn_ref.item()
+    ref = st.params()
+    for n, v in m.state_dict().items():
+        assert (v.cpu() - ref[n]).abs().max().item() < 2e-5, n
+
+
+def test_dropout_statistics_and_train_mode():
+    dev = _cuda()
+    from silent_speech_b200 import ops, synth
+    x = torch.ones(1 << 20, device=dev)
+    y = ops.dropout(x, 0.1, 1234)
+    keep = (y != 0).float().mean().item()
+    assert abs(keep - 0.9) < 3e-3
+    assert torch.allclose(y[y != 0], torch.full((1,), 1 / 0.9, device=dev))
+    assert torch.equal(y, ops.dropout(x, 0.1, 1234)) and not torch.equal(y, ops.dropout(x, 0.1, 1235))
+    # train-mode forward/backward runs, is finite, and differs from eval (masks active)
+    p = ref_model.synth_params(5)
+    d = synth.clip_batch(6, 16, mode="uniform", seed=2)
+    m = _model(p, True, dev)
+    args = (torch.from_numpy(d["X"]).to(dev), torch.from_numpy(d["lengths"]).to(dev), torch.from_numpy(d["R"]).to(dev))
+    m.train()
+    lt = m(*args)
+    lt.sum().backward()
+    assert all(torch.isfinite(q.grad).all() for q in m.parameters())
+    m.eval()
+    with torch.no_grad():
+        le = m(*args)
+    assert (lt - le).abs().max().item() > 1e-4
