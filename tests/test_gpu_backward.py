@@ -3,7 +3,12 @@ and the Adam update against the reference's golden values and against the CPU or
 autograd) on seeded inputs.  Dropout is inactive for gradient parity and is
 checked statistically on its own.
 
-Tolerance: |g - g_ref|_inf <= 1e-4 * |g_ref|_inf per tensor (fp32, different summation order)."""
+Tolerance: |g - g_ref|_inf <= 1e-4 * |g_ref|_inf per tensor (fp32, different summation order).
+``pool.score.bias`` is the one exception: its true gradient is exactly 0 (a softmax is invariant to
+a shift of all scores), so the reference's value is pure rounding noise (~1e-9) -- it is checked
+to be noise-sized instead, and its Adam update (noise/|noise| * lr) to be at most lr per step."""
+
+ZERO_GRAD = "pool.score.bias"
 import os
 
 import numpy as np
@@ -54,6 +59,9 @@ def test_autograd_grads_vs_reference_golden(golden_dir, name):
     assert abs(loss.item() - float(g["loss"])) < 1e-5
     worst = {}
     for n, prm in m.named_parameters():
+        if n == ZERO_GRAD:
+            assert prm.grad.abs().max().item() < 1e-6 and abs(float(g[f"grad_samp/{n}"][0])) < 1e-6
+            continue
         ref = g[f"grad_samp/{n}"]
         got = prm.grad.reshape(-1)[::97].cpu().numpy()
         scale = max(np.abs(ref).max(), g[f"grad_stat/{n}"][0] / np.sqrt(prm.numel()))
@@ -81,7 +89,8 @@ def test_grads_vs_oracle_seeded(use_roi, B, T):
     loss = torch.nn.functional.cross_entropy(logits, y.to(dev), label_smoothing=0.05)
     loss.backward()
     assert abs(loss.item() - loss_ref.item()) < 1e-5
-    errs = {n: rel_err(prm.grad, grads_ref[n]) for n, prm in m.named_parameters()}
+    errs = {n: rel_err(prm.grad, grads_ref[n]) for n, prm in m.named_parameters() if n != ZERO_GRAD}
+    assert dict(m.named_parameters())[ZERO_GRAD].grad.abs().max().item() < 1e-6
     bad = {k: v for k, v in errs.items() if v > 1e-4}
     assert not bad, bad
 
@@ -104,7 +113,8 @@ def test_train_step_vs_reference_golden(golden_dir, name):
         ref = g[f"step_samp/{n}"]
         got = v.reshape(-1)[::97].cpu().numpy()
         # one Adam step moves every weight by ~lr; agree to 1% of that step
-        assert np.abs(got - ref).max() <= 3e-6, (n, np.abs(got - ref).max())
+        tol = 2 * 3e-4 + 1e-6 if n == ZERO_GRAD else 3e-6
+        assert np.abs(got - ref).max() <= tol, (n, np.abs(got - ref).max())
 
 
 def test_three_train_steps_vs_oracle():
@@ -124,7 +134,8 @@ def test_three_train_steps_vs_oracle():
         assert abs(tr.grad_norm.item() - gn_ref.item()) < 2e-4 * gn_ref.item()
     ref = st.params()
     for n, v in m.state_dict().items():
-        assert (v.cpu() - ref[n]).abs().max().item() < 2e-5, n
+        tol = 2 * 3 * 3e-4 if n == ZERO_GRAD else 2e-5
+        assert (v.cpu() - ref[n]).abs().max().item() < tol, n
 
 
 def test_dropout_statistics_and_train_mode():
