@@ -122,6 +122,14 @@ int ssb_clip_adam_step(float* p, float* g, float* m, float* v, int64_t n, const 
 /* Counter-based dropout: y = x * keep(seed, i) / (1-p)  (nn.GRU inter-layer dropout, train:266). */
 int ssb_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, void* stream);
 
+/* K3a on the tensor cores: C[M,N] = [A1 | A2] . W[N, K1+K2]^T + bias with tcgen05.mma (bf16 operands
+ * converted on the fly from fp32, fp32 accumulation in TMEM).  passes = 1: bf16; 3: split-bf16 (fp32 grade).
+ * The matmuls inside nn.GRU (train_model_official.py:261-267); A2 may be NULL. */
+int ssb_gemm_tc(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                const float* W, int64_t ldw, const float* bias, float* C, int64_t ldc,
+                int64_t M, int64_t N, int32_t passes, int32_t accumulate,
+                const int64_t* lengths, int64_t T, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

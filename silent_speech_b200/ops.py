@@ -215,3 +215,18 @@ def clip_adam_step(p, g, m, v, sqnorm, max_norm, lr, beta1, beta2, eps, step, wr
     check(_lib.lib().ssb_clip_adam_step(ptr(p), ptr(g), ptr(m), ptr(v), i64(p.numel()), ptr(sqnorm), f32(max_norm),
                                         f32(lr), f32(beta1), f32(beta2), f32(eps), i64(step),
                                         i32(1 if write_back_grad else 0), ptr(norm_out), stream_ptr()))
+
+
+# ----------------------------------------------------------------------------- tensor-core path
+def gemm_tc(A1: torch.Tensor, W: torch.Tensor, bias, C2d: torch.Tensor, A2: Optional[torch.Tensor] = None,
+            passes: int = 3, accumulate: bool = False, lengths=None, T: int = 0, c_col0: int = 0):
+    """C[:, c_col0:c_col0+N] = [A1 | A2] @ W^T + bias on tcgen05 (bf16 x passes, fp32 accumulate)."""
+    import ctypes
+    M, K1 = A1.shape
+    N = W.shape[0]
+    K2 = 0 if A2 is None else A2.shape[1]
+    check(_lib.lib().ssb_gemm_tc(ptr(A1), i64(A1.stride(0)), i64(K1), ptr(A2), i64(0 if A2 is None else A2.stride(0)),
+                                 i64(K2), ptr(W), i64(W.stride(0)), ptr(bias),
+                                 ctypes.c_void_p(C2d.data_ptr() + 4 * c_col0), i64(C2d.stride(0)), i64(M), i64(N),
+                                 i32(passes), i32(1 if accumulate else 0), ptr(lengths), i64(T), stream_ptr()))
+    return C2d
