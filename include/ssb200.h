@@ -130,6 +130,17 @@ int ssb_gemm_tc(const float* A1, int64_t lda1, int64_t K1, const float* A2, int6
                 int64_t M, int64_t N, int32_t passes, int32_t accumulate,
                 const int64_t* lengths, int64_t T, void* stream);
 
+/* K3b on the tensor cores (cluster of 4 CTAs, W_hh resident in shared memory as bf16, tcgen05.mma per
+ * step, h slices exchanged by bulk DSMEM copies).  Same semantics/layouts as ssb_gru_layer_fwd, except that
+ * gi must already include b_ih + (b_hr, b_hz, 0) -- build that bias with ssb_gru_fold_bias and pass it to the
+ * projection GEMM.  order (nullable) = clip index per batch slot (e.g. sorted by length). passes = 1 or 3. */
+int ssb_gru_fold_bias(const float* bih_f, const float* bhh_f, const float* bih_r, const float* bhh_r,
+                      float* out1152, void* stream);
+int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_t* lengths, const int32_t* order,
+                         int64_t B, int64_t T, int32_t hidden,
+                         const float* whh_f, const float* bhh_f, const float* whh_r, const float* bhh_r,
+                         float* out, float* gates, int32_t passes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

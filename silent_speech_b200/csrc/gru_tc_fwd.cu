@@ -1,0 +1,305 @@
+// K3b on the tensor cores -- GRU time recurrence as a persistent thread-block-cluster kernel.
+//
+// Same semantics as gru_fwd.cu (packed-sequence nn.GRU, train_model_official.py:261-267, 301-305).
+// W_hh (576x192) does not fit one SM, so a cluster of 4 CTAs splits the 192 hidden units: CTA `rank`
+// owns units 48*rank..+47, i.e. 144 gate rows of W_hh, resident in shared memory as bf16 for the whole
+// sequence.  Per step every CTA computes D[128 clips x 144] = h[128 x 192] . W_slice^T with tcgen05.mma
+// (fp32 accumulators in TMEM), applies the gate non-linearities to its 48 units in registers (fp32
+// master copy of h stays in registers), writes the new h slice as bf16 into its own A-operand buffer and
+// pushes that 12 KB slice to the three peers with ONE bulk DSMEM copy each (cp.async.bulk
+// shared::cta -> shared::cluster) that completes on the peer's mbarrier.  No cluster-wide barrier in the
+// loop: `full` (bytes landed) and `empty` (peer's MMA finished reading) mbarriers carry the dependencies.
+//
+// kSplit = false: bf16 operands (fast mode).  kSplit = true: split-bf16 (h = hi + lo, W = hi + lo,
+// D += Ahi.Bhi + Ahi.Blo + Alo.Bhi) -- fp32-parity grade.
+//
+// gi must carry b_ih + (b_hr, b_hz, 0): the r/z parts of b_hh are folded into the projection bias
+// (ssb_gru_fold_bias); b_hn stays separate because it sits inside r * (W_hn h + b_hn).
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace ssb {
+namespace grutc {
+
+constexpr int H = kHidden, G3 = 3 * H;
+constexpr int CL = 4;                      // cluster size
+constexpr int U = H / CL;                  // 48 units per CTA
+constexpr int NG = 3 * U;                  // 144 gate columns per CTA (UMMA N)
+constexpr int BM = 128;                    // clips per cluster (UMMA M)
+constexpr int KCH = H / 8;                 // 24 k-chunks of 8
+constexpr int A_LBO = (BM / 8) * 128;      // 2048: one k-chunk holds all 128 rows
+constexpr int B_LBO = (NG / 8) * 128;      // 2304
+constexpr int A_BYTES = KCH * A_LBO;       // 49,152
+constexpr int B_BYTES = KCH * B_LBO;       // 55,296
+constexpr int SLICE = (U / 8) * A_LBO;     // 12,288: this CTA's 6 k-chunks of the A operand
+constexpr int EPI_THREADS = 256, THREADS = EPI_THREADS + 32;
+constexpr int TMEM_COLS = 256;
+
+struct Ctl {
+  uint64_t full, mma_done, empty;
+  uint32_t tmem_base;
+  int maxlen;
+};
+
+template <bool kSplit>
+constexpr size_t smem_bytes() { return (kSplit ? 2 : 1) * (A_BYTES + B_BYTES) + sizeof(Ctl); }
+
+__device__ __forceinline__ float sigm(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+template <bool kSplit, bool kSave>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(THREADS, 1)
+gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
+                  const float* __restrict__ whh_f, const float* __restrict__ whh_r,
+                  const float* __restrict__ bhn_f, const float* __restrict__ bhn_r,
+                  const int64_t* __restrict__ lengths, const int32_t* __restrict__ order, int B, int T,
+                  float* __restrict__ out, float* __restrict__ gates) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* a_hi = smem;
+  uint8_t* b_hi = smem + A_BYTES;
+  uint8_t* a_lo = smem + A_BYTES + B_BYTES;                 // only when kSplit
+  uint8_t* b_lo = smem + 2 * A_BYTES + B_BYTES;
+  Ctl& ctl = *reinterpret_cast<Ctl*>(smem + (kSplit ? 2 : 1) * (A_BYTES + B_BYTES));
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = tc::cluster_ctarank();
+  const int dir = blockIdx.y;
+  const int b0 = (blockIdx.x / CL) * BM;
+  const float* __restrict__ whh = dir ? whh_r : whh_f;
+  const float* __restrict__ bhn = dir ? bhn_r : bhn_f;
+
+  // ---- one-time: W_hh slice -> bf16 (hi, lo) in the canonical K-major layout; h = 0
+  for (int p = tid; p < NG * KCH; p += THREADS) {
+    const int n = p / KCH, kc = p % KCH;
+    const int g = n / U, u = n % U;
+    const float* src = whh + (int64_t)(g * H + rank * U + u) * H + kc * 8;
+    const float4 v0 = __ldg(reinterpret_cast<const float4*>(src)), v1 = __ldg(reinterpret_cast<const float4*>(src + 4));
+    const float x[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    const uint32_t off = kc * B_LBO + (n >> 3) * 128 + (n & 7) * 16;
+    float hh[8], ll[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) tc::split_bf16(x[j], hh[j], ll[j]);
+    *reinterpret_cast<uint4*>(b_hi + off) = make_uint4(tc::pack_bf16(hh[0], hh[1]), tc::pack_bf16(hh[2], hh[3]),
+                                                       tc::pack_bf16(hh[4], hh[5]), tc::pack_bf16(hh[6], hh[7]));
+    if (kSplit)
+      *reinterpret_cast<uint4*>(b_lo + off) = make_uint4(tc::pack_bf16(ll[0], ll[1]), tc::pack_bf16(ll[2], ll[3]),
+                                                         tc::pack_bf16(ll[4], ll[5]), tc::pack_bf16(ll[6], ll[7]));
+  }
+  for (int i = tid; i < A_BYTES / 16; i += THREADS) {
+    reinterpret_cast<uint4*>(a_hi)[i] = make_uint4(0, 0, 0, 0);
+    if (kSplit) reinterpret_cast<uint4*>(a_lo)[i] = make_uint4(0, 0, 0, 0);
+  }
+  if (tid == 0) {
+    tc::mbar_init(&ctl.full, 1);
+    tc::mbar_init(&ctl.mma_done, 1);
+    tc::mbar_init(&ctl.empty, CL - 1);
+    tc::mbar_fence_init();
+    ctl.maxlen = 0;
+  }
+  if (warp == EPI_THREADS / 32) tc::tmem_alloc<TMEM_COLS>(&ctl.tmem_base);
+  __syncthreads();
+
+  // ---- this thread's clip (epilogue threads: one row each, two threads per row split the 48 units)
+  const int m = (warp & 3) * 32 + lane;          // row of the tile == TMEM lane
+  const int hf = (warp >> 2) & 1;                // which 24 of the CTA's 48 units
+  int b = -1, len = 0;
+  if (tid < EPI_THREADS && b0 + m < B) {
+    b = order ? order[b0 + m] : b0 + m;
+    len = max(0, min((int)lengths[b], T));
+  }
+  if (tid < EPI_THREADS) atomicMax(&ctl.maxlen, len);
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const int maxlen = ctl.maxlen;
+  const uint32_t tmem = ctl.tmem_base;
+  tc::cluster_sync_all();                        // every CTA's barriers exist before any remote operation
+
+  constexpr uint32_t idesc = tc::make_idesc_bf16(BM, NG);
+  constexpr uint32_t kTxBytes = (CL - 1) * SLICE * (kSplit ? 2 : 1);
+
+  if (warp == EPI_THREADS / 32) {
+    // =============================== MMA issuer warp ===============================
+    for (int s = 1; s < maxlen; ++s) {
+      tc::mbar_wait_cluster(&ctl.full, (s - 1) & 1);            // all four h slices of step s-1 are in place
+      tc::fence_after_sync();
+      if (lane == 0) {
+#pragma unroll 1
+        for (int j = 0; j < H / 16; ++j) {
+          const uint64_t dah = tc::make_desc(tc::smem_u32(a_hi) + j * 2 * A_LBO, A_LBO, 128);
+          const uint64_t dbh = tc::make_desc(tc::smem_u32(b_hi) + j * 2 * B_LBO, B_LBO, 128);
+          tc::mma_bf16(tmem, dah, dbh, idesc, j > 0);
+          if (kSplit) {
+            const uint64_t dal = tc::make_desc(tc::smem_u32(a_lo) + j * 2 * A_LBO, A_LBO, 128);
+            const uint64_t dbl = tc::make_desc(tc::smem_u32(b_lo) + j * 2 * B_LBO, B_LBO, 128);
+            tc::mma_bf16(tmem, dah, dbl, idesc, true);
+            tc::mma_bf16(tmem, dal, dbh, idesc, true);
+          }
+        }
+        tc::mma_commit(&ctl.mma_done);
+      }
+      __syncwarp();
+    }
+  } else {
+    // =============================== gate / state warps ===============================
+    const int j0 = (int)rank * U + hf * 24;                      // first global hidden unit of this thread
+    float h[24], bn[24];
+#pragma unroll
+    for (int q = 0; q < 24; ++q) { h[q] = 0.f; bn[q] = __ldg(bhn + j0 + q); }
+    const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    const uint32_t a_row_off = (m >> 3) * 128 + (m & 7) * 16;
+
+    for (int s = 0; s < maxlen; ++s) {
+      const bool act = s < len;
+      const int t = dir ? (len - 1 - s) : s;
+      const int64_t bt = (int64_t)(act ? b : 0) * T + (act ? t : 0);
+      float4 g4[18];                                             // gi: 3 gates x 24 units, issued before the wait
+      if (act) {
+        const float* gp = gi + bt * gi_ld + dir * G3 + j0;
+#pragma unroll
+        for (int g = 0; g < 3; ++g)
+#pragma unroll
+          for (int v = 0; v < 6; ++v) g4[g * 6 + v] = __ldg(reinterpret_cast<const float4*>(gp + g * H) + v);
+      }
+      if (s >= 1) {
+        tc::mbar_wait_bounded(&ctl.mma_done, (s - 1) & 1);
+        tc::fence_after_sync();
+        if (tid == 0) {                                          // tell the peers: my tensor core is done reading h(s-1)
+          for (uint32_t p = 1; p < CL; ++p) tc::mbar_arrive_remote(tc::mapa(tc::smem_u32(&ctl.empty), (rank + p) % CL));
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        float ar[8], az[8], an[8];
+        if (s >= 1) {
+          tc::tmem_ld8(trow + 0 * U + hf * 24 + c * 8, ar);
+          tc::tmem_ld8(trow + 1 * U + hf * 24 + c * 8, az);
+          tc::tmem_ld8(trow + 2 * U + hf * 24 + c * 8, an);
+          tc::tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) ar[q] = az[q] = an[q] = 0.f;
+        }
+        if (act) {
+          const float* gr = reinterpret_cast<const float*>(&g4[0 * 6 + c * 2]);
+          const float* gz = reinterpret_cast<const float*>(&g4[1 * 6 + c * 2]);
+          const float* gn = reinterpret_cast<const float*>(&g4[2 * 6 + c * 2]);
+          float hn8[8], r8[8], z8[8], n8[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const int u = c * 8 + q;
+            r8[q] = sigm(gr[q] + ar[q]);
+            z8[q] = sigm(gz[q] + az[q]);
+            hn8[q] = an[q] + bn[u];
+            n8[q] = tanhf(gn[q] + r8[q] * hn8[q]);
+            h[u] = (1.0f - z8[q]) * n8[q] + z8[q] * h[u];
+          }
+          float* orow = out + bt * (2 * H) + dir * H + j0 + c * 8;
+          *reinterpret_cast<float4*>(orow) = make_float4(h[c * 8], h[c * 8 + 1], h[c * 8 + 2], h[c * 8 + 3]);
+          *reinterpret_cast<float4*>(orow + 4) = make_float4(h[c * 8 + 4], h[c * 8 + 5], h[c * 8 + 6], h[c * 8 + 7]);
+          if (kSave) {
+            float* gs = gates + (bt * 2 + dir) * (4 * H) + j0 + c * 8;
+            *reinterpret_cast<float4*>(gs) = make_float4(r8[0], r8[1], r8[2], r8[3]);
+            *reinterpret_cast<float4*>(gs + 4) = make_float4(r8[4], r8[5], r8[6], r8[7]);
+            *reinterpret_cast<float4*>(gs + H) = make_float4(z8[0], z8[1], z8[2], z8[3]);
+            *reinterpret_cast<float4*>(gs + H + 4) = make_float4(z8[4], z8[5], z8[6], z8[7]);
+            *reinterpret_cast<float4*>(gs + 2 * H) = make_float4(n8[0], n8[1], n8[2], n8[3]);
+            *reinterpret_cast<float4*>(gs + 2 * H + 4) = make_float4(n8[4], n8[5], n8[6], n8[7]);
+            *reinterpret_cast<float4*>(gs + 3 * H) = make_float4(hn8[0], hn8[1], hn8[2], hn8[3]);
+            *reinterpret_cast<float4*>(gs + 3 * H + 4) = make_float4(hn8[4], hn8[5], hn8[6], hn8[7]);
+          }
+          // new h (8 units = one 16-byte core-matrix row) into this CTA's slice of the A operand
+          const uint32_t off = (uint32_t)((rank * U + hf * 24 + c * 8) >> 3) * A_LBO + a_row_off;
+          float hh[8], ll[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) tc::split_bf16(h[c * 8 + q], hh[q], ll[q]);
+          *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(tc::pack_bf16(hh[0], hh[1]), tc::pack_bf16(hh[2], hh[3]),
+                                                             tc::pack_bf16(hh[4], hh[5]), tc::pack_bf16(hh[6], hh[7]));
+          if (kSplit)
+            *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(tc::pack_bf16(ll[0], ll[1]), tc::pack_bf16(ll[2], ll[3]),
+                                                               tc::pack_bf16(ll[4], ll[5]), tc::pack_bf16(ll[6], ll[7]));
+        }
+      }
+      tc::fence_async_smem();                                    // slice visible to the async proxy (MMA, bulk copy)
+      tc::fence_before_sync();                                   // TMEM reads ordered before the next step's MMA
+      asm volatile("bar.sync 1, %0;\n" ::"n"(EPI_THREADS) : "memory");
+      if (tid == 0 && s + 1 < maxlen) {
+        if (s >= 1) tc::mbar_wait_cluster(&ctl.empty, (s - 1) & 1);   // peers finished reading h(s-1) from their A
+        tc::mbar_arrive_expect_tx(&ctl.full, kTxBytes);               // my own slice is in place; expect the peers' bytes
+        const uint32_t src_hi = tc::smem_u32(a_hi) + rank * SLICE, src_lo = tc::smem_u32(a_lo) + rank * SLICE;
+        for (uint32_t p = 1; p < CL; ++p) {
+          const uint32_t peer = (rank + p) % CL;
+          const uint32_t bar = tc::mapa(tc::smem_u32(&ctl.full), peer);
+          tc::bulk_copy_to_peer(tc::mapa(src_hi, peer), src_hi, SLICE, bar);
+          if (kSplit) tc::bulk_copy_to_peer(tc::mapa(src_lo, peer), src_lo, SLICE, bar);
+        }
+      }
+    }
+    // zeros past each clip's length (pad_packed_sequence semantics)
+    if (b >= 0) {
+      for (int t = len; t < T; ++t) {
+        float* orow = out + ((int64_t)b * T + t) * (2 * H) + dir * H + j0;
+#pragma unroll
+        for (int v = 0; v < 6; ++v) reinterpret_cast<float4*>(orow)[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  }
+  tc::fence_before_sync();
+  tc::cluster_sync_all();                        // no CTA leaves while a peer may still touch its shared memory
+  if (warp == EPI_THREADS / 32) tc::tmem_dealloc<TMEM_COLS>(tmem);
+}
+
+// gi_bias[d*576 + i] = b_ih_d[i] + (i < 384 ? b_hh_d[i] : 0)
+__global__ void fold_bias_kernel(const float* __restrict__ bih_f, const float* __restrict__ bhh_f,
+                                 const float* __restrict__ bih_r, const float* __restrict__ bhh_r, float* __restrict__ o) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 2 * G3) return;
+  const int d = i / G3, k = i % G3;
+  const float* bi = d ? bih_r : bih_f;
+  const float* bh = d ? bhh_r : bhh_f;
+  o[i] = bi[k] + (k < 2 * H ? bh[k] : 0.f);
+}
+
+}  // namespace grutc
+}  // namespace ssb
+
+extern "C" int ssb_gru_fold_bias(const float* bih_f, const float* bhh_f, const float* bih_r, const float* bhh_r,
+                                 float* out1152, void* stream) {
+  using namespace ssb;
+  SSB_REQUIRE(bih_f && bhh_f && bih_r && bhh_r && out1152, "null pointer");
+  grutc::fold_bias_kernel<<<cdiv(2 * grutc::G3, 256), 256, 0, (cudaStream_t)stream>>>(bih_f, bhh_f, bih_r, bhh_r, out1152);
+  SSB_LAUNCH_CHECK();
+  return SSB_OK;
+}
+
+// Tensor-core recurrence of one bidirectional layer.  gi [B,T,gi_ld] must already contain
+// b_ih + (b_hr, b_hz, 0) (ssb_gru_fold_bias); bhh_* are the full b_hh vectors (the n part is read).
+// order (nullable) = clip index per batch slot, e.g. sorted by length so that tiles are homogeneous.
+// passes = 1 (bf16) or 3 (split-bf16).  Output / gates layouts as ssb_gru_layer_fwd.
+extern "C" int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_t* lengths, const int32_t* order,
+                                    int64_t B, int64_t T, int32_t hidden,
+                                    const float* whh_f, const float* bhh_f, const float* whh_r, const float* bhh_r,
+                                    float* out, float* gates, int32_t passes, void* stream) {
+  using namespace ssb;
+  using namespace ssb::grutc;
+  SSB_REQUIRE(gi && lengths && whh_f && bhh_f && whh_r && bhh_r && out, "null pointer");
+  SSB_REQUIRE(hidden == H, "hidden must be 192");
+  SSB_REQUIRE(gi_ld >= 2 * G3 && gi_ld % 4 == 0 && ((uintptr_t)gi & 15) == 0, "gi must be 16-byte aligned rows of >= 1152");
+  SSB_REQUIRE(((uintptr_t)whh_f & 15) == 0 && ((uintptr_t)whh_r & 15) == 0 && ((uintptr_t)out & 15) == 0, "alignment");
+  SSB_REQUIRE(passes == 1 || passes == 3, "passes must be 1 or 3");
+  if (B == 0) return SSB_OK;
+  dim3 grid(CL * cdiv(B, BM), 2), block(THREADS);
+  cudaStream_t st = (cudaStream_t)stream;
+#define SSB_LAUNCH_GRUTC(SPLIT, SAVE)                                                                          \
+  do {                                                                                                          \
+    SSB_CUDA(cudaFuncSetAttribute(gru_tc_fwd_kernel<SPLIT, SAVE>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                  (int)smem_bytes<SPLIT>()));                                                   \
+    gru_tc_fwd_kernel<SPLIT, SAVE><<<grid, block, smem_bytes<SPLIT>(), st>>>(                                   \
+        gi, gi_ld, whh_f, whh_r, bhh_f + 2 * H, bhh_r + 2 * H, lengths, order, (int)B, (int)T, out, gates);     \
+  } while (0)
+  if (passes == 3) { if (gates) SSB_LAUNCH_GRUTC(true, true); else SSB_LAUNCH_GRUTC(true, false); }
+  else             { if (gates) SSB_LAUNCH_GRUTC(false, true); else SSB_LAUNCH_GRUTC(false, false); }
+#undef SSB_LAUNCH_GRUTC
+  SSB_LAUNCH_CHECK();
+  return SSB_OK;
+}

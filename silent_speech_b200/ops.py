@@ -230,3 +230,24 @@ def gemm_tc(A1: torch.Tensor, W: torch.Tensor, bias, C2d: torch.Tensor, A2: Opti
                                  ctypes.c_void_p(C2d.data_ptr() + 4 * c_col0), i64(C2d.stride(0)), i64(M), i64(N),
                                  i32(passes), i32(1 if accumulate else 0), ptr(lengths), i64(T), stream_ptr()))
     return C2d
+
+
+def gru_fold_bias(bih_f, bhh_f, bih_r, bhh_r) -> torch.Tensor:
+    out = torch.empty(2 * 3 * HIDDEN, device=bih_f.device, dtype=torch.float32)
+    check(_lib.lib().ssb_gru_fold_bias(ptr(bih_f), ptr(bhh_f), ptr(bih_r), ptr(bhh_r), ptr(out), stream_ptr()))
+    return out
+
+
+def gru_layer_fwd_tc(gi, lengths, whh_f, bhh_f, whh_r, bhh_r, passes=3, order=None, out=None, gates=None):
+    """Tensor-core recurrence; gi must include the folded bias (gru_fold_bias)."""
+    _need(gi, torch.float32, "gi")
+    _need(lengths, torch.int64, "lengths")
+    B, T, ld = gi.shape
+    if out is None:
+        out = torch.empty(B, T, 2 * HIDDEN, device=gi.device, dtype=torch.float32)
+    if order is not None:
+        _need(order, torch.int32, "order")
+    check(_lib.lib().ssb_gru_layer_fwd_tc(ptr(gi), i64(ld), ptr(lengths), ptr(order), i64(B), i64(T), i32(HIDDEN),
+                                          ptr(whh_f), ptr(bhh_f), ptr(whh_r), ptr(bhh_r), ptr(out), ptr(gates),
+                                          i32(passes), stream_ptr()))
+    return out

@@ -42,3 +42,34 @@ def test_gemm_tc_vs_fp64(M, N, K1, K2):
         ops.gemm_tc(A1[:Mr].to(dev), W.to(dev), None, C, A2=None if A2 is None else A2[:Mr].to(dev), passes=3,
                     accumulate=True, lengths=L.to(dev), T=T)
         assert rel_err(C, A[:Mr].double() @ W.double().T + 1.0) < 2e-5
+
+
+@pytest.mark.parametrize("B,T", [(5, 7), (200, 23)])
+def test_gru_tc_recurrence_vs_fp32_kernel(B, T):
+    dev = _cuda()
+    from oracle import ref_model
+    from silent_speech_b200 import ops
+    p = ref_model.synth_params(21, scale=1.5)
+    g = torch.Generator().manual_seed(B)
+    L = torch.randint(1, T + 1, (B,), generator=g); L[0] = T; L[min(1, B - 1)] = 1
+    gi = (torch.randn(B, T, 1152, generator=g) * 0.7).to(dev)
+    w = [p[f"gru.{n}"].to(dev).contiguous() for n in ("weight_hh_l0", "bias_hh_l0", "weight_hh_l0_reverse", "bias_hh_l0_reverse")]
+    Ld = L.to(dev)
+    gates_ref = torch.zeros(B, T, 2, 4, 192, device=dev)
+    ref = ops.gru_layer_fwd(gi, Ld, *w, gates=gates_ref)
+    # the TC kernel expects b_hr, b_hz folded into gi
+    fold = torch.zeros(1152, device=dev)
+    fold[:384] = w[1][:384]; fold[576:960] = w[3][:384]
+    gi_f = (gi + fold).contiguous()
+    order = torch.argsort(Ld, descending=True).to(torch.int32)
+    mask = (torch.arange(T)[None, :] < L[:, None]).to(dev)
+    for passes, tol in ((3, 2e-5), (1, 3e-2)):
+        for od in (None, order):
+            gates = torch.zeros(B, T, 2, 4, 192, device=dev)
+            out = ops.gru_layer_fwd_tc(gi_f, Ld, *w, passes=passes, order=od, gates=gates)
+            torch.cuda.synchronize()
+            e = rel_err(out, ref)
+            assert e < tol, (passes, od is not None, e)
+            assert torch.all(out[~mask] == 0)
+            eg = rel_err(gates * mask[..., None, None, None], gates_ref * mask[..., None, None, None])
+            assert eg < tol * 5, (passes, eg)
