@@ -173,6 +173,8 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="clips per GPU (default 4096 infer / 128 train)")
     ap.add_argument("--lengths", default="full", choices=["full", "uniform"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", default="tc3", choices=["fp32", "tc3", "bf16"],
+                    help="fp32 = CUDA-core FMA; tc3 = tcgen05 split-bf16 x3 (fp32-parity grade); bf16 = tcgen05 single pass")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
@@ -192,7 +194,7 @@ def main():
     B = args.batch or (4096 if args.workload == "infer" else 128)
     peaks = load_peaks()
     p = ref_model.synth_params(42)         # seed-42 weights of the reference's init magnitudes (no ckpt is shipped)
-    model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=True)
+    model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=True, precision=args.precision)
     model.load_state_dict(p)
     model = model.to(dev)
     d = make_batch(B, T_FRAMES, args.lengths, seed=42 + rank)
@@ -290,8 +292,10 @@ def main():
             cpu = {"value": v, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample}
         line = {"metric": metric_name(args.workload), "value": value, "unit": "clips/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": workload_config(args.workload, B) | {"lengths": "all=T" if args.lengths == "full" else "uniform[6,T]"},
+                "scaling": "weak", "vs_baseline": None,
+                "dtype": {"fp32": "f32", "tc3": "bf16x3 split operands, f32 accumulate (f32-parity grade); CNN f32", "bf16": "bf16 operands, f32 accumulate; CNN f32"}[args.precision],
+                "data": "synthetic",
+                "config": workload_config(args.workload, B) | {"precision": args.precision} | {"lengths": "all=T" if args.lengths == "full" else "uniform[6,T]"},
                 "clocks": clk.summary(),
                 "e2e": {"value": e2e_val, "unit": "clips/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}

@@ -54,21 +54,33 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
     gi = torch.empty(B, T, 2 * G3, device=dev, dtype=torch.float32)
     gi2d = gi.view(B * T, 2 * G3)
     p0, p1 = model.gru.layer(0), model.gru.layer(1)
+    prec = getattr(model, "precision", "fp32")
+    passes = {"fp32": 0, "tc3": 3, "bf16": 1}[prec]
+    order = None
+    if passes and B > 128:      # homogeneous 128-clip tiles: each cluster runs max(len in tile) steps
+        order = torch.argsort(lengths, descending=True).to(torch.int32)
 
-    _project(X.view(B * T, x_dim), p0["weight_ih"], p0["bias_ih"], gi2d, lengths, T,
-             extra=None if emb is None else emb.view(B * T, -1))
+    def layer(pl, A2d, extra, gates):
+        if not passes:
+            _project(A2d, pl["weight_ih"], pl["bias_ih"], gi2d, lengths, T, extra=extra)
+            return ops.gru_layer_fwd(gi, lengths, pl["weight_hh"][0], pl["bias_hh"][0], pl["weight_hh"][1],
+                                     pl["bias_hh"][1], gates=gates)
+        fold = ops.gru_fold_bias(pl["bias_ih"][0], pl["bias_hh"][0], pl["bias_ih"][1], pl["bias_hh"][1])
+        for d in (0, 1):
+            ops.gemm_tc(A2d, pl["weight_ih"][d], fold[d * G3:(d + 1) * G3], gi2d, A2=extra, passes=passes,
+                        lengths=lengths, T=T, c_col0=d * G3)
+        return ops.gru_layer_fwd_tc(gi, lengths, pl["weight_hh"][0], pl["bias_hh"][0], pl["weight_hh"][1],
+                                    pl["bias_hh"][1], passes=passes, order=order, gates=gates)
+
     gates0 = torch.empty(B, T, 2, 4, H, device=dev, dtype=torch.float32) if save else None
-    seq0 = ops.gru_layer_fwd(gi, lengths, p0["weight_hh"][0], p0["bias_hh"][0], p0["weight_hh"][1],
-                             p0["bias_hh"][1], gates=gates0)
+    seq0 = layer(p0, X.view(B * T, x_dim), None if emb is None else emb.view(B * T, -1), gates0)
     seq0_in = seq0
     drop_seed = 0
     if training and model.gru_dropout > 0:
         drop_seed = model._next_seed()
         seq0_in = ops.dropout(seq0, model.gru_dropout, drop_seed)
-    _project(seq0_in.view(B * T, 2 * H), p1["weight_ih"], p1["bias_ih"], gi2d, lengths, T)
     gates1 = torch.empty(B, T, 2, 4, H, device=dev, dtype=torch.float32) if save else None
-    seq1 = ops.gru_layer_fwd(gi, lengths, p1["weight_hh"][0], p1["bias_hh"][0], p1["weight_hh"][1],
-                             p1["bias_hh"][1], gates=gates1)
+    seq1 = layer(p1, seq0_in.view(B * T, 2 * H), None, gates1)
     saved = None
     if save:
         saved = [torch.empty(B, T, device=dev), torch.empty(B, 2 * H, device=dev), torch.empty(B, 2 * H, device=dev),

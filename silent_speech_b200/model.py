@@ -102,8 +102,13 @@ class _PoolParams(nn.Module):
 
 class BiGRUClassifier(nn.Module):
     def __init__(self, x_dim: int, num_classes: int, use_roi: bool = False, roi_emb: int = ROI_EMB,
-                 hidden: int = HIDDEN, gru_layers: int = 2, standardize_roi: bool = True):
+                 hidden: int = HIDDEN, gru_layers: int = 2, standardize_roi: bool = True,
+                 precision: str = "tc3"):
         super().__init__()
+        if precision not in ("fp32", "tc3", "bf16"):
+            raise ValueError("precision must be 'fp32' (CUDA-core FMA), 'tc3' (tensor cores, split-bf16 x3, "
+                             "fp32-parity grade) or 'bf16' (tensor cores, single bf16 pass)")
+        self.precision = precision
         if hidden != HIDDEN or roi_emb != ROI_EMB or gru_layers != 2:
             raise ValueError("libssb200 kernels are specialised for hidden=192, roi_emb=32, 2 GRU layers "
                              "(train_model_official.py:402, live_infer_official.py:209-217)")
