@@ -127,25 +127,33 @@ gemm_tc_kernel(const float* __restrict__ A1, int64_t lda1, int K1, const float* 
     const int c = chunks - 1;
     tc::mbar_wait(&tail.bar[c % STAGES], (c / STAGES) & 1);
     tc::fence_after_sync();
-    const int row = m0 + (warp & 3) * 32 + lane;
+    // all MMAs have completed, so the operand stages are free: each warp transposes its 32x32 blocks
+    // through a private padded smem tile so that global stores are full 128-byte row segments
+    float* tile = reinterpret_cast<float*>(smem) + warp * (32 * 33);
+    const int row0 = m0 + (warp & 3) * 32;
     const int jbeg = (warp >> 2) * 3;
 #pragma unroll 1
     for (int j = jbeg; j < jbeg + 3; ++j) {
       float v[32];
       tc::tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + j * 32, v);
       tc::tmem_ld_wait();
-      if (row < M) {
-        float* crow = C + (int64_t)row * ldc + n0 + j * 32;
 #pragma unroll
-        for (int q = 0; q < 32; ++q) {
-          const int n = n0 + j * 32 + q;
-          if (n < N) {
-            float o = v[q] + (bias ? __ldg(bias + n) : 0.f);
-            if (accumulate) o += crow[q];
-            crow[q] = o;
+      for (int q = 0; q < 32; ++q) tile[lane * 33 + q] = v[q];
+      __syncwarp();
+      const int n = n0 + j * 32 + lane;
+      const float bv = (bias && n < N) ? __ldg(bias + n) : 0.f;
+      if (n < N) {
+#pragma unroll 4
+        for (int r = 0; r < 32; ++r) {
+          if (row0 + r < M) {
+            float* c = C + (int64_t)(row0 + r) * ldc + n;
+            float o = tile[r * 33 + lane] + bv;
+            if (accumulate) o += *c;
+            *c = o;
           }
         }
       }
+      __syncwarp();
     }
   }
   tc::fence_before_sync();

@@ -32,7 +32,8 @@ constexpr int B_LBO = (NG / 8) * 128;      // 2304
 constexpr int A_BYTES = KCH * A_LBO;       // 49,152
 constexpr int B_BYTES = KCH * B_LBO;       // 55,296
 constexpr int SLICE = (U / 8) * A_LBO;     // 12,288: this CTA's 6 k-chunks of the A operand
-constexpr int EPI_THREADS = 256, THREADS = EPI_THREADS + 32;
+constexpr int EPI_THREADS = 384, THREADS = EPI_THREADS + 32;   // 12 gate warps (3 per TMEM lane quarter) + 1 MMA warp
+constexpr int UT = 16;                     // hidden units per gate thread
 constexpr int TMEM_COLS = 256;
 
 struct Ctl {
@@ -44,7 +45,12 @@ struct Ctl {
 template <bool kSplit>
 constexpr size_t smem_bytes() { return (kSplit ? 2 : 1) * (A_BYTES + B_BYTES) + sizeof(Ctl); }
 
-__device__ __forceinline__ float sigm(float x) { return 1.0f / (1.0f + expf(-x)); }
+// fast, ~1e-7-accurate gate functions: one ex2 + one rcp each (the recurrence is MUFU/latency-bound)
+__device__ __forceinline__ float sigm(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanh_fast(float x) {
+  const float e = __expf(-2.0f * fabsf(x));
+  return copysignf(__fdividef(1.0f - e, 1.0f + e), x);
+}
 
 template <bool kSplit, bool kSave>
 __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(THREADS, 1)
@@ -98,9 +104,9 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   if (warp == EPI_THREADS / 32) tc::tmem_alloc<TMEM_COLS>(&ctl.tmem_base);
   __syncthreads();
 
-  // ---- this thread's clip (epilogue threads: one row each, two threads per row split the 48 units)
+  // ---- this thread's clip (gate threads: one row each, three threads per row split the 48 units)
   const int m = (warp & 3) * 32 + lane;          // row of the tile == TMEM lane
-  const int hf = (warp >> 2) & 1;                // which 24 of the CTA's 48 units
+  const int ug = (warp >> 2) % 3;                // which 16 of the CTA's 48 units
   int b = -1, len = 0;
   if (tid < EPI_THREADS && b0 + m < B) {
     b = order ? order[b0 + m] : b0 + m;
@@ -142,10 +148,10 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
     }
   } else {
     // =============================== gate / state warps ===============================
-    const int j0 = (int)rank * U + hf * 24;                      // first global hidden unit of this thread
-    float h[24], bn[24];
+    const int j0 = (int)rank * U + ug * UT;                      // first global hidden unit of this thread
+    float h[UT], bn[UT];
 #pragma unroll
-    for (int q = 0; q < 24; ++q) { h[q] = 0.f; bn[q] = __ldg(bhn + j0 + q); }
+    for (int q = 0; q < UT; ++q) { h[q] = 0.f; bn[q] = __ldg(bhn + j0 + q); }
     const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     const uint32_t a_row_off = (m >> 3) * 128 + (m & 7) * 16;
 
@@ -153,13 +159,13 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
       const bool act = s < len;
       const int t = dir ? (len - 1 - s) : s;
       const int64_t bt = (int64_t)(act ? b : 0) * T + (act ? t : 0);
-      float4 g4[18];                                             // gi: 3 gates x 24 units, issued before the wait
+      float4 g4[12];                                             // gi: 3 gates x 16 units, issued before the wait
       if (act) {
         const float* gp = gi + bt * gi_ld + dir * G3 + j0;
 #pragma unroll
         for (int g = 0; g < 3; ++g)
 #pragma unroll
-          for (int v = 0; v < 6; ++v) g4[g * 6 + v] = __ldg(reinterpret_cast<const float4*>(gp + g * H) + v);
+          for (int v = 0; v < 4; ++v) g4[g * 4 + v] = __ldg(reinterpret_cast<const float4*>(gp + g * H) + v);
       }
       if (s >= 1) {
         tc::mbar_wait_bounded(&ctl.mma_done, (s - 1) & 1);
@@ -169,21 +175,21 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
         }
       }
 #pragma unroll
-      for (int c = 0; c < 3; ++c) {
+      for (int c = 0; c < 2; ++c) {
         float ar[8], az[8], an[8];
         if (s >= 1) {
-          tc::tmem_ld8(trow + 0 * U + hf * 24 + c * 8, ar);
-          tc::tmem_ld8(trow + 1 * U + hf * 24 + c * 8, az);
-          tc::tmem_ld8(trow + 2 * U + hf * 24 + c * 8, an);
+          tc::tmem_ld8(trow + 0 * U + ug * UT + c * 8, ar);
+          tc::tmem_ld8(trow + 1 * U + ug * UT + c * 8, az);
+          tc::tmem_ld8(trow + 2 * U + ug * UT + c * 8, an);
           tc::tmem_ld_wait();
         } else {
 #pragma unroll
           for (int q = 0; q < 8; ++q) ar[q] = az[q] = an[q] = 0.f;
         }
         if (act) {
-          const float* gr = reinterpret_cast<const float*>(&g4[0 * 6 + c * 2]);
-          const float* gz = reinterpret_cast<const float*>(&g4[1 * 6 + c * 2]);
-          const float* gn = reinterpret_cast<const float*>(&g4[2 * 6 + c * 2]);
+          const float* gr = reinterpret_cast<const float*>(&g4[0 * 4 + c * 2]);
+          const float* gz = reinterpret_cast<const float*>(&g4[1 * 4 + c * 2]);
+          const float* gn = reinterpret_cast<const float*>(&g4[2 * 4 + c * 2]);
           float hn8[8], r8[8], z8[8], n8[8];
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
@@ -191,7 +197,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
             r8[q] = sigm(gr[q] + ar[q]);
             z8[q] = sigm(gz[q] + az[q]);
             hn8[q] = an[q] + bn[u];
-            n8[q] = tanhf(gn[q] + r8[q] * hn8[q]);
+            n8[q] = tanh_fast(gn[q] + r8[q] * hn8[q]);
             h[u] = (1.0f - z8[q]) * n8[q] + z8[q] * h[u];
           }
           float* orow = out + bt * (2 * H) + dir * H + j0 + c * 8;
@@ -209,7 +215,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
             *reinterpret_cast<float4*>(gs + 3 * H + 4) = make_float4(hn8[4], hn8[5], hn8[6], hn8[7]);
           }
           // new h (8 units = one 16-byte core-matrix row) into this CTA's slice of the A operand
-          const uint32_t off = (uint32_t)((rank * U + hf * 24 + c * 8) >> 3) * A_LBO + a_row_off;
+          const uint32_t off = (uint32_t)((rank * U + ug * UT + c * 8) >> 3) * A_LBO + a_row_off;
           float hh[8], ll[8];
 #pragma unroll
           for (int q = 0; q < 8; ++q) tc::split_bf16(h[c * 8 + q], hh[q], ll[q]);
@@ -240,7 +246,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
       for (int t = len; t < T; ++t) {
         float* orow = out + ((int64_t)b * T + t) * (2 * H) + dir * H + j0;
 #pragma unroll
-        for (int v = 0; v < 6; ++v) reinterpret_cast<float4*>(orow)[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int v = 0; v < UT / 4; ++v) reinterpret_cast<float4*>(orow)[v] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
     }
   }
