@@ -141,6 +141,12 @@ int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_t* lengths,
                          const float* whh_f, const float* bhh_f, const float* whh_r, const float* bhh_r,
                          float* out, float* gates, int32_t passes, void* stream);
 
+/* K2 on the tensor cores: same contract as ssb_roi_cnn_fwd; conv2/conv3 run as implicit GEMMs on
+ * tcgen05 (bf16 operands, fp32 accumulators in TMEM).  passes = 1 (bf16) or 3 (split-bf16, fp32 grade). */
+int ssb_roi_cnn_fwd_tc(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
+                       int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
+                       float* out, int64_t out_stride, int32_t passes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

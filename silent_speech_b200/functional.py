@@ -48,7 +48,8 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
     emb = None
     if R is not None:
         R = R.to(dev).contiguous()
-        emb = ops.roi_cnn_fwd(R, lengths, model.roi_cnn.tensors(), standardize=model.standardize_roi)
+        emb = ops.roi_cnn_fwd(R, lengths, model.roi_cnn.tensors(), standardize=model.standardize_roi,
+                              passes={"fp32": 0, "tc3": 3, "bf16": 1}[getattr(model, "precision", "fp32")])
         ctx["R"] = R
         ctx["emb"] = emb
     gi = torch.empty(B, T, 2 * G3, device=dev, dtype=torch.float32)
