@@ -34,7 +34,7 @@ constexpr int A1_BYTES = ROWS1 * PITCH1 * 16;          // 20,800
 constexpr int PLANE2 = ROWS2 * PITCH2 * 16;            // 7,488
 constexpr int A2_BYTES = 2 * PLANE2;                   // 14,976
 constexpr int IN_BYTES = IN_ROWS * IN_LD * 4;          // 20,000
-constexpr int TMEM_COLS = 256;
+template <bool kSplit> constexpr int kTmemCols = kSplit ? 256 : 128;   // x1: 6x16 / 3x32 = 96 columns in use
 
 template <bool kSplit>
 struct Layout {
@@ -114,7 +114,7 @@ __device__ __forceinline__ void build_weight_operands(uint8_t* smem, const Weigh
 
 
 template <bool kSplit>
-__global__ void __launch_bounds__(THREADS, 2)
+__global__ void __launch_bounds__(THREADS, kSplit ? 2 : 3)
 roi_cnn_tc_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ lengths, int B, int T,
                   Weights gw, int standardize, float* __restrict__ out, int64_t out_stride) {
   using L = Layout<kSplit>;
@@ -136,7 +136,7 @@ roi_cnn_tc_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
   if (tid < C3P) mz.b3[tid] = tid < C3 ? gw.b3[tid] : 0.f;
   if (tid < E) mz.bfc[tid] = gw.bfc[tid];
   for (int i = tid; i < L::P * A1_BYTES / 16; i += THREADS) reinterpret_cast<uint4*>(a1)[i] = make_uint4(0, 0, 0, 0);
-  if (warp == 0) tc::tmem_alloc<TMEM_COLS>(&mz.tmem_base);
+  if (warp == 0) tc::tmem_alloc<kTmemCols<kSplit>>(&mz.tmem_base);
   if (tid == 32) { tc::mbar_init(&mz.bar, 1); tc::mbar_fence_init(); }
   tc::fence_before_sync();
   __syncthreads();
@@ -159,28 +159,32 @@ roi_cnn_tc_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
       continue;
     }
     // ================= P0: load + standardise (train_model_official.py:286-291)
+    // mean and unbiased variance from EXACT integer sums of the u8 pixels (dp4a), one block reduction:
+    //   (u/255 - mu)/max(sd, 1e-6)  ==  (u - S1/N) / max(sqrt((S2 - S1^2/N)/(N-1)), 255e-6)
     {
-      float v[20];
-      float sum = 0.f;
+      uint32_t wv[5];
+      uint32_t s1 = 0, s2 = 0;
 #pragma unroll
       for (int j = 0; j < 5; ++j) {
         const int word = tid + j * THREADS;
-        const uint32_t w = word < NPIX / 4 ? __ldg(reinterpret_cast<const uint32_t*>(R + f * NPIX) + word) : 0u;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { v[4 * j + k] = (float)((w >> (8 * k)) & 0xffu) / 255.0f; sum += word < NPIX / 4 ? v[4 * j + k] : 0.f; }
+        wv[j] = word < NPIX / 4 ? __ldg(reinterpret_cast<const uint32_t*>(R + f * NPIX) + word) : 0u;
+        s1 = __dp4a(wv[j], 0x01010101u, s1);
+        s2 = __dp4a(wv[j], wv[j], s2);
       }
+      float mean_u = 0.f, inv_s = 1.0f / 255.0f;
       if (standardize) {
-        const float mu = block_sum(sum, mz.red, tid) / (float)NPIX;
-        float sq = 0.f;
+        s1 = __reduce_add_sync(0xffffffffu, s1);
+        s2 = __reduce_add_sync(0xffffffffu, s2);
+        uint32_t* redu = reinterpret_cast<uint32_t*>(mz.red);
+        if (lane == 0) { redu[warp] = s1; redu[8 + warp] = s2; }
+        __syncthreads();
+        uint32_t t1 = 0, t2 = 0;
 #pragma unroll
-        for (int j = 0; j < 5; ++j)
-          if (tid + j * THREADS < NPIX / 4) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) { const float d = v[4 * j + k] - mu; sq += d * d; }
-          }
-        const float sd = fmaxf(sqrtf(block_sum(sq, mz.red, tid) / (float)(NPIX - 1)), 1e-6f);
-#pragma unroll
-        for (int k = 0; k < 20; ++k) v[k] = (v[k] - mu) / sd;
+        for (int i = 0; i < THREADS / 32; ++i) { t1 += redu[i]; t2 += redu[8 + i]; }
+        const double S1 = (double)t1, S2 = (double)t2;
+        const double var_u = fmax(S2 - S1 * S1 / (double)NPIX, 0.0) / (double)(NPIX - 1);
+        mean_u = (float)(S1 / (double)NPIX);
+        inv_s = (float)(1.0 / fmax(sqrt(var_u), 255.0e-6));
       }
       // the border of the fp32 plane must read as zero padding: region R0 was a2 a moment ago
       for (int i = tid; i < IN_ROWS; i += THREADS) { s_in[i * IN_LD] = 0.f; s_in[i * IN_LD + W0 + 1] = 0.f; }
@@ -191,7 +195,8 @@ roi_cnn_tc_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
         if (word < NPIX / 4) {
           const int y = word / (W0 / 4), x = (word % (W0 / 4)) * 4;
           float* d = s_in + (y + 1) * IN_LD + x + 1;
-          d[0] = v[4 * j]; d[1] = v[4 * j + 1]; d[2] = v[4 * j + 2]; d[3] = v[4 * j + 3];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) d[k] = ((float)((wv[j] >> (8 * k)) & 0xffu) - mean_u) * inv_s;
         }
       }
     }
@@ -341,10 +346,18 @@ roi_cnn_tc_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
           tc::tmem_ld_wait();
         }
 #pragma unroll
-        for (int c = 0; c < C3; ++c) {
-          const float s = warp_sum(fmaxf(v[c] + mz.b3[c], 0.f));
-          if (lane == 0) atomicAdd(&mz.sum[c], s);
+        for (int c = 0; c < C3P; ++c) v[c] = c < C3 ? fmaxf(v[c] + mz.b3[c], 0.f) : 0.f;
+        // transpose-reduce: 31 shuffles leave the sum over the warp's 32 positions of channel `lane` in v[0]
+#pragma unroll
+        for (int off = 16, n = 16; off >= 1; off >>= 1, n >>= 1) {
+          const bool up = (lane & off) != 0;
+#pragma unroll
+          for (int i = 0; i < n; ++i) {
+            const float send = up ? v[i] : v[i + n], keep = up ? v[i + n] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+          }
         }
+        if (lane < C3) atomicAdd(&mz.sum[lane], v[0]);
       }
     }
     tc::fence_before_sync();
@@ -360,7 +373,7 @@ roi_cnn_tc_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
   }
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 0) tc::tmem_dealloc<TMEM_COLS>(tmem);
+  if (warp == 0) tc::tmem_dealloc<kTmemCols<kSplit>>(tmem);
 }
 
 }  // namespace cnntc
@@ -381,7 +394,8 @@ extern "C" int ssb_roi_cnn_fwd_tc(const uint8_t* R, const int64_t* lengths, int6
   if (B * T == 0) return SSB_OK;
   Weights gw{weights[0], weights[1], weights[2], weights[3], weights[4], weights[5], weights[6], weights[7]};
   const int64_t frames = B * T;
-  const int grid = (int)(frames < 2 * kSMs ? frames : 2 * kSMs);
+  const int per_sm = passes == 3 ? 2 : 3;
+  const int grid = (int)(frames < per_sm * kSMs ? frames : per_sm * kSMs);
   cudaStream_t st = (cudaStream_t)stream;
   if (passes == 3) {
     const size_t smem = Layout<true>::OFF_MISC + sizeof(Misc);
