@@ -16,8 +16,8 @@
 namespace ssb {
 namespace gemmtc {
 
-constexpr int BM = 128, BN = 192, BK = 64, THREADS = 256, STAGES = 2;
-constexpr int LBO = 128, SBO = (BK / 8) * 128;            // 8 k-chunks of 16 B per 8-row group = 1024 B
+constexpr int BM = 128, BN = 192, BK = 32, THREADS = 256, STAGES = 2;   // 40 KB per stage -> 2 CTAs per SM
+constexpr int LBO = 128, SBO = (BK / 8) * 128;            // BK/8 k-chunks of 16 B per 8-row group
 constexpr int A_BYTES = (BM / 8) * SBO, B_BYTES = (BN / 8) * SBO;   // 16 KB, 24 KB
 constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;              // hi + lo of both = 80 KB
 constexpr int TMEM_COLS = 256;
@@ -27,14 +27,14 @@ struct Tail {
   uint32_t tmem_base;
 };
 
-// rows x 64 fp32 (global, row stride ld) -> bf16 hi (and lo) in the canonical no-swizzle K-major layout
+// rows x BK fp32 (global, row stride ld) -> bf16 hi (and lo) in the canonical no-swizzle K-major layout
 template <int ROWS, bool kSplit>
 __device__ __forceinline__ void stage_operand(const float* __restrict__ src, int64_t ld, int rows_valid, int k_valid,
                                               uint8_t* hi, uint8_t* lo, int tid) {
 #pragma unroll
-  for (int i = 0; i < ROWS * 8 / THREADS; ++i) {
+  for (int i = 0; i < ROWS * (BK / 8) / THREADS; ++i) {
     const int p = tid + i * THREADS;
-    const int r8 = p & 7, kc = (p >> 3) & 7, rg = p >> 6;
+    const int r8 = p & 7, kc = (p >> 3) & (BK / 8 - 1), rg = p / (8 * (BK / 8));
     const int row = rg * 8 + r8, k = kc * 8;
     float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
     if (row < rows_valid) {
@@ -60,7 +60,7 @@ __device__ __forceinline__ void stage_operand(const float* __restrict__ src, int
 }
 
 template <bool kSplit>
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void __launch_bounds__(THREADS, 2)
 gemm_tc_kernel(const float* __restrict__ A1, int64_t lda1, int K1, const float* __restrict__ A2, int64_t lda2, int K2,
                const float* __restrict__ W, int64_t ldw, const float* __restrict__ bias,
                float* __restrict__ C, int64_t ldc, int M, int N, int accumulate,
