@@ -173,8 +173,8 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="clips per GPU (default 4096 infer / 128 train)")
     ap.add_argument("--lengths", default="full", choices=["full", "uniform"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--precision", default="tc3", choices=["fp32", "tc3", "bf16"],
-                    help="fp32 = CUDA-core FMA; tc3 = tcgen05 split-bf16 x3 (fp32-parity grade); bf16 = tcgen05 single pass")
+    ap.add_argument("--precision", default="tc3", choices=["fp32", "tc3", "fp16"],
+                    help="fp32 = CUDA-core FMA; tc3 = tcgen05 split-fp16 (fp32-parity grade); fp16 = tcgen05 single pass")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
@@ -267,7 +267,7 @@ def main():
     # ---- dominant kernel (fused ROI CNN) timed alone for the roofline line
     from silent_speech_b200 import ops
     w = model.roi_cnn.tensors()
-    cnn_passes = {"fp32": 0, "tc3": 3, "bf16": 1}[args.precision]
+    cnn_passes = {"fp32": 0, "tc3": 3, "fp16": 1}[args.precision]
     for _ in range(2):
         ops.roi_cnn_fwd(R, L, w, passes=cnn_passes)
     torch.cuda.synchronize()
@@ -294,7 +294,7 @@ def main():
         line = {"metric": metric_name(args.workload), "value": value, "unit": "clips/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None,
-                "dtype": {"fp32": "f32", "tc3": "bf16x3 split operands, f32 accumulate (f32-parity grade); CNN f32", "bf16": "bf16 operands, f32 accumulate; CNN f32"}[args.precision],
+                "dtype": {"fp32": "f32", "tc3": "f16 hi/lo split operands, f32 accumulate (f32-parity grade)", "fp16": "f16 operands, f32 accumulate"}[args.precision],
                 "data": "synthetic",
                 "config": workload_config(args.workload, B) | {"precision": args.precision} | {"lengths": "all=T" if args.lengths == "full" else "uniform[6,T]"},
                 "clocks": clk.summary(),

@@ -49,14 +49,14 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
     if R is not None:
         R = R.to(dev).contiguous()
         emb = ops.roi_cnn_fwd(R, lengths, model.roi_cnn.tensors(), standardize=model.standardize_roi,
-                              passes={"fp32": 0, "tc3": 3, "bf16": 1}[getattr(model, "precision", "fp32")])
+                              passes={"fp32": 0, "tc3": 3, "fp16": 1}[getattr(model, "precision", "fp32")])
         ctx["R"] = R
         ctx["emb"] = emb
     gi = torch.empty(B, T, 2 * G3, device=dev, dtype=torch.float32)
     gi2d = gi.view(B * T, 2 * G3)
     p0, p1 = model.gru.layer(0), model.gru.layer(1)
     prec = getattr(model, "precision", "fp32")
-    passes = {"fp32": 0, "tc3": 3, "bf16": 1}[prec]
+    passes = {"fp32": 0, "tc3": 3, "fp16": 1}[prec]
     order = None
     if passes and B > 128:      # homogeneous 128-clip tiles: each cluster runs max(len in tile) steps
         order = torch.argsort(lengths, descending=True).to(torch.int32)

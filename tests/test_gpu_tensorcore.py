@@ -27,7 +27,7 @@ def test_gemm_tc_vs_fp64(M, N, K1, K2):
     b = torch.randn(N, generator=g)
     A = A1 if A2 is None else torch.cat([A1, A2], 1)
     ref = A.double() @ W.double().T + b.double()
-    for passes, tol in ((3, 2e-5), (1, 2e-2)):
+    for passes, tol in ((3, 2e-5), (1, 3e-3)):
         C = torch.full((M, N + 8), -7.0, device=dev)
         ops.gemm_tc(A1.to(dev), W.to(dev), b.to(dev), C, A2=None if A2 is None else A2.to(dev), passes=passes, c_col0=8)
         e = rel_err(C[:, 8:], ref)
@@ -63,7 +63,7 @@ def test_gru_tc_recurrence_vs_fp32_kernel(B, T):
     gi_f = (gi + fold).contiguous()
     order = torch.argsort(Ld, descending=True).to(torch.int32)
     mask = (torch.arange(T)[None, :] < L[:, None]).to(dev)
-    for passes, tol in ((3, 2e-5), (1, 3e-2)):
+    for passes, tol in ((3, 2e-5), (1, 5e-3)):
         for od in (None, order):
             gates = torch.zeros(B, T, 2, 4, 192, device=dev)
             out = ops.gru_layer_fwd_tc(gi_f, Ld, *w, passes=passes, order=od, gates=gates)
@@ -75,11 +75,11 @@ def test_gru_tc_recurrence_vs_fp32_kernel(B, T):
             assert eg < tol * 5, (passes, eg)
 
 
-@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("tc3", 1e-4), ("bf16", 5e-2)])
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("tc3", 1e-4), ("fp16", 2e-3)])
 @pytest.mark.parametrize("use_roi,B,T,mode", [(True, 150, 90, "uniform"), (False, 260, 64, "uniform")])
 def test_model_logits_by_precision(precision, tol, use_roi, B, T, mode):
     """fp32 and tc3 (split-bf16 on the tensor cores) must meet the 1e-4 logits bar with identical argmax;
-    bf16 is the fast mode with its own stated tolerance (5e-2 of max |logit|) and >= 97 % argmax agreement."""
+    fp16 (single pass) is the fast mode with its own stated tolerance: 2e-3 of max |logit|, >= 99 % argmax agreement."""
     import os
     dev = _cuda()
     from oracle import ref_model
@@ -100,10 +100,10 @@ def test_model_logits_by_precision(precision, tol, use_roi, B, T, mode):
     agree = (logits.argmax(1).cpu() == ref.argmax(1)).float().mean().item()
     print(f"precision={precision} roi={use_roi} rel_err={e:.3e} argmax_agree={agree:.4f}")
     assert e < tol, e
-    assert agree == 1.0 if precision != "bf16" else agree >= 0.97
+    assert agree == 1.0 if precision != "fp16" else agree >= 0.99
 
 
-@pytest.mark.parametrize("passes,tol", [(3, 1e-4), (1, 3e-2)])
+@pytest.mark.parametrize("passes,tol", [(3, 1e-4), (1, 3e-3)])
 @pytest.mark.parametrize("standardize", [True, False])
 def test_roi_cnn_tc_vs_oracle(passes, tol, standardize):
     import numpy as np
