@@ -147,6 +147,12 @@ int ssb_roi_cnn_fwd_tc(const uint8_t* R, const int64_t* lengths, int64_t B, int6
                        int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
                        float* out, int64_t out_stride, int32_t passes, void* stream);
 
+/* K2 v2: all three convolutions on tcgen05; the 2x2 max-pools are folded into the GEMM's N dimension
+ * (one 4x4-patch GEMM per pooled layer), two frame slots per CTA.  Same arguments as ssb_roi_cnn_fwd_tc. */
+int ssb_roi_cnn_fwd_tc2(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
+                        int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
+                        float* out, int64_t out_stride, int32_t passes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

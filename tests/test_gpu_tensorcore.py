@@ -103,9 +103,10 @@ def test_model_logits_by_precision(precision, tol, use_roi, B, T, mode):
     assert agree == 1.0 if precision != "fp16" else agree >= 0.99
 
 
+@pytest.mark.parametrize("version", [1, 2])
 @pytest.mark.parametrize("passes,tol", [(3, 1e-4), (1, 3e-3)])
 @pytest.mark.parametrize("standardize", [True, False])
-def test_roi_cnn_tc_vs_oracle(passes, tol, standardize):
+def test_roi_cnn_tc_vs_oracle(passes, tol, standardize, version):
     import numpy as np
     dev = _cuda()
     from oracle import ref_model
@@ -115,16 +116,17 @@ def test_roi_cnn_tc_vs_oracle(passes, tol, standardize):
     L = np.array([9, 4, 1, 7, 9, 9, 2], np.int64)
     R = synth.rois(B, T, L, seed=3)
     R[0, 2] = 0
+    R[4, 3, 10, 20] = 255; R[4, 3, 0, 0] = 255; R[4, 3, 47, 95] = 0      # corners / outliers
     names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
              "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
     w = [p[n].to(dev).contiguous() for n in names]
     Rd, Ld = torch.from_numpy(R).to(dev), torch.from_numpy(L).to(dev)
-    emb = ops.roi_cnn_fwd(Rd, Ld, w, standardize=standardize, passes=passes)
+    emb = ops.roi_cnn_fwd(Rd, Ld, w, standardize=standardize, passes=passes, version=version)
     torch.cuda.synchronize()
     ref32 = ops.roi_cnn_fwd(Rd, Ld, w, standardize=standardize)
     ref = ref_model.roi_cnn(p, ref_model.roi_prepare(torch.from_numpy(R), standardize))
     mask = torch.arange(T)[None, :] < torch.from_numpy(L)[:, None]
     ref = ref * mask[..., None]
-    print(f"cnn passes={passes} std={standardize} vs oracle {rel_err(emb, ref):.3e} vs fp32 kernel {rel_err(emb, ref32):.3e}")
+    print(f"cnn v{version} passes={passes} std={standardize} vs oracle {rel_err(emb, ref):.3e} vs fp32 kernel {rel_err(emb, ref32):.3e}")
     assert rel_err(emb, ref) < tol
     assert torch.all(emb.cpu()[~mask] == 0)
