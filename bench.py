@@ -45,6 +45,18 @@ def load_peaks():
     return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor_sustained": 1400.0, "src": "fallback"}
 
 
+def ncu_traffic(precision, B, lengths):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed `ncu --set full`
+    capture of this same launch shape (profiles/roofline_traffic.json); None when no capture matches."""
+    path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if not os.path.exists(path):
+        return None
+    for e in json.load(open(path)):
+        if e["precision"] == precision and e["clips"] == B and e["lengths"] == lengths:
+            return {"bytes_per_launch": e["dram_bytes"], "algorithmic_bytes": e["algorithmic_bytes"], "source": e["source"]}
+    return None
+
+
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons sampled while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -173,6 +185,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="clips per GPU (default 4096 infer / 128 train)")
     ap.add_argument("--lengths", default="full", choices=["full", "uniform"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-chunk", type=int, default=512, help="clips per pipelined host->device chunk in the e2e arm")
     ap.add_argument("--precision", default="tc3", choices=["fp32", "tc3", "fp16"],
                     help="fp32 = CUDA-core FMA; tc3 = tcgen05 split-fp16 (fp32-parity grade); fp16 = tcgen05 single pass")
     args = ap.parse_args()
@@ -241,22 +254,27 @@ def main():
     ms = float(t.item())
     value = B * world * args.steps / (ms / 1e3)
 
-    # ---- end to end through the public API with host buffers (H2D + D2H inside the timed region)
+    # ---- end to end through the public API with host buffers (H2D + D2H inside the timed region).
+    # Inference: model.infer_host(X, lengths, R) -- pinned host batch in, host logits out; it overlaps the
+    # host->device copy of one 512-clip chunk with the compute of the previous one.  Train: Trainer.step on
+    # freshly copied tensors, loss read back.
+    h_out = torch.empty(B, NUM_CLASSES, dtype=torch.float32).pin_memory()
+
     def e2e_step():
-        Xd, Ld, Rd = hX.to(dev, non_blocking=True), hL.to(dev, non_blocking=True), hR.to(dev, non_blocking=True)
         if args.workload == "train":
+            Xd, Ld, Rd = hX.to(dev, non_blocking=True), hL.to(dev, non_blocking=True), hR.to(dev, non_blocking=True)
             return trainer.step(Xd, Ld, Rd, hy.to(dev, non_blocking=True)).cpu()
-        with torch.no_grad():
-            return model(Xd, Ld, Rd).cpu()
+        return model.infer_host(hX, hL, hR, chunk=args.e2e_chunk, out=h_out)
     e2e_step()
     barrier()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n_e2e = max(2, min(args.steps, 5))
-    e2.record()
-    for _ in range(n_e2e):
-        res = e2e_step()
-    e3.record()
-    barrier()
+    with ClockSampler(local) as clk2:
+        e2.record()
+        for _ in range(n_e2e):
+            res = e2e_step()
+        e3.record()
+        barrier()
     t = torch.tensor([e2.elapsed_time(e3)], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -280,11 +298,14 @@ def main():
     cnn_ms = k0.elapsed_time(k1) / 5
     achieved = CNN_FLOP_PER_FRAME * frames / (cnn_ms / 1e3) / 1e12
     roofline = {"kernel": "roi_cnn_tc_kernel" if cnn_passes else "roi_cnn_fwd_kernel", "bound": "tensor", "achieved": achieved, "peak": peaks["tensor_burst"],
-                "unit": "TFLOP/s", "frac": achieved / peaks["tensor_burst"], "traffic": None,
+                "unit": "TFLOP/s", "frac": achieved / peaks["tensor_burst"],
+                "traffic": ncu_traffic(args.precision, B, args.lengths),
                 "peak_src": f"{peaks['src']} bf16 burst", "ms_per_launch": cnn_ms,
                 "note": "K2 (fused ROI CNN), algorithmic 5,309,952 FLOP/frame; step-level: %.1f TFLOP/s over %.0f MFLOP/clip" % (
                     FWD_FLOP_PER_FRAME * frames * world * args.steps / (ms / 1e3) / 1e12, FWD_FLOP_PER_FRAME * T_FRAMES / 1e6)}
 
+    clk.rows += clk2.rows                   # clocks sampled over both timed regions (device-resident and e2e)
+    clocks = clk.summary()
     if rank == 0:
         cpu = None
         if not args.no_cpu_baseline:
@@ -297,7 +318,7 @@ def main():
                 "dtype": {"fp32": "f32", "tc3": "f16 hi/lo split operands, f32 accumulate (f32-parity grade)", "fp16": "f16 operands, f32 accumulate"}[args.precision],
                 "data": "synthetic",
                 "config": workload_config(args.workload, B) | {"precision": args.precision} | {"lengths": "all=T" if args.lengths == "full" else "uniform[6,T]"},
-                "clocks": clk.summary(),
+                "clocks": clocks,
                 "e2e": {"value": e2e_val, "unit": "clips/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)

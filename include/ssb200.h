@@ -153,6 +153,13 @@ int ssb_roi_cnn_fwd_tc2(const uint8_t* R, const int64_t* lengths, int64_t B, int
                         int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
                         float* out, int64_t out_stride, int32_t passes, void* stream);
 
+/* K2 v3 (the default): v2's formulation re-organised for latency hiding -- passes = 1: four 128-thread frame
+ * slots per CTA with one MMA issuer each; frames handed out by an atomic counter; next frame prefetched;
+ * conv2 tiles committed one by one.  Same arguments as ssb_roi_cnn_fwd_tc. */
+int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
+                        int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
+                        float* out, int64_t out_stride, int32_t passes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -31,3 +31,30 @@ extern "C" int ssb_device_info(int32_t* sm_count, int32_t* cc_major, int32_t* cc
   }
   return SSB_OK;
 }
+
+// Per-device ring of launch counters (see common.cuh).
+#include <atomic>
+extern "C" int ssb_scratch_counter_(cudaStream_t stream, unsigned int** counter) {
+  constexpr int kMaxDev = 64, kRing = 1024;
+  static unsigned int* ring[kMaxDev] = {};
+  static std::atomic<unsigned int> next[kMaxDev];
+  static std::atomic_flag lock = ATOMIC_FLAG_INIT;
+  int dev = 0;
+  SSB_CUDA(cudaGetDevice(&dev));
+  SSB_REQUIRE(dev >= 0 && dev < kMaxDev, "device index out of range");
+  if (!ring[dev]) {
+    while (lock.test_and_set(std::memory_order_acquire)) {}
+    cudaError_t e = cudaSuccess;
+    if (!ring[dev]) {
+      unsigned int* p = nullptr;
+      e = cudaMalloc(&p, kRing * sizeof(unsigned int));
+      if (e == cudaSuccess) ring[dev] = p;
+    }
+    lock.clear(std::memory_order_release);
+    SSB_CUDA(e);
+  }
+  unsigned int* c = ring[dev] + next[dev].fetch_add(1) % kRing;
+  SSB_CUDA(cudaMemsetAsync(c, 0, sizeof(unsigned int), stream));
+  *counter = c;
+  return SSB_OK;
+}

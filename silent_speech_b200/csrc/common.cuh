@@ -76,3 +76,9 @@ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx, float 
 inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
 }  // namespace ssb
+
+// A zeroed 32-bit device counter for one kernel launch on `stream` (dynamic work hand-out of persistent
+// kernels).  The only device memory the library owns: one 4 KB ring of counters per device, allocated on first
+// use and never freed; consecutive launches rotate through the ring, so launches on different streams do not
+// share a counter.  Returns SSB_OK or an error code.
+extern "C" int ssb_scratch_counter_(cudaStream_t stream, unsigned int** counter);

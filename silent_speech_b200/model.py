@@ -147,6 +147,59 @@ class BiGRUClassifier(nn.Module):
         return F_ssb.classifier_forward(self, X, lengths, R if self.use_roi else None)
 
     @torch.no_grad()
+    def infer_host(self, X: torch.Tensor, lengths: torch.Tensor, R: Optional[torch.Tensor] = None,
+                   chunk: int = 512, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``model(X, lengths, R)`` for HOST tensors (what collate_fn, train_model_official.py:174-204, yields):
+        the batch is cut into chunks of ``chunk`` clips (clips are independent), each chunk's host->device copy
+        runs on a copy stream while the previous chunk computes, and the logits come back into a host tensor.
+        Pinned inputs give true overlap; pageable ones still work (the copies then serialise).  Returns f32 [B,C]
+        on the host.  The PCIe copy of R (414,720 B/clip) is the floor of this call."""
+        dev = next(self.parameters()).device
+        if dev.type != "cuda":
+            raise F_ssb.ops._lib.SsbError("infer_host needs the model on a CUDA device (no CPU path)")
+        B = X.shape[0]
+        use_roi = self.use_roi and R is not None
+        if out is None:
+            out = torch.empty(B, self.num_classes, dtype=torch.float32).pin_memory()
+        main = torch.cuda.current_stream(dev)
+        st = self.__dict__.setdefault("_h2d_state", {})
+        if st.get("dev") != dev:
+            st.clear()
+            st.update(dev=dev, copy=torch.cuda.Stream(dev), bufs={})
+        copy = st["copy"]
+        key = (chunk, tuple(X.shape[1:]), tuple(R.shape[1:]) if use_roi else None)
+        if key not in st["bufs"]:
+            st["bufs"].clear()
+            st["bufs"][key] = [dict(X=torch.empty((chunk,) + tuple(X.shape[1:]), device=dev, dtype=torch.float32),
+                                    L=torch.empty(chunk, device=dev, dtype=torch.int64),
+                                    R=torch.empty((chunk,) + tuple(R.shape[1:]), device=dev, dtype=torch.uint8) if use_roi else None,
+                                    ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
+        bufs = st["bufs"][key]
+        was_training = self.training
+        self.eval()
+        copy.wait_stream(main)
+        for i, lo in enumerate(range(0, B, chunk)):
+            hi = min(B, lo + chunk)
+            n = hi - lo
+            b = bufs[i & 1]
+            with torch.cuda.stream(copy):
+                if i >= 2:
+                    copy.wait_event(b["free"])             # the compute that read this buffer two chunks ago is done
+                b["X"][:n].copy_(X[lo:hi], non_blocking=True)
+                b["L"][:n].copy_(lengths[lo:hi], non_blocking=True)
+                if use_roi:
+                    b["R"][:n].copy_(R[lo:hi], non_blocking=True)
+                b["ready"].record(copy)
+            main.wait_event(b["ready"])
+            logits = F_ssb.classifier_forward(self, b["X"][:n], b["L"][:n], b["R"][:n] if use_roi else None)
+            out[lo:hi].copy_(logits, non_blocking=True)
+            b["free"].record(main)
+        if was_training:
+            self.train()
+        main.synchronize()
+        return out
+
+    @torch.no_grad()
     def predict_topk(self, X, lengths, R=None, k: int = 3):
         """softmax + top-k fused into the head kernel (live_infer_official.py:223-226)."""
         return F_ssb.classifier_forward(self, X, lengths, R if self.use_roi else None, k_top=k)

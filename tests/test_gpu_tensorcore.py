@@ -103,7 +103,7 @@ def test_model_logits_by_precision(precision, tol, use_roi, B, T, mode):
     assert agree == 1.0 if precision != "fp16" else agree >= 0.99
 
 
-@pytest.mark.parametrize("version", [1, 2])
+@pytest.mark.parametrize("version", [1, 2, 3])
 @pytest.mark.parametrize("passes,tol", [(3, 1e-4), (1, 3e-3)])
 @pytest.mark.parametrize("standardize", [True, False])
 def test_roi_cnn_tc_vs_oracle(passes, tol, standardize, version):
@@ -130,3 +130,28 @@ def test_roi_cnn_tc_vs_oracle(passes, tol, standardize, version):
     print(f"cnn v{version} passes={passes} std={standardize} vs oracle {rel_err(emb, ref):.3e} vs fp32 kernel {rel_err(emb, ref32):.3e}")
     assert rel_err(emb, ref) < tol
     assert torch.all(emb.cpu()[~mask] == 0)
+
+
+@pytest.mark.parametrize("passes,tol", [(3, 1e-4), (1, 3e-3)])
+def test_roi_cnn_tc3_many_frames_dynamic_handout(passes, tol):
+    """More frames than resident slots, ragged lengths: exercises the atomic frame hand-out, the register
+    prefetch across padded frames and slot re-use; checked against the fp32 CUDA-core kernel, and repeated
+    launches must be bit-identical (no race in the hand-out)."""
+    dev = _cuda()
+    from oracle import ref_model
+    from silent_speech_b200 import ops, synth
+    p = ref_model.synth_params(13)
+    B, T = 96, 90
+    d = synth.clip_batch(B, T, mode="uniform", seed=4)
+    names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
+             "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
+    w = [p[n].to(dev).contiguous() for n in names]
+    Rd, Ld = torch.from_numpy(d["R"]).to(dev), torch.from_numpy(d["lengths"]).to(dev)
+    ref32 = ops.roi_cnn_fwd(Rd, Ld, w, passes=0)
+    a = ops.roi_cnn_fwd(Rd, Ld, w, passes=passes, version=3)
+    b = ops.roi_cnn_fwd(Rd, Ld, w, passes=passes, version=3)
+    torch.cuda.synchronize()
+    assert torch.equal(a, b)
+    assert rel_err(a, ref32) < tol
+    mask = (torch.arange(T)[None, :] < torch.from_numpy(d["lengths"])[:, None])
+    assert torch.all(a.cpu()[~mask] == 0)
