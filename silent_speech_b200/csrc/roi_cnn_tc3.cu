@@ -178,11 +178,20 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16);
 
   // ---- per-thread addressing, hoisted out of the frame loop
-  uint32_t pixoff[WPT];                                // byte offset of word j's first pixel in the padded frame plane
+  // 4-pixel words of the frame per thread.  ST == 128: every warp owns 12 whole rows (288 words = 9 x 32), so the
+  // left neighbour of a word is the previous lane (or lane 31 of the previous iteration) and each thread can
+  // store ONE aligned 8-byte group [left neighbour's last pixel, a, b, c] -- the 1-pixel border shift of the
+  // padded plane costs a shuffle instead of three misaligned stores.
+  constexpr bool kRowWarp = (ST == 128);
+  auto word_of = [&](int j) { return kRowWarp ? 288 * warp + 32 * j + lane : tid + j * ST; };
+  uint32_t pixoff[WPT];                                // byte offset of word j's store in the padded frame plane
+  uint32_t rowend = 0, rowstart = 0;                   // bit j: word j is the last / first of its row
 #pragma unroll
   for (int j = 0; j < WPT; ++j) {
-    const int word = tid + j * ST, y = word / (W0 / 4), x = (word % (W0 / 4)) * 4;
-    pixoff[j] = ((y + 1) * PIX_LD + x + 1) * 2;
+    const int word = word_of(j), y = word / (W0 / 4), x = (word % (W0 / 4)) * 4;
+    pixoff[j] = ((y + 1) * PIX_LD + x + (kRowWarp ? 0 : 1)) * 2;
+    if (word % (W0 / 4) == W0 / 4 - 1) rowend |= 1u << j;
+    if (word % (W0 / 4) == 0) rowstart |= 1u << j;
   }
   uint32_t gsrc[GIT], gdst[GIT];                       // conv1 patch gather of round 0 (rounds advance by 8 pooled rows)
 #pragma unroll
@@ -215,7 +224,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     if (live) {
 #pragma unroll
       for (int j = 0; j < WPT; ++j) {
-        const int word = tid + j * ST;
+        const int word = word_of(j);
         wv[j] = word < NPIX / 4 ? __ldg(reinterpret_cast<const uint32_t*>(R + fr * NPIX) + word) : 0u;
       }
     }
@@ -253,8 +262,10 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         for (int p = 0; p < L::P; ++p) {
           uint32_t* pw = reinterpret_cast<uint32_t*>(r0 + p * PIX_BYTES);
           pw[tid] = 0; pw[(PIX_ROWS - 1) * (PIX_LD / 2) + tid] = 0;                 // rows 0 and 49
-          uint16_t* ph = reinterpret_cast<uint16_t*>(r0 + p * PIX_BYTES);
-          ph[tid * PIX_LD] = 0; ph[tid * PIX_LD + W0 + 1] = 0;                      // columns 0 and 97
+          if (!kRowWarp) {
+            uint16_t* ph = reinterpret_cast<uint16_t*>(r0 + p * PIX_BYTES);
+            ph[tid * PIX_LD] = 0; ph[tid * PIX_LD + W0 + 1] = 0;                    // columns 0 and 97
+          }
         }
       }
       slot_sync<ST>(slot);
@@ -268,24 +279,42 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         mean_u = (float)(S1 / (double)NPIX);
         inv_s = (float)(1.0 / fmax(sqrt(var_u), 255.0e-6));
       }
+      uint32_t carry_hi = 0, carry_lo = 0;             // lane 31's last pixel of the previous iteration (kRowWarp)
 #pragma unroll
       for (int j = 0; j < WPT; ++j) {
-        if (WPT * ST == NPIX / 4 || tid + j * ST < NPIX / 4) {
+        if (WPT * ST == NPIX / 4 || word_of(j) < NPIX / 4) {
           float hi[4], lo[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            tc::split_bf16(((float)((wv[j] >> (8 * k)) & 0xffu) - mean_u) * inv_s, hi[k], lo[k]);
+            hi[k] = ((float)((wv[j] >> (8 * k)) & 0xffu) - mean_u) * inv_s;
+            if (kSplit) tc::split_bf16(hi[k], hi[k], lo[k]);
           }
-          uint8_t* d = r0 + pixoff[j];                                  // column x+1 is odd: a | (b,c) | d
-          const uint32_t ad = tc::pack_bf16(hi[0], hi[3]);
-          *reinterpret_cast<uint16_t*>(d) = (uint16_t)(ad & 0xffffu);
-          *reinterpret_cast<uint32_t*>(d + 2) = tc::pack_bf16(hi[1], hi[2]);
-          *reinterpret_cast<uint16_t*>(d + 6) = (uint16_t)(ad >> 16);
-          if (kSplit) {
-            const uint32_t al = tc::pack_bf16(lo[0], lo[3]);
-            *reinterpret_cast<uint16_t*>(d + PIX_BYTES) = (uint16_t)(al & 0xffffu);
-            *reinterpret_cast<uint32_t*>(d + PIX_BYTES + 2) = tc::pack_bf16(lo[1], lo[2]);
-            *reinterpret_cast<uint16_t*>(d + PIX_BYTES + 6) = (uint16_t)(al >> 16);
+          uint8_t* d = r0 + pixoff[j];
+          if (kRowWarp) {
+            // [left neighbour's d | a] [b | c] as one 8-byte store; the row's last word also stores [d | 0]
+#pragma unroll
+            for (int p = 0; p < L::P; ++p) {
+              const float* v = p ? lo : hi;
+              uint32_t& carry = p ? carry_lo : carry_hi;
+              const uint32_t ad = tc::pack_bf16(v[0], v[3]);                       // a low half, d high half
+              uint32_t left = __shfl_up_sync(0xffffffffu, ad, 1);
+              if (lane == 0) left = carry;
+              if ((rowstart >> j) & 1u) left = 0u;                                 // column 0 of the padded plane
+              carry = __shfl_sync(0xffffffffu, ad, 31);
+              *reinterpret_cast<uint2*>(d + p * PIX_BYTES) = make_uint2(__byte_perm(left, ad, 0x5432), tc::pack_bf16(v[1], v[2]));
+              if ((rowend >> j) & 1u) *reinterpret_cast<uint32_t*>(d + p * PIX_BYTES + 8) = ad >> 16;   // [d | column 97 = 0]
+            }
+          } else {
+            const uint32_t ad = tc::pack_bf16(hi[0], hi[3]);                        // column x+1 is odd: a | (b,c) | d
+            *reinterpret_cast<uint16_t*>(d) = (uint16_t)(ad & 0xffffu);
+            *reinterpret_cast<uint32_t*>(d + 2) = tc::pack_bf16(hi[1], hi[2]);
+            *reinterpret_cast<uint16_t*>(d + 6) = (uint16_t)(ad >> 16);
+            if (kSplit) {
+              const uint32_t al = tc::pack_bf16(lo[0], lo[3]);
+              *reinterpret_cast<uint16_t*>(d + PIX_BYTES) = (uint16_t)(al & 0xffffu);
+              *reinterpret_cast<uint32_t*>(d + PIX_BYTES + 2) = tc::pack_bf16(lo[1], lo[2]);
+              *reinterpret_cast<uint16_t*>(d + PIX_BYTES + 6) = (uint16_t)(al >> 16);
+            }
           }
         }
       }
@@ -361,7 +390,8 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 #pragma unroll
           for (int co = 0; co < 8; ++co) {
             const float m4 = fmaxf(fmaxf(v[co], v[8 + co]), fmaxf(v[16 + co], v[24 + co]));
-            tc::split_bf16(fmaxf(m4 + sh.b1[co], 0.f), hi[co], lo[co]);
+            hi[co] = fmaxf(m4 + sh.b1[co], 0.f);
+            if (kSplit) tc::split_bf16(hi[co], hi[co], lo[co]);          // single pass: pack8 rounds once
           }
           uint32_t off;
           if (9 % L::STRIP_TILES == 0) {
@@ -413,7 +443,8 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 #pragma unroll
         for (int co = 0; co < 16; ++co) {
           const float m4 = fmaxf(fmaxf(v[co], v[16 + co]), fmaxf(w[co], w[16 + co]));
-          tc::split_bf16(fmaxf(m4 + sh.b2[co], 0.f), hi[co], lo[co]);
+          hi[co] = fmaxf(m4 + sh.b2[co], 0.f);
+          if (kSplit) tc::split_bf16(hi[co], hi[co], lo[co]);
         }
         const uint32_t off = (uint32_t)a2off[tl];
         *reinterpret_cast<uint4*>(r0 + off) = pack8(hi);
@@ -484,6 +515,9 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1;
     tc::fence_after_sync();
     if (q < 3) {
+      float acc[C3P];
+#pragma unroll
+      for (int c = 0; c < C3P; ++c) acc[c] = 0.f;
 #pragma unroll 1
       for (int tx = wg; tx < 3; tx += NWG) {
         float v[32];
@@ -498,25 +532,26 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           tc::tmem_ld_wait();
         }
 #pragma unroll
-        for (int c = 0; c < C3P; ++c) v[c] = c < C3 ? fmaxf(v[c] + sh.b3[c], 0.f) : 0.f;
-#pragma unroll
-        for (int off = 16, n = 16; off >= 1; off >>= 1, n >>= 1) {
-          const bool up = (lane & off) != 0;
-#pragma unroll
-          for (int i = 0; i < n; ++i) {
-            const float send = up ? v[i] : v[i + n], keep = up ? v[i + n] : v[i];
-            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-          }
-        }
-        mz.part[tx * 3 + q][lane] = v[0];            // lane c holds channel c's sum over this warp's 32 pixels
+        for (int c = 0; c < C3; ++c) acc[c] += fmaxf(v[c] + sh.b3[c], 0.f);
       }
+      // one transposing reduction per warp: lane c ends with channel c's sum over the warp's pixels
+#pragma unroll
+      for (int off = 16, n = 16; off >= 1; off >>= 1, n >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < n; ++i) {
+          const float send = up ? acc[i] : acc[i + n], keep = up ? acc[i + n] : acc[i];
+          acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+      }
+      mz.part[wg * 3 + q][lane] = acc[0];
     }
     tc::fence_before_sync();
     slot_sync<ST>(slot);
     if (tid < E) {                                      // warp 0: deterministic channel means, then the 24 -> 32 fc
       float cs = 0.f;
 #pragma unroll
-      for (int i = 0; i < 9; ++i) cs += mz.part[i][lane];
+      for (int i = 0; i < 3 * NWG; ++i) cs += mz.part[i][lane];
       cs *= 1.0f / (float)(H2 * W2);
       float a = sh.bfc[tid];
 #pragma unroll
