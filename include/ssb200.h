@@ -160,6 +160,18 @@ int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int64_t B, int
                         int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
                         float* out, int64_t out_stride, int32_t passes, void* stream);
 
+/* K3a v2 (fp16 single-pass mode): the input projections of BOTH directions as one persistent GEMM,
+ * C[M, N] = [A1 | A2] . [W_a ; W_b]^T + bias (nn.GRU's x W_ih^T + b_ih, train_model_official.py:261-267, forward and
+ * reverse direction stacked: N = 2 x 576).  ssb_proj_prepack converts the weights once into fp16 blocks that the GEMM
+ * streams with bulk async copies (a derived cache of the state-dict tensors; rebuild when they change);
+ * `packed` is caller-owned, ssb_proj_packed_bytes(N, K1, K2) bytes.  Rows of padded frames are not written. */
+int64_t ssb_proj_packed_bytes(int64_t N, int64_t K1, int64_t K2);
+int ssb_proj_prepack(const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int64_t K1, int64_t K2,
+                     void* packed, void* stream);
+int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                  const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
+                  const int64_t* lengths, int64_t T, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,273 @@
+// K3a v2 -- GRU input projection for BOTH directions as one persistent tcgen05 GEMM (fp16 single-pass mode).
+//
+//   C[M, N] = [A1 | A2] (M x (K1+K2), fp32) . [W_fwd ; W_rev] (N x (K1+K2), fp32)^T + bias     N = 2 x 576 = 1152
+//   (nn.GRU's x W_ih^T + b_ih of train_model_official.py:261-267 for the forward and reverse direction at once;
+//   the concat of train:297 is two K segments of A)
+//
+// The output (M x 1152 fp32, 1.7 GB at 4096 clips) makes this an HBM-write-bound kernel; the design keeps
+// everything else off the critical path:
+//   * the weights are packed ONCE per call (ssb_proj_prepack) into fp16 blocks of 128 rows x 64 k in the
+//     canonical no-swizzle K-major UMMA layout, so a weight block is ONE 16 KB bulk async copy (TMA, 1-D)
+//     straight into its shared-memory stage -- no register staging, no conversion in the main loop;
+//   * a persistent CTA owns a 128-row tile of A: it is read from HBM once, converted to fp16 once and stays
+//     resident in shared memory while the CTA sweeps all nine 128-column tiles of N;
+//   * warp roles: warps 0-3 epilogue (one TMEM lane quarter each), warp 4 weight producer, warp 5 MMA issuer;
+//     6-stage weight ring and two 128-column TMEM accumulators, so the epilogue (TMEM -> +bias -> global)
+//     of tile n overlaps the MMAs of tile n+1.
+// K is laid out as [A1 padded to 8 | A2 padded to 8 | zeros to a multiple of 64] on both operands.
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace ssb {
+namespace gemm2 {
+
+constexpr int BM = 128, BN = 128, KB = 64;
+constexpr int CHUNK = 2048;                              // one k-chunk (8 k) of 128 rows: 16 groups x 128 B
+constexpr int W_BLOCK = (KB / 8) * CHUNK;                // 16,384 B
+constexpr int STAGES = 6;
+constexpr int EPI_WARPS = 4, THREADS = (EPI_WARPS + 2) * 32;
+constexpr int TMEM_COLS = 256;
+constexpr int MAX_KP = 384, MAX_N = 1152;
+
+struct Ctl {
+  uint64_t full[STAGES], empty[STAGES], accfull[2], accempty[2];
+  uint32_t tmem_base;
+};
+
+__host__ __device__ constexpr int round_up(int x, int m) { return (x + m - 1) / m * m; }
+__host__ __device__ constexpr int kp_of(int K1, int K2) { return round_up(round_up(K1, 8) + round_up(K2, 8), KB); }
+
+// packed[(nt * nkb + kb) * W_BLOCK + (k/8) * CHUNK + (r/8) * 128 + (r%8) * 16 + (k%8) * 2]  for row nt*128 + r, column kb*64 + k
+__global__ void prepack_kernel(const float* __restrict__ Wa, const float* __restrict__ Wb, int64_t ldw, int n_each,
+                               int K1, int K2, int N, uint8_t* __restrict__ packed) {
+  const int K1p = round_up(K1, 8), Kp = kp_of(K1, K2), nkb = Kp / KB;
+  const int items = round_up(N, BN) * (Kp / 8);          // one item = 8 consecutive k of one row
+  for (int it = blockIdx.x * blockDim.x + threadIdx.x; it < items; it += gridDim.x * blockDim.x) {
+    const int n = it / (Kp / 8), c = it % (Kp / 8);
+    float x[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int kk = c * 8 + j;
+      int col = -1;
+      if (kk < K1p) { if (kk < K1) col = kk; }
+      else if (kk - K1p < K2) col = K1 + (kk - K1p);
+      float v = 0.f;
+      if (n < N && col >= 0) v = n < n_each ? Wa[(int64_t)n * ldw + col] : Wb[(int64_t)(n - n_each) * ldw + col];
+      x[j] = v;
+    }
+    const int nt = n / BN, r = n % BN, kb = c / (KB / 8), kc = c % (KB / 8);
+    uint8_t* dst = packed + ((size_t)(nt * nkb + kb)) * W_BLOCK + kc * CHUNK + (r >> 3) * 128 + (r & 7) * 16;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(tc::pack_bf16(x[0], x[1]), tc::pack_bf16(x[2], x[3]),
+                                                tc::pack_bf16(x[4], x[5]), tc::pack_bf16(x[6], x[7]));
+  }
+}
+
+struct Args {
+  const float* A1; int64_t lda1; int K1;
+  const float* A2; int64_t lda2; int K2;
+  const uint8_t* Wp; const float* bias;
+  float* C; int64_t ldc;
+  int M, N;
+  const int64_t* lengths; int T;
+};
+
+__global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int K1p = round_up(a.K1, 8), Kp = kp_of(a.K1, a.K2), nkb = Kp / KB, nnt = (a.N + BN - 1) / BN;
+  uint8_t* a_s = smem;                                       // Kp/8 chunks x 2048 B
+  uint8_t* w_s = a_s + (Kp / 8) * CHUNK;                     // STAGES x 16 KB
+  float* tile_s = reinterpret_cast<float*>(w_s + STAGES * W_BLOCK);        // 4 x 32 x 33 floats
+  float* bias_s = tile_s + EPI_WARPS * 32 * 33;              // nnt * 128 floats
+  uint8_t* live_s = reinterpret_cast<uint8_t*>(bias_s + nnt * BN);         // 128 bytes
+  Ctl& ctl = *reinterpret_cast<Ctl*>(live_s + BM);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  for (int i = tid; i < nnt * BN; i += THREADS) bias_s[i] = (a.bias && i < a.N) ? a.bias[i] : 0.f;
+  if (warp == 0) tc::tmem_alloc<TMEM_COLS>(&ctl.tmem_base);
+  if (tid == 32) {
+    for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&ctl.full[s], 1); tc::mbar_init(&ctl.empty[s], 1); }
+    for (int b = 0; b < 2; ++b) { tc::mbar_init(&ctl.accfull[b], 1); tc::mbar_init(&ctl.accempty[b], EPI_WARPS); }
+    tc::mbar_fence_init();
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = ctl.tmem_base;
+  const uint32_t a_u = tc::smem_u32(a_s), w_u = tc::smem_u32(w_s);
+  constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN);
+  uint32_t w_it = 0, acc_it = 0;                             // running weight-block / accumulator counters (ring phases)
+
+  const int m_tiles = (a.M + BM - 1) / BM;
+  for (int mt = blockIdx.x; mt < m_tiles; mt += gridDim.x) {
+    const int m0 = mt * BM;
+    // ---- tile liveness: a tile made only of padded frames (t >= lengths[b]) is never read downstream
+    int live = 0;
+    if (tid < BM) {
+      const int m = m0 + tid;
+      live = m < a.M && (!a.lengths || (m % a.T) < (int)a.lengths[m / a.T]);
+      live_s[tid] = (uint8_t)live;
+    }
+    if (!__syncthreads_or(live)) continue;                  // also: every MMA of the previous tile has completed
+    // ---- A tile: fp32 global -> fp16 canonical K-major, once per tile.  A warp covers 8 rows x 4 chunks per pass:
+    // 128 B contiguous per row from global, conflict-free 16-byte stores.
+    {
+      const int items = BM * (Kp / 8);
+#pragma unroll 4
+      for (int idx = tid; idx < items; idx += THREADS) {
+        const int r8 = idx & 7, c4 = (idx >> 3) & 3, rest = idx >> 5, rg = rest & 15, cg = rest >> 4;
+        const int row = rg * 8 + r8, chunk = cg * 4 + c4, kk = chunk * 8;
+        float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+        if (m0 + row < a.M) {
+          if (kk < K1p) {
+            const float* g = a.A1 + (int64_t)(m0 + row) * a.lda1 + kk;
+            if (kk < a.K1) v0 = __ldg(reinterpret_cast<const float4*>(g));
+            if (kk + 4 < a.K1) v1 = __ldg(reinterpret_cast<const float4*>(g + 4));
+          } else if (kk - K1p < a.K2) {
+            const int k2 = kk - K1p;
+            const float* g = a.A2 + (int64_t)(m0 + row) * a.lda2 + k2;
+            v0 = __ldg(reinterpret_cast<const float4*>(g));
+            if (k2 + 4 < a.K2) v1 = __ldg(reinterpret_cast<const float4*>(g + 4));
+          }
+        }
+        *reinterpret_cast<uint4*>(a_s + chunk * CHUNK + rg * 128 + r8 * 16) =
+            make_uint4(tc::pack_bf16(v0.x, v0.y), tc::pack_bf16(v0.z, v0.w), tc::pack_bf16(v1.x, v1.y), tc::pack_bf16(v1.z, v1.w));
+      }
+    }
+    tc::fence_async_smem();
+    __syncthreads();
+
+    if (warp == EPI_WARPS) {
+      // =============================== weight producer ===============================
+      if (lane == 0) {
+        for (int nt = 0; nt < nnt; ++nt)
+          for (int kb = 0; kb < nkb; ++kb, ++w_it) {
+            const uint32_t s = w_it % STAGES, ph = (w_it / STAGES) & 1;
+            tc::mbar_wait_bounded(&ctl.empty[s], ph ^ 1);
+            tc::mbar_arrive_expect_tx(&ctl.full[s], W_BLOCK);
+            tc::bulk_copy_g2s(w_u + s * W_BLOCK, a.Wp + (size_t)(nt * nkb + kb) * W_BLOCK, W_BLOCK, &ctl.full[s]);
+          }
+      } else {
+        w_it += nnt * nkb;
+      }
+      w_it = __shfl_sync(0xffffffffu, w_it, 0);
+    } else if (warp == EPI_WARPS + 1) {
+      // =============================== MMA issuer ===============================
+      if (lane == 0) {
+        for (int nt = 0; nt < nnt; ++nt, ++acc_it) {
+          const uint32_t buf = acc_it & 1;
+          tc::mbar_wait_bounded(&ctl.accempty[buf], ((acc_it >> 1) & 1) ^ 1);
+          tc::fence_after_sync();
+          for (int kb = 0; kb < nkb; ++kb, ++w_it) {
+            const uint32_t s = w_it % STAGES, ph = (w_it / STAGES) & 1;
+            tc::mbar_wait_bounded(&ctl.full[s], ph);
+            tc::fence_after_sync();
+#pragma unroll
+            for (int j = 0; j < KB / 16; ++j) {
+              const uint64_t da = tc::make_desc(a_u + (kb * (KB / 8) + 2 * j) * CHUNK, CHUNK, 128);
+              const uint64_t db = tc::make_desc(w_u + s * W_BLOCK + 2 * j * CHUNK, CHUNK, 128);
+              tc::mma_bf16(tmem + buf * BN, da, db, idesc, (kb | j) != 0);
+            }
+            tc::mma_commit(&ctl.empty[s]);
+          }
+          tc::mma_commit(&ctl.accfull[buf]);
+        }
+      } else {
+        w_it += nnt * nkb; acc_it += nnt;
+      }
+      w_it = __shfl_sync(0xffffffffu, w_it, 0);
+      acc_it = __shfl_sync(0xffffffffu, acc_it, 0);
+    } else {
+      // =============================== epilogue warps ===============================
+      float* tile = tile_s + warp * (32 * 33);
+      const int row0 = m0 + warp * 32;
+      const uint32_t tlane = tmem + ((uint32_t)(warp * 32) << 16);
+      for (int nt = 0; nt < nnt; ++nt, ++acc_it) {
+        const uint32_t buf = acc_it & 1;
+        tc::mbar_wait_bounded(&ctl.accfull[buf], (acc_it >> 1) & 1);
+        tc::fence_after_sync();
+#pragma unroll 1
+        for (int cg = 0; cg < BN / 32; ++cg) {
+          float v[32];
+          tc::tmem_ld32(tlane + buf * BN + cg * 32, v);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 32; ++q) tile[lane * 33 + q] = v[q];
+          __syncwarp();
+          const int n = nt * BN + cg * 32 + lane;
+          if (n < a.N) {
+            const float bv = bias_s[n];
+            float* c = a.C + (int64_t)row0 * a.ldc + n;
+#pragma unroll 8
+            for (int r = 0; r < 32; ++r)
+              if (live_s[warp * 32 + r]) c[(int64_t)r * a.ldc] = tile[r * 33 + lane] + bv;
+          }
+          __syncwarp();
+        }
+        tc::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&ctl.accempty[buf]);
+      }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc<TMEM_COLS>(tmem);
+}
+
+inline size_t smem_bytes(int Kp, int nnt) {
+  return (size_t)(Kp / 8) * CHUNK + STAGES * W_BLOCK + EPI_WARPS * 32 * 33 * 4 + (size_t)nnt * BN * 4 + BM + sizeof(Ctl);
+}
+
+}  // namespace gemm2
+}  // namespace ssb
+
+// Bytes of the packed-weight workspace ssb_proj_prepack writes (caller-owned device memory).
+extern "C" int64_t ssb_proj_packed_bytes(int64_t N, int64_t K1, int64_t K2) {
+  using namespace ssb::gemm2;
+  return (int64_t)round_up((int)N, BN) * kp_of((int)K1, (int)K2) * 2;
+}
+
+// Packs [W_a ; W_b] (n_each rows each, row stride ldw, K1+K2 columns; W_b may be NULL with N = n_each) into the
+// fp16 block layout ssb_proj_gemm streams.  A derived cache of the state-dict tensors: rebuild after they change.
+extern "C" int ssb_proj_prepack(const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int64_t K1, int64_t K2,
+                                void* packed, void* stream) {
+  using namespace ssb;
+  using namespace ssb::gemm2;
+  SSB_REQUIRE(W_a && packed, "null pointer");
+  SSB_REQUIRE(K1 > 0 && K2 >= 0 && n_each > 0, "bad shape");
+  SSB_REQUIRE(((uintptr_t)packed & 15) == 0, "packed must be 16-byte aligned");
+  const int N = (int)(W_b ? 2 * n_each : n_each);
+  SSB_REQUIRE(kp_of((int)K1, (int)K2) <= MAX_KP && N <= MAX_N, "K > 384 or N > 1152 not supported");
+  const int items = round_up(N, BN) * (kp_of((int)K1, (int)K2) / 8);
+  prepack_kernel<<<cdiv(items, 256), 256, 0, (cudaStream_t)stream>>>(W_a, W_b ? W_b : W_a, ldw, (int)n_each, (int)K1, (int)K2, N,
+                                                                   reinterpret_cast<uint8_t*>(packed));
+  SSB_LAUNCH_CHECK();
+  return SSB_OK;
+}
+
+// C[M, N] = [A1 | A2] . packed^T + bias (fp16 operands, fp32 accumulation in TMEM).  lengths/T (optional): rows of
+// padded frames (m % T >= lengths[m / T]) are not written.  K1, K2, lda1, lda2 multiples of 4; 16-byte aligned bases.
+extern "C" int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                             const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
+                             const int64_t* lengths, int64_t T, void* stream) {
+  using namespace ssb;
+  using namespace ssb::gemm2;
+  SSB_REQUIRE(A1 && packed && C, "null pointer");
+  SSB_REQUIRE(K1 > 0 && K1 % 4 == 0 && lda1 % 4 == 0, "K1/lda1 must be multiples of 4");
+  SSB_REQUIRE(!A2 || (K2 > 0 && K2 % 4 == 0 && lda2 % 4 == 0), "K2/lda2 must be multiples of 4");
+  SSB_REQUIRE(((uintptr_t)A1 & 15) == 0 && ((uintptr_t)A2 & 15) == 0 && ((uintptr_t)packed & 15) == 0, "operands must be 16-byte aligned");
+  SSB_REQUIRE(!lengths || T > 0, "row mask needs T");
+  if (!A2) K2 = 0;
+  const int Kp = kp_of((int)K1, (int)K2);
+  SSB_REQUIRE(Kp <= MAX_KP && N <= MAX_N && N > 0, "K > 384 or N > 1152 not supported");
+  SSB_REQUIRE(M < (int64_t)1 << 31, "M too large");
+  if (M == 0) return SSB_OK;
+  Args a{A1, lda1, (int)K1, A2, lda2, (int)K2, reinterpret_cast<const uint8_t*>(packed), bias, C, ldc, (int)M, (int)N, lengths, (int)T};
+  const int nnt = cdiv(N, BN);
+  const size_t smem = smem_bytes(Kp, nnt);
+  const int m_tiles = cdiv(M, BM);
+  SSB_CUDA(cudaFuncSetAttribute(proj_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  proj_gemm_kernel<<<m_tiles < kSMs ? m_tiles : kSMs, THREADS, smem, (cudaStream_t)stream>>>(a);
+  SSB_LAUNCH_CHECK();
+  return SSB_OK;
+}

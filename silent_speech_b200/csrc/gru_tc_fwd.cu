@@ -214,6 +214,10 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
             *reinterpret_cast<float4*>(gs + 3 * H) = make_float4(hn8[0], hn8[1], hn8[2], hn8[3]);
             *reinterpret_cast<float4*>(gs + 3 * H + 4) = make_float4(hn8[4], hn8[5], hn8[6], hn8[7]);
           }
+          // Before this CTA's slice is overwritten with h(s): every peer has finished MMA #s, i.e. it has consumed
+          // h(s-1) -- which also means the outgoing bulk copies of h(s-1), whose SOURCE is this slice, have landed
+          // (a copy still reading its source while the next step overwrote it was a rare lo-part race).
+          if (c == 0 && s >= 1) tc::mbar_wait_cluster(&ctl.empty, (s - 1) & 1);
           // new h (8 units = one 16-byte core-matrix row) into this CTA's slice of the A operand
           const uint32_t off = (uint32_t)((rank * U + ug * UT + c * 8) >> 3) * A_LBO + a_row_off;
           float hh[8], ll[8];
@@ -230,7 +234,9 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
       tc::fence_before_sync();                                   // TMEM reads ordered before the next step's MMA
       asm volatile("bar.sync 1, %0;\n" ::"n"(EPI_THREADS) : "memory");
       if (tid == 0 && s + 1 < maxlen) {
-        if (s >= 1) tc::mbar_wait_cluster(&ctl.empty, (s - 1) & 1);   // peers finished reading h(s-1) from their A
+        // every ACTIVE gate thread awaited the `empty` phase of step s-1 before rewriting the slice; if this
+        // thread's own clip has ended it has not, so it does now (the phase cannot advance before h(s) is sent)
+        if (s >= 1 && !act) tc::mbar_wait_cluster(&ctl.empty, (s - 1) & 1);
         tc::mbar_arrive_expect_tx(&ctl.full, kTxBytes);               // my own slice is in place; expect the peers' bytes
         const uint32_t src_hi = tc::smem_u32(a_hi) + rank * SLICE, src_lo = tc::smem_u32(a_lo) + rank * SLICE;
         for (uint32_t p = 1; p < CL; ++p) {

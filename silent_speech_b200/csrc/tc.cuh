@@ -147,6 +147,15 @@ __device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_cluster_addr, uin
                ::"r"(dst_cluster_addr), "r"(src_local_addr), "r"(bytes), "r"(peer_bar_cluster_addr) : "memory");
 }
 
+// bulk async copy global -> own shared memory (TMA, 1-D); the bytes complete_tx on the local mbarrier
+__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst_smem_addr, const void* src_global, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+               ::"r"(dst_smem_addr), "l"(src_global), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(smem_u32(bar)) : "memory");
+}
+
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
   uint32_t* r = reinterpret_cast<uint32_t*>(v);
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n"

@@ -239,6 +239,32 @@ def gemm_tc(A1: torch.Tensor, W: torch.Tensor, bias, C2d: torch.Tensor, A2: Opti
     return C2d
 
 
+def proj_prepack(W_a: torch.Tensor, W_b: Optional[torch.Tensor], K1: int, K2: int = 0) -> torch.Tensor:
+    """[W_a ; W_b] (each [n_each, K1+K2] fp32) -> fp16 block layout streamed by proj_gemm (a derived cache)."""
+    _need(W_a, torch.float32, "W_a")
+    if W_b is not None:
+        _need(W_b, torch.float32, "W_b")
+    n_each = W_a.shape[0]
+    N = n_each * (2 if W_b is not None else 1)
+    L = _lib.lib()
+    L.ssb_proj_packed_bytes.restype = i64
+    nbytes = L.ssb_proj_packed_bytes(i64(N), i64(K1), i64(K2))
+    packed = torch.empty(nbytes, device=W_a.device, dtype=torch.uint8)
+    check(L.ssb_proj_prepack(ptr(W_a), ptr(W_b), i64(W_a.stride(0)), i64(n_each), i64(K1), i64(K2), ptr(packed), stream_ptr()))
+    return packed
+
+
+def proj_gemm(A1: torch.Tensor, packed: torch.Tensor, bias, C2d: torch.Tensor, N: int, A2: Optional[torch.Tensor] = None,
+              lengths=None, T: int = 0):
+    """C[:, :N] = [A1 | A2] @ packed^T + bias: both directions' input projections in one persistent tcgen05 GEMM."""
+    M, K1 = A1.shape
+    K2 = 0 if A2 is None else A2.shape[1]
+    check(_lib.lib().ssb_proj_gemm(ptr(A1), i64(A1.stride(0)), i64(K1), ptr(A2), i64(0 if A2 is None else A2.stride(0)),
+                                   i64(K2), ptr(packed), ptr(bias), ptr(C2d), i64(C2d.stride(0)), i64(M), i64(N),
+                                   ptr(lengths), i64(T), stream_ptr()))
+    return C2d
+
+
 def gru_fold_bias(bih_f, bhh_f, bih_r, bhh_r) -> torch.Tensor:
     out = torch.empty(2 * 3 * HIDDEN, device=bih_f.device, dtype=torch.float32)
     check(_lib.lib().ssb_gru_fold_bias(ptr(bih_f), ptr(bhh_f), ptr(bih_r), ptr(bhh_r), ptr(out), stream_ptr()))

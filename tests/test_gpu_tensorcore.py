@@ -155,3 +155,44 @@ def test_roi_cnn_tc3_many_frames_dynamic_handout(passes, tol):
     assert rel_err(a, ref32) < tol
     mask = (torch.arange(T)[None, :] < torch.from_numpy(d["lengths"])[:, None])
     assert torch.all(a.cpu()[~mask] == 0)
+
+
+@pytest.mark.parametrize("M,n_each,K1,K2,T", [(128, 576, 180, 32, 0), (1000, 576, 384, 0, 10), (77, 576, 180, 0, 0),
+                                              (39960, 576, 180, 32, 90), (300, 200, 64, 0, 0)])
+def test_proj_gemm_vs_fp64(M, n_each, K1, K2, T):
+    """Persistent both-direction projection GEMM (packed fp16 weights, bulk-copy weight ring) against an fp64
+    matmul of the fp16-rounded operands (exact products, fp32 accumulation error only) and of the raw operands."""
+    dev = _cuda()
+    from silent_speech_b200 import ops
+    g = torch.Generator().manual_seed(M + K1)
+    A1 = torch.randn(M, K1, generator=g)
+    A2 = torch.randn(M, K2, generator=g) if K2 else None
+    Wa = torch.randn(n_each, K1 + K2, generator=g) * 0.1
+    Wb = torch.randn(n_each, K1 + K2, generator=g) * 0.1
+    b = torch.randn(2 * n_each, generator=g)
+    A = A1 if A2 is None else torch.cat([A1, A2], 1)
+    W = torch.cat([Wa, Wb], 0)
+    ref16 = A.half().double() @ W.half().double().T + b.double()
+    ref = A.double() @ W.double().T + b.double()
+    N = 2 * n_each
+    C = torch.full((M, N + 4), -7.0, device=dev)
+    Cv = C[:, :N]
+    L = None
+    if T:
+        Lh = torch.randint(1, T + 1, (M // T,), generator=g)
+        Lh[0] = T
+        L = Lh.to(dev)
+    packed = ops.proj_prepack(Wa.to(dev), Wb.to(dev), K1, K2)
+    ops.proj_gemm(A1.to(dev), packed, b.to(dev), Cv, N, A2=None if A2 is None else A2.to(dev), lengths=L, T=T)
+    torch.cuda.synchronize()
+    out = C.cpu()
+    assert torch.all(out[:, N:] == -7.0)
+    if T:
+        Mr = (M // T) * T
+        mask = (torch.arange(T)[None, :] < Lh[:, None]).reshape(-1)
+        live = torch.zeros(M, dtype=torch.bool); live[:Mr] = mask
+        assert torch.all(out[~live][:, :N] == -7.0)          # rows of padded frames are not written
+    else:
+        live = torch.ones(M, dtype=torch.bool)
+    assert rel_err(out[live][:, :N], ref16[live]) < 2e-6
+    assert rel_err(out[live][:, :N], ref[live]) < 3e-3

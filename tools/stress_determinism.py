@@ -1,0 +1,54 @@
+"""Repeat each tensor-core stage on fixed inputs and report run-to-run deviations (race hunting; GPU only)."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from oracle import ref_model
+from silent_speech_b200 import ops, synth
+
+dev = torch.device("cuda")
+p = ref_model.synth_params(7, use_roi=False)
+B, T = 260, 64
+d = synth.clip_batch(B, T, mode="uniform", seed=9, use_roi=False)
+X = torch.from_numpy(d["X"]).to(dev); L = torch.from_numpy(d["lengths"]).to(dev)
+G3 = 576
+reps = int(sys.argv[1]) if len(sys.argv) > 1 else 40
+mask = (torch.arange(T, device=dev)[None, :] < L[:, None])
+
+
+def dev_of(name):
+    return p[name].to(dev).contiguous()
+
+
+wih = [dev_of("gru.weight_ih_l0"), dev_of("gru.weight_ih_l0_reverse")]
+whh = [dev_of("gru.weight_hh_l0"), dev_of("gru.weight_hh_l0_reverse")]
+bih = [dev_of("gru.bias_ih_l0"), dev_of("gru.bias_ih_l0_reverse")]
+bhh = [dev_of("gru.bias_hh_l0"), dev_of("gru.bias_hh_l0_reverse")]
+fold = ops.gru_fold_bias(bih[0], bhh[0], bih[1], bhh[1])
+order = torch.argsort(L, descending=True).to(torch.int32)
+for passes in (3, 1):
+    gi_ref = None
+    out_ref = None
+    bad_g = bad_r = 0
+    for it in range(reps):
+        # churn the allocator so buffers move around / contain garbage
+        junk = torch.randn(1 << 20, device=dev) * 1e3
+        gi = torch.empty(B, T, 2 * G3, device=dev)
+        gi.fill_(float("nan"))
+        gi2d = gi.view(B * T, 2 * G3)
+        for dd in (0, 1):
+            ops.gemm_tc(X.view(B * T, 180), wih[dd], fold[dd * G3:(dd + 1) * G3], gi2d, passes=passes, lengths=L, T=T, c_col0=dd * G3)
+        g = torch.where(mask[..., None], gi, torch.zeros_like(gi))
+        if gi_ref is None:
+            gi_ref = g.clone()
+        elif not torch.equal(g, gi_ref):
+            bad_g += 1
+            print(f"passes={passes} it={it}: gemm_tc differs, max abs {float((g - gi_ref).abs().max()):.3e}, nan={bool(torch.isnan(g).any())}")
+        out = ops.gru_layer_fwd_tc(gi_ref.clone() if False else gi, L, whh[0], bhh[0], whh[1], bhh[1], passes=passes, order=order)
+        if out_ref is None:
+            out_ref = out.clone()
+        elif not torch.equal(out, out_ref):
+            bad_r += 1
+            print(f"passes={passes} it={it}: gru_tc differs, max abs {float((out - out_ref).abs().max()):.3e}")
+        del junk
+    torch.cuda.synchronize()
+    print(f"passes={passes}: {reps} reps, gemm mismatches {bad_g}, gru mismatches {bad_r}")
