@@ -11,8 +11,8 @@
 //     straight into its shared-memory stage -- no register staging, no conversion in the main loop;
 //   * a persistent CTA owns a 128-row tile of A: it is read from HBM once, converted to fp16 once and stays
 //     resident in shared memory while the CTA sweeps all nine 128-column tiles of N;
-//   * warp roles: warps 0-3 epilogue (one TMEM lane quarter each), warp 4 weight producer, warp 5 MMA issuer;
-//     6-stage weight ring and two 128-column TMEM accumulators, so the epilogue (TMEM -> +bias -> global)
+//   * warp roles: warps 0-7 epilogue (two per TMEM lane quarter), warp 8 weight producer, warp 9 MMA issuer;
+//     4-stage weight ring and two 128-column TMEM accumulators, so the epilogue (TMEM -> +bias -> global)
 //     of tile n overlaps the MMAs of tile n+1.
 // K is laid out as [A1 padded to 8 | A2 padded to 8 | zeros to a multiple of 64] on both operands.
 #include "common.cuh"
@@ -24,8 +24,9 @@ namespace gemm2 {
 constexpr int BM = 128, BN = 128, KB = 64;
 constexpr int CHUNK = 2048;                              // one k-chunk (8 k) of 128 rows: 16 groups x 128 B
 constexpr int W_BLOCK = (KB / 8) * CHUNK;                // 16,384 B
-constexpr int STAGES = 6;
-constexpr int EPI_WARPS = 4, THREADS = (EPI_WARPS + 2) * 32;
+constexpr int STAGES = 4;
+constexpr int EPI_WARPS = 8, THREADS = (EPI_WARPS + 2) * 32;   // two epilogue warps per TMEM lane quarter
+constexpr int TILE_LD = 36;                              // floats per row of an epilogue transpose tile (conflict-free 16-byte accesses)
 constexpr int TMEM_COLS = 256;
 constexpr int MAX_KP = 384, MAX_N = 1152;
 
@@ -76,8 +77,8 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
   const int K1p = round_up(a.K1, 8), Kp = kp_of(a.K1, a.K2), nkb = Kp / KB, nnt = (a.N + BN - 1) / BN;
   uint8_t* a_s = smem;                                       // Kp/8 chunks x 2048 B
   uint8_t* w_s = a_s + (Kp / 8) * CHUNK;                     // STAGES x 16 KB
-  float* tile_s = reinterpret_cast<float*>(w_s + STAGES * W_BLOCK);        // 4 x 32 x 33 floats
-  float* bias_s = tile_s + EPI_WARPS * 32 * 33;              // nnt * 128 floats
+  float* tile_s = reinterpret_cast<float*>(w_s + STAGES * W_BLOCK);        // EPI_WARPS x 32 x TILE_LD floats
+  float* bias_s = tile_s + EPI_WARPS * 32 * TILE_LD;              // nnt * 128 floats
   uint8_t* live_s = reinterpret_cast<uint8_t*>(bias_s + nnt * BN);         // 128 bytes
   Ctl& ctl = *reinterpret_cast<Ctl*>(live_s + BM);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -112,25 +113,35 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
     // 128 B contiguous per row from global, conflict-free 16-byte stores.
     {
       const int items = BM * (Kp / 8);
-#pragma unroll 4
-      for (int idx = tid; idx < items; idx += THREADS) {
-        const int r8 = idx & 7, c4 = (idx >> 3) & 3, rest = idx >> 5, rg = rest & 15, cg = rest >> 4;
-        const int row = rg * 8 + r8, chunk = cg * 4 + c4, kk = chunk * 8;
-        float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
-        if (m0 + row < a.M) {
-          if (kk < K1p) {
-            const float* g = a.A1 + (int64_t)(m0 + row) * a.lda1 + kk;
-            if (kk < a.K1) v0 = __ldg(reinterpret_cast<const float4*>(g));
-            if (kk + 4 < a.K1) v1 = __ldg(reinterpret_cast<const float4*>(g + 4));
-          } else if (kk - K1p < a.K2) {
-            const int k2 = kk - K1p;
-            const float* g = a.A2 + (int64_t)(m0 + row) * a.lda2 + k2;
-            v0 = __ldg(reinterpret_cast<const float4*>(g));
-            if (k2 + 4 < a.K2) v1 = __ldg(reinterpret_cast<const float4*>(g + 4));
+      constexpr int NB = 4;                                  // items per batch: 8 x 16-byte loads in flight per thread
+      for (int base = tid; base < items; base += NB * THREADS) {
+        float4 v0[NB], v1[NB];
+        uint32_t dst[NB];
+#pragma unroll
+        for (int u = 0; u < NB; ++u) {
+          const int idx = base + u * THREADS;
+          const int r8 = idx & 7, c4 = (idx >> 3) & 3, rest = idx >> 5, rg = rest & 15, cg = rest >> 4;
+          const int row = rg * 8 + r8, chunk = cg * 4 + c4, kk = chunk * 8;
+          v0[u] = make_float4(0.f, 0.f, 0.f, 0.f); v1[u] = v0[u];
+          dst[u] = idx < items ? (uint32_t)(chunk * CHUNK + rg * 128 + r8 * 16) : 0xffffffffu;
+          if (idx < items && m0 + row < a.M) {
+            if (kk < K1p) {
+              const float* g = a.A1 + (int64_t)(m0 + row) * a.lda1 + kk;
+              if (kk < a.K1) v0[u] = __ldg(reinterpret_cast<const float4*>(g));
+              if (kk + 4 < a.K1) v1[u] = __ldg(reinterpret_cast<const float4*>(g + 4));
+            } else if (kk - K1p < a.K2) {
+              const int k2 = kk - K1p;
+              const float* g = a.A2 + (int64_t)(m0 + row) * a.lda2 + k2;
+              v0[u] = __ldg(reinterpret_cast<const float4*>(g));
+              if (k2 + 4 < a.K2) v1[u] = __ldg(reinterpret_cast<const float4*>(g + 4));
+            }
           }
         }
-        *reinterpret_cast<uint4*>(a_s + chunk * CHUNK + rg * 128 + r8 * 16) =
-            make_uint4(tc::pack_bf16(v0.x, v0.y), tc::pack_bf16(v0.z, v0.w), tc::pack_bf16(v1.x, v1.y), tc::pack_bf16(v1.z, v1.w));
+#pragma unroll
+        for (int u = 0; u < NB; ++u)
+          if (dst[u] != 0xffffffffu)
+            *reinterpret_cast<uint4*>(a_s + dst[u]) = make_uint4(tc::pack_bf16(v0[u].x, v0[u].y), tc::pack_bf16(v0[u].z, v0[u].w),
+                                                                 tc::pack_bf16(v1[u].x, v1[u].y), tc::pack_bf16(v1[u].z, v1[u].w));
       }
     }
     tc::fence_async_smem();
@@ -178,28 +189,40 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
       acc_it = __shfl_sync(0xffffffffu, acc_it, 0);
     } else {
       // =============================== epilogue warps ===============================
-      float* tile = tile_s + warp * (32 * 33);
-      const int row0 = m0 + warp * 32;
-      const uint32_t tlane = tmem + ((uint32_t)(warp * 32) << 16);
+      // warp w reads TMEM lanes 32 (w % 4) ..; warps w and w + 4 split the four 32-column groups of a tile.
+      // TMEM -> registers -> per-warp transpose tile (16-byte stores) -> + bias -> global: every store instruction
+      // writes four full 128-byte row segments.
+      float* tile = tile_s + warp * (32 * TILE_LD);
+      const int q = warp & 3, half = warp >> 2;
+      const int row0 = m0 + q * 32;
+      const uint32_t tlane = tmem + ((uint32_t)(q * 32) << 16);
+      const uint32_t live_mask = __ballot_sync(0xffffffffu, live_s[q * 32 + lane] != 0);
+      const int rsub = lane >> 3, cch = lane & 7;          // read-back: 4 rows x 8 column chunks per instruction
       for (int nt = 0; nt < nnt; ++nt, ++acc_it) {
         const uint32_t buf = acc_it & 1;
         tc::mbar_wait_bounded(&ctl.accfull[buf], (acc_it >> 1) & 1);
         tc::fence_after_sync();
 #pragma unroll 1
-        for (int cg = 0; cg < BN / 32; ++cg) {
+        for (int cgi = 0; cgi < 2; ++cgi) {
+          const int cg = half * 2 + cgi;
           float v[32];
           tc::tmem_ld32(tlane + buf * BN + cg * 32, v);
           tc::tmem_ld_wait();
 #pragma unroll
-          for (int q = 0; q < 32; ++q) tile[lane * 33 + q] = v[q];
+          for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(tile + lane * TILE_LD + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
           __syncwarp();
-          const int n = nt * BN + cg * 32 + lane;
-          if (n < a.N) {
-            const float bv = bias_s[n];
+          const int n = nt * BN + cg * 32 + cch * 4;
+          if (n < a.N) {                                     // N is a multiple of 4
+            const float4 bv = *reinterpret_cast<const float4*>(bias_s + n);
             float* c = a.C + (int64_t)row0 * a.ldc + n;
-#pragma unroll 8
-            for (int r = 0; r < 32; ++r)
-              if (live_s[warp * 32 + r]) c[(int64_t)r * a.ldc] = tile[r * 33 + lane] + bv;
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int r = it * 4 + rsub;
+              float4 o = *reinterpret_cast<const float4*>(tile + r * TILE_LD + 4 * cch);
+              o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+              if ((live_mask >> r) & 1u) *reinterpret_cast<float4*>(c + (int64_t)r * a.ldc) = o;
+            }
           }
           __syncwarp();
         }
@@ -215,7 +238,7 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
 }
 
 inline size_t smem_bytes(int Kp, int nnt) {
-  return (size_t)(Kp / 8) * CHUNK + STAGES * W_BLOCK + EPI_WARPS * 32 * 33 * 4 + (size_t)nnt * BN * 4 + BM + sizeof(Ctl);
+  return (size_t)(Kp / 8) * CHUNK + STAGES * W_BLOCK + EPI_WARPS * 32 * TILE_LD * 4 + (size_t)nnt * BN * 4 + BM + sizeof(Ctl);
 }
 
 }  // namespace gemm2
@@ -257,6 +280,7 @@ extern "C" int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const fl
   SSB_REQUIRE(!A2 || (K2 > 0 && K2 % 4 == 0 && lda2 % 4 == 0), "K2/lda2 must be multiples of 4");
   SSB_REQUIRE(((uintptr_t)A1 & 15) == 0 && ((uintptr_t)A2 & 15) == 0 && ((uintptr_t)packed & 15) == 0, "operands must be 16-byte aligned");
   SSB_REQUIRE(!lengths || T > 0, "row mask needs T");
+  SSB_REQUIRE(N % 4 == 0 && ldc % 4 == 0 && ((uintptr_t)C & 15) == 0, "N, ldc multiples of 4 and C 16-byte aligned");
   if (!A2) K2 = 0;
   const int Kp = kp_of((int)K1, (int)K2);
   SSB_REQUIRE(Kp <= MAX_KP && N <= MAX_N && N > 0, "K > 384 or N > 1152 not supported");

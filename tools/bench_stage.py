@@ -1,0 +1,71 @@
+"""Time one stage of the hot path alone (CUDA events, inputs larger than L2 or L2 flushed between runs).
+    python tools/bench_stage.py {cnn|proj|gru|head} [--precision fp16|tc3] [--batch 4096] [--layer 0|1] [--reps 5]"""
+import argparse, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from oracle import ref_model
+from silent_speech_b200 import ops, synth
+
+ap = argparse.ArgumentParser()
+ap.add_argument("stage")
+ap.add_argument("--precision", default="fp16")
+ap.add_argument("--batch", type=int, default=4096)
+ap.add_argument("--layer", type=int, default=1)
+ap.add_argument("--reps", type=int, default=5)
+ap.add_argument("--lengths", default="full")
+a = ap.parse_args()
+dev = torch.device("cuda")
+B, T, G3, H = a.batch, 90, 576, 192
+passes = {"fp16": 1, "tc3": 3}[a.precision]
+p = {k: v.to(dev).contiguous() for k, v in ref_model.synth_params(42).items()}
+L = torch.from_numpy(synth.lengths(B, T, a.lengths)).to(dev)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+
+def timeit(fn):
+    for _ in range(2):
+        fn()
+    ts = []
+    for _ in range(a.reps):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return min(ts), sum(ts) / len(ts)
+
+
+if a.stage == "cnn":
+    R = torch.randint(0, 256, (B, T, 48, 96), dtype=torch.uint8, device=dev)
+    names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
+             "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
+    w = [p[n] for n in names]
+    best, mean = timeit(lambda: ops.roi_cnn_fwd(R, L, w, passes=passes))
+    fl = 5_309_952 * int(L.sum())
+    print(f"cnn {a.precision} B={B}: best {best:.3f} ms mean {mean:.3f} ms  {fl / best / 1e9:.1f} TFLOP/s algorithmic")
+elif a.stage == "proj":
+    K1, K2 = (180, 32) if a.layer == 0 else (384, 0)
+    A1 = torch.randn(B * T, K1, device=dev)
+    A2 = torch.randn(B * T, K2, device=dev) if K2 else None
+    sfx = f"_l{a.layer}"
+    Wa, Wb = p["gru.weight_ih" + sfx], p["gru.weight_ih" + sfx + "_reverse"]
+    bias = torch.randn(2 * G3, device=dev)
+    gi = torch.empty(B * T, 2 * G3, device=dev)
+    if passes == 1:
+        packed = ops.proj_prepack(Wa, Wb, K1, K2)
+        fn = lambda: ops.proj_gemm(A1, packed, bias, gi, 2 * G3, A2=A2, lengths=L, T=T)
+    else:
+        def fn():
+            for d, W in enumerate((Wa, Wb)):
+                ops.gemm_tc(A1, W, bias[d * G3:(d + 1) * G3], gi, A2=A2, passes=3, lengths=L, T=T, c_col0=d * G3)
+    best, mean = timeit(fn)
+    by = B * T * (2 * G3 + K1 + K2) * 4
+    print(f"proj layer {a.layer} {a.precision} B={B}: best {best:.3f} ms mean {mean:.3f} ms  {by / best / 1e6:.0f} GB/s algorithmic (A read + C write)")
+elif a.stage == "gru":
+    gi = torch.randn(B, T, 2 * G3, device=dev) * 0.5
+    sfx = f"_l{a.layer}"
+    w = [p["gru.weight_hh" + sfx], p["gru.bias_hh" + sfx], p["gru.weight_hh" + sfx + "_reverse"], p["gru.bias_hh" + sfx + "_reverse"]]
+    order = torch.argsort(L, descending=True).to(torch.int32)
+    out = torch.empty(B, T, 2 * H, device=dev)
+    best, mean = timeit(lambda: ops.gru_layer_fwd_tc(gi, L, *w, passes=passes, order=order, out=out))
+    print(f"gru layer {a.precision} B={B}: best {best:.3f} ms mean {mean:.3f} ms  {best * 1e3 / T:.2f} us per step")
