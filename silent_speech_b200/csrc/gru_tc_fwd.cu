@@ -17,6 +17,7 @@
 // (ssb_gru_fold_bias); b_hn stays separate because it sits inside r * (W_hn h + b_hn).
 #include "common.cuh"
 #include "tc.cuh"
+#include <stdlib.h>
 
 namespace ssb {
 namespace grutc {
@@ -42,10 +43,18 @@ struct Ctl {
   int maxlen;
 };
 
+// single-pass mode has shared memory to spare: the next step's input projections (48 floats per gate thread) are
+// prefetched with cp.async into a thread-private staging area, so their HBM latency never sits on the step's
+// critical path; split mode (two operand copies resident) prefetches into L2 only.
+constexpr int GI_STAGE_BYTES = 12 * EPI_THREADS * 16;        // [12 float4][384 threads]: conflict-free 16-byte accesses
 template <bool kSplit>
-constexpr size_t smem_bytes() { return (kSplit ? 2 : 1) * (A_BYTES + B_BYTES) + sizeof(Ctl); }
+constexpr size_t smem_bytes() { return (kSplit ? 2 : 1) * (A_BYTES + B_BYTES) + (kSplit ? 0 : GI_STAGE_BYTES) + sizeof(Ctl); }
 
 // fast, ~1e-7-accurate gate functions: one ex2 + one rcp each (the recurrence is MUFU/latency-bound)
+// single-pass mode: the hardware tanh (MUFU.TANH, |err| <= 2^-11, the same grade as the fp16 operands) serves both
+// non-linearities -- sigmoid(x) = 0.5 tanh(0.5 x) + 0.5 -- so a GRU unit costs 3 MUFU ops instead of 6
+__device__ __forceinline__ float tanh_hw(float x) { float y; asm("tanh.approx.f32 %0, %1;\n" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sigm_hw(float x) { return fmaf(tanh_hw(0.5f * x), 0.5f, 0.5f); }
 __device__ __forceinline__ float sigm(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
 __device__ __forceinline__ float tanh_fast(float x) {
   const float e = __expf(-2.0f * fabsf(x));
@@ -57,14 +66,15 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(THREADS, 1)
 gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
                   const float* __restrict__ whh_f, const float* __restrict__ whh_r,
                   const float* __restrict__ bhn_f, const float* __restrict__ bhn_r,
-                  const int64_t* __restrict__ lengths, const int32_t* __restrict__ order, int B, int T,
+                  const int64_t* __restrict__ lengths, const int32_t* __restrict__ order, int B, int T, int dbg,
                   float* __restrict__ out, float* __restrict__ gates) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* a_hi = smem;
   uint8_t* b_hi = smem + A_BYTES;
   uint8_t* a_lo = smem + A_BYTES + B_BYTES;                 // only when kSplit
   uint8_t* b_lo = smem + 2 * A_BYTES + B_BYTES;
-  Ctl& ctl = *reinterpret_cast<Ctl*>(smem + (kSplit ? 2 : 1) * (A_BYTES + B_BYTES));
+  float4* gstage = reinterpret_cast<float4*>(smem + (kSplit ? 2 : 1) * (A_BYTES + B_BYTES));   // !kSplit only
+  Ctl& ctl = *reinterpret_cast<Ctl*>(smem + (kSplit ? 2 : 1) * (A_BYTES + B_BYTES) + (kSplit ? 0 : GI_STAGE_BYTES));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t rank = tc::cluster_ctarank();
@@ -97,7 +107,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   if (tid == 0) {
     tc::mbar_init(&ctl.full, 1);
     tc::mbar_init(&ctl.mma_done, 1);
-    tc::mbar_init(&ctl.empty, CL - 1);
+    tc::mbar_init(&ctl.empty, CL);                 // one multicast tcgen05.commit arrive per CTA of the cluster (incl. this one)
     tc::mbar_fence_init();
     ctl.maxlen = 0;
   }
@@ -127,7 +137,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   if (warp == EPI_THREADS / 32) {
     // =============================== MMA issuer warp ===============================
     for (int s = 1; s < maxlen; ++s) {
-      tc::mbar_wait_cluster(&ctl.full, (s - 1) & 1);            // all four h slices of step s-1 are in place
+      tc::mbar_wait_bounded(&ctl.full, (s - 1) & 1);            // all four h slices of step s-1 are in place
       tc::fence_after_sync();
       if (lane == 0) {
 #pragma unroll 1
@@ -143,6 +153,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
           }
         }
         tc::mma_commit(&ctl.mma_done);
+        tc::mma_commit_multicast(&ctl.empty, (uint16_t)((1u << CL) - 1));   // every CTA: "rank's tensor core has consumed h(s-1)"
       }
       __syncwarp();
     }
@@ -155,24 +166,51 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
     const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     const uint32_t a_row_off = (m >> 3) * 128 + (m & 7) * 16;
 
+    // gi of step s2 for this thread: 3 gates x 16 units.  !kSplit: cp.async into the private staging slots;
+    // kSplit: L2 prefetch of the three 64-byte segments.
+    auto prefetch_gi = [&](int s2) {
+      if (s2 < len) {
+        const int t2 = dir ? (len - 1 - s2) : s2;
+        const float* gp = gi + ((int64_t)b * T + t2) * gi_ld + dir * G3 + j0;
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+          if (kSplit) {
+            asm volatile("prefetch.global.L2 [%0];\n" ::"l"(gp + g * H));
+          } else {
+#pragma unroll
+            for (int v = 0; v < 4; ++v)
+              asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(tc::smem_u32(gstage + (g * 4 + v) * EPI_THREADS + tid)),
+                           "l"(gp + g * H + v * 4) : "memory");
+          }
+        }
+      }
+      if (!kSplit) asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    prefetch_gi(0);
     for (int s = 0; s < maxlen; ++s) {
       const bool act = s < len;
       const int t = dir ? (len - 1 - s) : s;
       const int64_t bt = (int64_t)(act ? b : 0) * T + (act ? t : 0);
-      float4 g4[12];                                             // gi: 3 gates x 16 units, issued before the wait
-      if (act) {
-        const float* gp = gi + bt * gi_ld + dir * G3 + j0;
+      float4 g4[12];                                             // gi: 3 gates x 16 units
+      if (kSplit) {
+        if (act) {
+          const float* gp = gi + bt * gi_ld + dir * G3 + j0;
 #pragma unroll
-        for (int g = 0; g < 3; ++g)
+          for (int g = 0; g < 3; ++g)
 #pragma unroll
-          for (int v = 0; v < 4; ++v) g4[g * 4 + v] = __ldg(reinterpret_cast<const float4*>(gp + g * H) + v);
+            for (int v = 0; v < 4; ++v) g4[g * 4 + v] = __ldg(reinterpret_cast<const float4*>(gp + g * H) + v);
+        }
+        prefetch_gi(s + 1);
+      } else {
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        if (act) {
+#pragma unroll
+          for (int v = 0; v < 12; ++v) g4[v] = gstage[v * EPI_THREADS + tid];
+        }
       }
       if (s >= 1) {
         tc::mbar_wait_bounded(&ctl.mma_done, (s - 1) & 1);
         tc::fence_after_sync();
-        if (tid == 0) {                                          // tell the peers: my tensor core is done reading h(s-1)
-          for (uint32_t p = 1; p < CL; ++p) tc::mbar_arrive_remote(tc::mapa(tc::smem_u32(&ctl.empty), (rank + p) % CL));
-        }
       }
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
@@ -194,15 +232,12 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
             const int u = c * 8 + q;
-            r8[q] = sigm(gr[q] + ar[q]);
-            z8[q] = sigm(gz[q] + az[q]);
+            r8[q] = kSplit ? sigm(gr[q] + ar[q]) : sigm_hw(gr[q] + ar[q]);
+            z8[q] = kSplit ? sigm(gz[q] + az[q]) : sigm_hw(gz[q] + az[q]);
             hn8[q] = an[q] + bn[u];
-            n8[q] = tanh_fast(gn[q] + r8[q] * hn8[q]);
+            n8[q] = kSplit ? tanh_fast(gn[q] + r8[q] * hn8[q]) : tanh_hw(gn[q] + r8[q] * hn8[q]);
             h[u] = (1.0f - z8[q]) * n8[q] + z8[q] * h[u];
           }
-          float* orow = out + bt * (2 * H) + dir * H + j0 + c * 8;
-          *reinterpret_cast<float4*>(orow) = make_float4(h[c * 8], h[c * 8 + 1], h[c * 8 + 2], h[c * 8 + 3]);
-          *reinterpret_cast<float4*>(orow + 4) = make_float4(h[c * 8 + 4], h[c * 8 + 5], h[c * 8 + 6], h[c * 8 + 7]);
           if (kSave) {
             float* gs = gates + (bt * 2 + dir) * (4 * H) + j0 + c * 8;
             *reinterpret_cast<float4*>(gs) = make_float4(r8[0], r8[1], r8[2], r8[3]);
@@ -217,7 +252,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
           // Before this CTA's slice is overwritten with h(s): every peer has finished MMA #s, i.e. it has consumed
           // h(s-1) -- which also means the outgoing bulk copies of h(s-1), whose SOURCE is this slice, have landed
           // (a copy still reading its source while the next step overwrote it was a rare lo-part race).
-          if (c == 0 && s >= 1) tc::mbar_wait_cluster(&ctl.empty, (s - 1) & 1);
+          if (c == 0 && s >= 1) tc::mbar_wait_bounded(&ctl.empty, (s - 1) & 1);
           // new h (8 units = one 16-byte core-matrix row) into this CTA's slice of the A operand
           const uint32_t off = (uint32_t)((rank * U + ug * UT + c * 8) >> 3) * A_LBO + a_row_off;
           float hh[8], ll[8];
@@ -236,16 +271,25 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
       if (tid == 0 && s + 1 < maxlen) {
         // every ACTIVE gate thread awaited the `empty` phase of step s-1 before rewriting the slice; if this
         // thread's own clip has ended it has not, so it does now (the phase cannot advance before h(s) is sent)
-        if (s >= 1 && !act) tc::mbar_wait_cluster(&ctl.empty, (s - 1) & 1);
-        tc::mbar_arrive_expect_tx(&ctl.full, kTxBytes);               // my own slice is in place; expect the peers' bytes
+        if (s >= 1 && !act) tc::mbar_wait_bounded(&ctl.empty, (s - 1) & 1);
+        tc::mbar_arrive_expect_tx(&ctl.full, (dbg & 1) ? (CL - 1) * 16u * (kSplit ? 2 : 1) : kTxBytes);   // my own slice is in place; expect the peers' bytes
         const uint32_t src_hi = tc::smem_u32(a_hi) + rank * SLICE, src_lo = tc::smem_u32(a_lo) + rank * SLICE;
         for (uint32_t p = 1; p < CL; ++p) {
           const uint32_t peer = (rank + p) % CL;
           const uint32_t bar = tc::mapa(tc::smem_u32(&ctl.full), peer);
-          tc::bulk_copy_to_peer(tc::mapa(src_hi, peer), src_hi, SLICE, bar);
-          if (kSplit) tc::bulk_copy_to_peer(tc::mapa(src_lo, peer), src_lo, SLICE, bar);
+          tc::bulk_copy_to_peer(tc::mapa(src_hi, peer), src_hi, (dbg & 1) ? 16u : SLICE, bar);
+          if (kSplit) tc::bulk_copy_to_peer(tc::mapa(src_lo, peer), src_lo, (dbg & 1) ? 16u : SLICE, bar);
         }
       }
+      // Global traffic goes AFTER the exchange has been kicked off: the proxy fence above waits for this thread's
+      // outstanding memory operations, and a global store / cp.async in front of it put HBM latency on every step.
+      if (act) {
+        float* orow = out + bt * (2 * H) + dir * H + j0;
+#pragma unroll
+        for (int v = 0; v < UT / 4; ++v)
+          reinterpret_cast<float4*>(orow)[v] = make_float4(h[4 * v], h[4 * v + 1], h[4 * v + 2], h[4 * v + 3]);
+      }
+      if (!kSplit) prefetch_gi(s + 1);                           // staging slots were consumed above; lands during the exchange
     }
     // zeros past each clip's length (pad_packed_sequence semantics)
     if (b >= 0) {
@@ -301,13 +345,14 @@ extern "C" int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_
   SSB_REQUIRE(passes == 1 || passes == 3, "passes must be 1 or 3");
   if (B == 0) return SSB_OK;
   dim3 grid(CL * cdiv(B, BM), 2), block(THREADS);
+  static const int dbg = getenv("SSB_GRU_DBG") ? atoi(getenv("SSB_GRU_DBG")) : 0;   // timing experiments only (wrong results)
   cudaStream_t st = (cudaStream_t)stream;
 #define SSB_LAUNCH_GRUTC(SPLIT, SAVE)                                                                          \
   do {                                                                                                          \
     SSB_CUDA(cudaFuncSetAttribute(gru_tc_fwd_kernel<SPLIT, SAVE>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
                                   (int)smem_bytes<SPLIT>()));                                                   \
     gru_tc_fwd_kernel<SPLIT, SAVE><<<grid, block, smem_bytes<SPLIT>(), st>>>(                                   \
-        gi, gi_ld, whh_f, whh_r, bhh_f + 2 * H, bhh_r + 2 * H, lengths, order, (int)B, (int)T, out, gates);     \
+        gi, gi_ld, whh_f, whh_r, bhh_f + 2 * H, bhh_r + 2 * H, lengths, order, (int)B, (int)T, dbg, out, gates);\
   } while (0)
   if (passes == 3) { if (gates) SSB_LAUNCH_GRUTC(true, true); else SSB_LAUNCH_GRUTC(true, false); }
   else             { if (gates) SSB_LAUNCH_GRUTC(false, true); else SSB_LAUNCH_GRUTC(false, false); }
