@@ -38,7 +38,7 @@ constexpr int UT = 16;                     // hidden units per gate thread
 constexpr int TMEM_COLS = 256;
 
 struct Ctl {
-  uint64_t full, mma_done, empty;
+  uint64_t full, mma_done, empty, ready;
   uint32_t tmem_base;
   int maxlen;
 };
@@ -107,6 +107,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   if (tid == 0) {
     tc::mbar_init(&ctl.full, 1);
     tc::mbar_init(&ctl.mma_done, 1);
+    tc::mbar_init(&ctl.ready, EPI_THREADS);
     tc::mbar_init(&ctl.empty, CL);                 // one multicast tcgen05.commit arrive per CTA of the cluster (incl. this one)
     tc::mbar_fence_init();
     ctl.maxlen = 0;
@@ -136,7 +137,22 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
 
   if (warp == EPI_THREADS / 32) {
     // =============================== MMA issuer warp ===============================
+    // The issuer warp also runs the exchange, so no gate thread sits on the step's serial chain:
+    // ready (all gate threads wrote h(s-1)) -> push this CTA's slice to the three peers -> full (all four slices here)
+    // -> MMA #s -> commits.  Every active gate thread awaited `empty`(s-2) before rewriting the slice, so the peers
+    // have consumed h(s-2) by the time `ready` completes.
+    const uint32_t src_hi = tc::smem_u32(a_hi) + rank * SLICE, src_lo = tc::smem_u32(a_lo) + rank * SLICE;
     for (int s = 1; s < maxlen; ++s) {
+      tc::mbar_wait_bounded(&ctl.ready, (s - 1) & 1);
+      if (lane == 0) {
+        tc::mbar_arrive_expect_tx(&ctl.full, (dbg & 1) ? (CL - 1) * 16u * (kSplit ? 2 : 1) : kTxBytes);
+        for (uint32_t p = 1; p < CL; ++p) {
+          const uint32_t peer = (rank + p) % CL;
+          const uint32_t bar = tc::mapa(tc::smem_u32(&ctl.full), peer);
+          tc::bulk_copy_to_peer(tc::mapa(src_hi, peer), src_hi, (dbg & 1) ? 16u : SLICE, bar);
+          if (kSplit) tc::bulk_copy_to_peer(tc::mapa(src_lo, peer), src_lo, (dbg & 1) ? 16u : SLICE, bar);
+        }
+      }
       tc::mbar_wait_bounded(&ctl.full, (s - 1) & 1);            // all four h slices of step s-1 are in place
       tc::fence_after_sync();
       if (lane == 0) {
@@ -267,20 +283,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
       }
       tc::fence_async_smem();                                    // slice visible to the async proxy (MMA, bulk copy)
       tc::fence_before_sync();                                   // TMEM reads ordered before the next step's MMA
-      asm volatile("bar.sync 1, %0;\n" ::"n"(EPI_THREADS) : "memory");
-      if (tid == 0 && s + 1 < maxlen) {
-        // every ACTIVE gate thread awaited the `empty` phase of step s-1 before rewriting the slice; if this
-        // thread's own clip has ended it has not, so it does now (the phase cannot advance before h(s) is sent)
-        if (s >= 1 && !act) tc::mbar_wait_bounded(&ctl.empty, (s - 1) & 1);
-        tc::mbar_arrive_expect_tx(&ctl.full, (dbg & 1) ? (CL - 1) * 16u * (kSplit ? 2 : 1) : kTxBytes);   // my own slice is in place; expect the peers' bytes
-        const uint32_t src_hi = tc::smem_u32(a_hi) + rank * SLICE, src_lo = tc::smem_u32(a_lo) + rank * SLICE;
-        for (uint32_t p = 1; p < CL; ++p) {
-          const uint32_t peer = (rank + p) % CL;
-          const uint32_t bar = tc::mapa(tc::smem_u32(&ctl.full), peer);
-          tc::bulk_copy_to_peer(tc::mapa(src_hi, peer), src_hi, (dbg & 1) ? 16u : SLICE, bar);
-          if (kSplit) tc::bulk_copy_to_peer(tc::mapa(src_lo, peer), src_lo, (dbg & 1) ? 16u : SLICE, bar);
-        }
-      }
+      tc::mbar_arrive(&ctl.ready);                               // 384 arrivals: h(s) is complete in this CTA's slice
       // Global traffic goes AFTER the exchange has been kicked off: the proxy fence above waits for this thread's
       // outstanding memory operations, and a global store / cp.async in front of it put HBM latency on every step.
       if (act) {
