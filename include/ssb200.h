@@ -172,6 +172,16 @@ int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const float* A2, in
                   const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
                   const int64_t* lengths, int64_t T, void* stream);
 
+/* K6: batched mouth-ROI crop + BGR->gray + resize to 96x48, bit-exact with OpenCV 4.13.
+ * Replaces crop_roi_gray (live_infer_official.py:171-187; flavor 0: INTER_AREA, box in double arithmetic) and
+ * crop_roi (record_landmarks_official.py:102-118; flavor 1: INTER_LINEAR, box in float32 arithmetic).
+ * frames u8 [n_frames,Hf,Wf,3] BGR; frame_index i32 [N] or NULL (crop n reads frame n); centers f32 [N,2];
+ * mouth_w f64 [N] (4th return value of extract_feature); out u8 [N,48,96], zeros where the reference returns
+ * None; ok u8 [N] or NULL. */
+int ssb_roi_crop(const uint8_t* frames, const int32_t* frame_index, int64_t Hf, int64_t Wf,
+                 const float* centers, const double* mouth_w, int64_t N, int32_t flavor,
+                 uint8_t* out, uint8_t* ok, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -173,6 +173,29 @@ def golden_roi_crop(live, record):
     print("roi_crop.npz", ok_live, ok_rec)
 
 
+def golden_roi_crop_many(live, record):
+    """40 seeded crops on a 240x320 frame: interior, clipped by each border, smaller than 96x48 (up-scaling
+    fallbacks), exact integer ratios (area-fast, and the 2x case INTER_LINEAR routes to INTER_AREA), rejected boxes."""
+    import cv2
+    rng = np.random.default_rng(12)
+    frame = cv2.GaussianBlur(rng.integers(0, 256, size=(240, 320, 3)).astype(np.uint8), (5, 5), 1.2)
+    centers = np.stack([rng.uniform(-5, 325, 40), rng.uniform(-5, 245, 40)], 1).astype(np.float32)
+    widths = rng.uniform(2.0, 75.0, 40)
+    centers[:6] = [[160, 120], [160.5, 120.5], [160, 120], [3.2, 100.0], [318.0, 236.0], [160, 120]]
+    widths[:6] = [80.0, 40.0, 48.0, 30.0, 25.0, 0.5]              # 192x160, 96x80, 2x-ish, clipped, clipped, rejected
+    widths = np.array([float(np.float32(w)) for w in widths])     # mouth widths are float32 norms turned into Python floats
+    outs_live, outs_rec, ok_live, ok_rec = [], [], [], []
+    for c, mw in zip(centers, widths):
+        a = live.crop_roi_gray(frame, c, float(mw)); b = record.crop_roi(frame, c, float(mw) + 1e-6)
+        ok_live.append(a is not None); ok_rec.append(b is not None)
+        outs_live.append(a if a is not None else np.zeros((48, 96), np.uint8))
+        outs_rec.append(b if b is not None else np.zeros((48, 96), np.uint8))
+    np.savez_compressed(os.path.join(OUT, "roi_crop_many.npz"), frame=frame, centers=centers, widths=widths,
+                        roi_live=np.stack(outs_live), roi_record=np.stack(outs_rec),
+                        ok_live=np.array(ok_live), ok_record=np.array(ok_rec))
+    print("roi_crop_many.npz", int(np.sum(ok_live)), int(np.sum(ok_rec)))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     train, live, record = import_reference()
@@ -182,6 +205,7 @@ def main():
     golden_model(train, live, "points", False, B=5, T=20, lens=[20, 6, 13, 1, 17], seed=102)
     golden_model(train, live, "roi_hot", True, B=3, T=10, lens=[7, 10, 3], seed=103, scale=2.0)
     golden_roi_crop(live, record)
+    golden_roi_crop_many(live, record)
 
 
 if __name__ == "__main__":

@@ -4,7 +4,7 @@ attention-pooled word head and its train step, behind the C ABI of include/ssb20
 
 The package never falls back to eager PyTorch or the CPU: if libssb200.so is missing
 or the tensors are not on a B200 the calls raise."""
-from .landmarks import FIXED_IDXS, extract_feature, extract_features  # noqa: F401
+from .landmarks import FIXED_IDXS, crop_rois, extract_feature, extract_features  # noqa: F401
 from .model import BiGRUClassifier, load_classifier  # noqa: F401
 
-__all__ = ["BiGRUClassifier", "load_classifier", "extract_features", "extract_feature", "FIXED_IDXS"]
+__all__ = ["BiGRUClassifier", "load_classifier", "extract_features", "extract_feature", "crop_rois", "FIXED_IDXS"]

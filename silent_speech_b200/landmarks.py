@@ -69,3 +69,13 @@ def extract_feature(face, w, h, idxs, prev_xy=None):
     if prev_xy is not None:
         feat[2 * K] = float(np.mean(np.linalg.norm(xy_n - np.asarray(prev_xy, np.float32), axis=1)))
     return feat, xy_n, out["center"][0, 0].cpu().numpy(), float(out["mouth_w"][0, 0])
+
+
+def crop_rois(frames, centers, mouth_w, flavor: str = "live", frame_index=None):
+    """Batched crop_roi_gray (flavor 'live', live_infer_official.py:171-187) / crop_roi (flavor 'record',
+    record_landmarks_official.py:102-118) on the GPU: frames u8 [F,H,W,3] BGR, centers f32 [N,2] and mouth_w [N]
+    as returned by extract_features -> (R u8 [N,48,96], ok u8 [N]); rows where the reference returns None are zero
+    frames (what live_infer_official.py:290-293 substitutes)."""
+    import torch
+    from . import ops
+    return ops.roi_crop(frames, centers.contiguous().float(), mouth_w.to(torch.float64).contiguous(), flavor, frame_index)

@@ -284,3 +284,26 @@ def gru_layer_fwd_tc(gi, lengths, whh_f, bhh_f, whh_r, bhh_r, passes=3, order=No
                                           ptr(whh_f), ptr(bhh_f), ptr(whh_r), ptr(bhh_r), ptr(out), ptr(gates),
                                           i32(passes), stream_ptr()))
     return out
+
+
+# ----------------------------------------------------------------------------- K6
+def roi_crop(frames: torch.Tensor, centers: torch.Tensor, mouth_w: torch.Tensor, flavor: str = "live",
+             frame_index: Optional[torch.Tensor] = None):
+    """frames u8 [F,Hf,Wf,3] (BGR), centers f32 [N,2], mouth_w f64 [N] -> (roi u8 [N,48,96], ok u8 [N]).
+    flavor 'live' = crop_roi_gray (INTER_AREA), 'record' = crop_roi (INTER_LINEAR); bit-exact with OpenCV."""
+    _need(frames, torch.uint8, "frames")
+    _need(centers, torch.float32, "centers")
+    _need(mouth_w, torch.float64, "mouth_w")
+    if frame_index is not None:
+        _need(frame_index, torch.int32, "frame_index")
+    F, Hf, Wf, C = frames.shape
+    if C != 3:
+        raise _lib.SsbError("frames must be [F,H,W,3] BGR")
+    N = centers.shape[0]
+    if frame_index is None and N != F:
+        raise _lib.SsbError("without frame_index there must be one frame per crop")
+    out = torch.empty(N, ROI_H, ROI_W, device=frames.device, dtype=torch.uint8)
+    ok = torch.empty(N, device=frames.device, dtype=torch.uint8)
+    check(_lib.lib().ssb_roi_crop(ptr(frames), ptr(frame_index), i64(Hf), i64(Wf), ptr(centers), ptr(mouth_w), i64(N),
+                                  i32({"live": 0, "record": 1}[flavor]), ptr(out), ptr(ok), stream_ptr()))
+    return out, ok

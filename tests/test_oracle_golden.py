@@ -79,3 +79,39 @@ def test_train_step_matches_reference(golden_dir, name):
     for k, v in st.params().items():
         ref = g[f"step_samp/{k}"]
         assert np.abs(v.reshape(-1)[::97].numpy() - ref).max() <= 1e-6, k
+
+
+# ------------------------------------------------------------------ K6 ROI crop
+@pytest.mark.parametrize("name", ["roi_crop.npz", "roi_crop_many.npz"])
+def test_roi_crop_oracle_matches_reference_outputs(golden_dir, name):
+    """oracle/ref_roi_crop.py against crops produced by the reference's own crop_roi_gray / crop_roi (cv2 4.13)."""
+    from oracle import ref_roi_crop as rc
+    g = _load(golden_dir, name)
+    n_ok = 0
+    for i, (c, mw) in enumerate(zip(g["centers"], g["widths"])):
+        for flavor, key, okk, eps in (("live", "roi_live", "ok_live", 0.0), ("record", "roi_record", "ok_record", 1e-6)):
+            scale = float(mw) + (eps if name == "roi_crop_many.npz" else 0.0)
+            o = rc.crop_roi(flavor, g["frame"], c, scale)
+            assert (o is not None) == bool(g[okk][i]), (i, flavor)
+            if o is not None:
+                assert np.array_equal(o, g[key][i]), (i, flavor, int(np.abs(o.astype(int) - g[key][i]).max()))
+                n_ok += 1
+    assert n_ok >= 6
+
+
+def test_roi_crop_oracle_matches_cv2_on_seeded_sizes():
+    """The restated OpenCV arithmetic (gray, INTER_AREA incl. its fast and up-scaling paths, fixed-point bilinear)
+    against cv2 itself, where cv2 is importable (it is in the build container)."""
+    cv2 = pytest.importorskip("cv2")
+    from oracle import ref_roi_crop as rc
+    rng = np.random.default_rng(5)
+    img = cv2.GaussianBlur(rng.integers(0, 256, (300, 460, 3)).astype(np.uint8), (5, 5), 1.5)
+    g = cv2.cvtColor(img, cv2.COLOR_BGR2GRAY)
+    assert np.array_equal(g, rc.bgr2gray(img))
+    sizes = [(297, 37), (68, 171), (17, 280), (192, 96), (288, 240), (96, 48), (3, 3)]
+    for it in range(60):
+        w, h = sizes[it] if it < len(sizes) else (int(rng.integers(3, 420)), int(rng.integers(3, 290)))
+        x, y = int(rng.integers(0, 460 - w)), int(rng.integers(0, 300 - h))
+        src = np.ascontiguousarray(g[y:y + h, x:x + w])
+        assert np.array_equal(cv2.resize(src, (96, 48), interpolation=cv2.INTER_AREA), rc.resize_area(src)), (w, h)
+        assert np.array_equal(cv2.resize(src, (96, 48)), rc.resize_linear(src)), (w, h)
