@@ -182,6 +182,17 @@ int ssb_roi_crop(const uint8_t* frames, const int32_t* frame_index, int64_t Hf, 
                  const float* centers, const double* mouth_w, int64_t N, int32_t flavor,
                  uint8_t* out, uint8_t* ok, void* stream);
 
+/* Sliding-window stream state (windowing policy of inactive/live_feed.py:155-213 driving the official model).
+ * ring f32 [S,W,D]: per-stream ring of rows [point features | ROI-CNN embedding].  ssb_ring_push writes row i
+ * (x [n,dx], e [n,de] or NULL) at ring[sid[i]][pos[i]]; ssb_ring_gather builds the time-ordered, zero-padded
+ * windows Xw [m,T,dx], Ew [m,T,de] (nullable) from rows start[i].. (mod W) and writes lengths[i] = min(count[i],T).
+ * Head / count bookkeeping is the caller's (host integers). */
+int ssb_ring_push(float* ring, int64_t W, int64_t D, const int32_t* sid, const int32_t* pos,
+                  const float* x, int64_t dx, const float* e, int64_t de, int64_t n, void* stream);
+int ssb_ring_gather(const float* ring, int64_t W, int64_t D, const int32_t* sid, const int32_t* start,
+                    const int32_t* count, int64_t m, float* Xw, int64_t dx, float* Ew, int64_t de,
+                    int64_t T, int64_t* lengths, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

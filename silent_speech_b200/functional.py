@@ -37,7 +37,9 @@ def _project(A2d, w_pair, b_pair, gi2d, lengths, T, extra=None, x_dim=None):
 
 
 def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 0, y=None,
-                 label_smoothing: float = 0.0):
+                 label_smoothing: float = 0.0, emb=None):
+    """emb (optional, inference): precomputed ROI-CNN embeddings f32 [B,T,32] used instead of running K2 on R --
+    the streaming scheduler caches them per frame."""
     dev = X.device
     if not X.is_cuda:
         raise ops._lib.SsbError("inputs must be CUDA tensors: this package has no CPU path")
@@ -45,8 +47,10 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
     lengths = lengths.to(device=dev, dtype=torch.int64).contiguous()
     B, T, x_dim = X.shape
     ctx = {"B": B, "T": T, "lengths": lengths, "X": X}
-    emb = None
-    if R is not None:
+    if emb is not None:
+        emb = emb.contiguous().float()
+        ctx["emb"] = emb
+    elif R is not None:
         R = R.to(dev).contiguous()
         emb = ops.roi_cnn_fwd(R, lengths, model.roi_cnn.tensors(), standardize=model.standardize_roi,
                               passes={"fp32": 0, "tc3": 3, "fp16": 1}[getattr(model, "precision", "fp32")])

@@ -307,3 +307,23 @@ def roi_crop(frames: torch.Tensor, centers: torch.Tensor, mouth_w: torch.Tensor,
     check(_lib.lib().ssb_roi_crop(ptr(frames), ptr(frame_index), i64(Hf), i64(Wf), ptr(centers), ptr(mouth_w), i64(N),
                                   i32({"live": 0, "record": 1}[flavor]), ptr(out), ptr(ok), stream_ptr()))
     return out, ok
+
+
+# ----------------------------------------------------------------------------- stream rings
+def ring_push(ring: torch.Tensor, sid: torch.Tensor, pos: torch.Tensor, x: torch.Tensor, e: Optional[torch.Tensor] = None):
+    _need(ring, torch.float32, "ring"); _need(sid, torch.int32, "sid"); _need(pos, torch.int32, "pos"); _need(x, torch.float32, "x")
+    S, W, D = ring.shape
+    check(_lib.lib().ssb_ring_push(ptr(ring), i64(W), i64(D), ptr(sid), ptr(pos), ptr(x), i64(x.shape[1]), ptr(e),
+                                   i64(0 if e is None else e.shape[1]), i64(x.shape[0]), stream_ptr()))
+
+
+def ring_gather(ring: torch.Tensor, sid: torch.Tensor, start: torch.Tensor, count: torch.Tensor, T: int, dx: int, de: int):
+    _need(ring, torch.float32, "ring"); _need(sid, torch.int32, "sid"); _need(start, torch.int32, "start"); _need(count, torch.int32, "count")
+    S, W, D = ring.shape
+    m = sid.shape[0]
+    Xw = torch.empty(m, T, dx, device=ring.device, dtype=torch.float32)
+    Ew = torch.empty(m, T, de, device=ring.device, dtype=torch.float32) if de else None
+    lengths = torch.empty(m, device=ring.device, dtype=torch.int64)
+    check(_lib.lib().ssb_ring_gather(ptr(ring), i64(W), i64(D), ptr(sid), ptr(start), ptr(count), i64(m), ptr(Xw), i64(dx),
+                                     ptr(Ew), i64(de), i64(T), ptr(lengths), stream_ptr()))
+    return Xw, Ew, lengths
