@@ -163,6 +163,161 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def run_extra(args, rank, world, local):
+    """configs[3] (landmarks-only GRU stress, T=256) and configs[4] (sliding-window streams).  Same JSON contract;
+    the roofline entry is the projection GEMM (HBM-bound: A read + gi write) for points256 and the whole tick for stream."""
+    import torch.distributed as dist
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    from silent_speech_b200 import BiGRUClassifier, _lib as ssb_lib, ops, synth
+    from oracle import ref_model
+    peaks = load_peaks()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        t = torch.tensor([ms], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    if args.workload == "points256":
+        T, B = 256, args.batch or 4096
+        p = ref_model.synth_params(42, use_roi=False)
+        model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=False, precision=args.precision)
+        model.load_state_dict(p)
+        model = model.to(dev).eval()
+        d = make_batch(B, T, args.lengths, use_roi=False, seed=42 + rank)
+        hX, hL = torch.from_numpy(d["X"]).pin_memory(), torch.from_numpy(d["lengths"]).pin_memory()
+        X, L = hX.to(dev), hL.to(dev)
+        frames = int(d["lengths"].sum())
+
+        def step():
+            with torch.no_grad():
+                return model(X, L)
+        for _ in range(args.warmup):
+            step()
+        barrier()
+        c0 = ssb_lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local) as clk:
+            e0.record()
+            for _ in range(args.steps):
+                step()
+            e1.record()
+            barrier()
+            launches = ssb_lib.launch_count() - c0
+            ms = max_over_ranks(e0.elapsed_time(e1))
+            h_out = torch.empty(B, NUM_CLASSES, dtype=torch.float32).pin_memory()
+            model.infer_host(hX, hL, None, chunk=args.e2e_chunk, out=h_out)
+            barrier()
+            e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            n_e2e = max(2, min(args.steps, 5))
+            e2.record()
+            for _ in range(n_e2e):
+                model.infer_host(hX, hL, None, chunk=args.e2e_chunk, out=h_out)
+            e3.record()
+            barrier()
+            e2e_ms = max_over_ranks(e2.elapsed_time(e3))
+        # dominant HBM mover: the layer-1 projection GEMM (A [M,384] read + gi [M,1152] written), timed alone
+        passes = {"fp32": 0, "tc3": 3, "fp16": 1}[args.precision]
+        roofline = None
+        if passes == 1:
+            A1 = torch.randn(B * T, 384, device=dev)
+            packed = ops.proj_prepack(model.gru.weight_ih_l1, model.gru.weight_ih_l1_reverse, 384, 0)
+            gi = torch.empty(B * T, 1152, device=dev)
+            bias = torch.zeros(1152, device=dev)
+            for _ in range(2):
+                ops.proj_gemm(A1, packed, bias, gi, 1152, lengths=L, T=T)
+            torch.cuda.synchronize()
+            k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            k0.record()
+            for _ in range(3):
+                ops.proj_gemm(A1, packed, bias, gi, 1152, lengths=L, T=T)
+            k1.record()
+            torch.cuda.synchronize()
+            kms = k0.elapsed_time(k1) / 3
+            by = frames * (384 + 1152) * 4
+            roofline = {"kernel": "proj_gemm_kernel (layer 1)", "bound": "hbm", "achieved": by / kms / 1e6, "peak": peaks["hbm"],
+                        "unit": "GB/s", "frac": by / kms / 1e6 / peaks["hbm"], "traffic": None, "ms_per_launch": kms,
+                        "peak_src": f"{peaks['src']} copy bandwidth", "note": "algorithmic bytes = frames x (384 + 1152) x 4"}
+        if rank == 0:
+            line = {"metric": "inference_clips_per_sec", "value": B * world * args.steps / (ms / 1e3), "unit": "clips/s",
+                    "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+                    "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+                    "config": {"workload": "configs[3]: landmarks-only BiGRU (no ROI CNN), T=256", "clips_per_gpu": B, "frames": T,
+                               "lengths": "all=T" if args.lengths == "full" else "uniform[6,T]", "precision": args.precision,
+                               "l2": "inputs (0.75 GB/step) larger than L2"},
+                    "clocks": clk.summary(),
+                    "e2e": {"value": B * world * n_e2e / (e2e_ms / 1e3), "unit": "clips/s",
+                            "h2d_bytes_per_step": int(hX.numel() * 4 + hL.numel() * 8), "d2h_bytes_per_step": int(h_out.numel() * 4)},
+                    "gpu_launches": launches, "roofline": roofline, "cpu_baseline": None}
+            print(json.dumps(line), flush=True)
+    else:
+        from silent_speech_b200.streaming import StreamScheduler
+        S, W = args.batch or 1250, T_FRAMES
+        p = ref_model.synth_params(42)
+        model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=True, precision=args.precision)
+        model.load_state_dict(p)
+        model = model.to(dev).eval()
+        sch = StreamScheduler(model, S, max_t=W)
+        rng = np.random.default_rng(42 + rank)
+        pool = 8                                            # distinct synthetic frames per stream, cycled
+        hX = torch.from_numpy(rng.normal(0, 0.5, (pool, S, X_DIM)).astype(np.float32)).pin_memory()
+        hR = torch.from_numpy(rng.integers(0, 256, (pool, S, 48, 96)).astype(np.uint8)).pin_memory()
+        ids = np.arange(S)
+
+        def tick(k):
+            Xd, Rd = hX[k % pool].to(dev, non_blocking=True), hR[k % pool].to(dev, non_blocking=True)
+            due, logits = sch.tick(ids, Xd, Rd)
+            return due, (None if logits is None else logits.cpu())      # host copy of the predictions: e2e by construction
+        for k in range(W + 2 * args.warmup):                # fill every window, then warm up
+            tick(k)
+        barrier()
+        c0 = ssb_lib.launch_count()
+        lat, preds = [], 0
+        with ClockSampler(local) as clk:
+            t_all0 = time.perf_counter()
+            for k in range(2 * args.steps):                 # a step = two camera frames = one prediction per stream
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                due, _ = tick(W + 2 * args.warmup + k)
+                e1.record()
+                e1.synchronize()
+                lat.append(e0.elapsed_time(e1))
+                preds += int(due.size)
+            barrier()
+            wall_ms = (time.perf_counter() - t_all0) * 1e3
+        launches = ssb_lib.launch_count() - c0
+        ms = max_over_ranks(float(np.sum(lat)))
+        tot = torch.tensor([preds], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tot)
+        if rank == 0:
+            val = float(tot.item()) / (ms / 1e3)
+            line = {"metric": "stream_predictions_per_sec", "value": val, "unit": "window classifications/s", "n_gpus": world,
+                    "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                    "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+                    "config": {"workload": "configs[4]: sliding-window streams (live_feed.py policy: window 90, predict every 2nd frame)",
+                               "streams_per_gpu": S, "window": W, "step": "2 camera frames per stream",
+                               "precision": args.precision, "l2": "ring state 95 MB + 6.7 MB new frames per tick"},
+                    "clocks": clk.summary(),
+                    "tick_latency_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
+                                        "frames_per_sec_sustained_per_stream": 1e3 * len(lat) / wall_ms},
+                    "e2e": {"value": val, "unit": "window classifications/s",
+                            "h2d_bytes_per_step": int(2 * S * (X_DIM * 4 + 48 * 96)), "d2h_bytes_per_step": int(S * NUM_CLASSES * 4)},
+                    "gpu_launches": launches, "roofline": None, "cpu_baseline": None}
+            print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def metric_name(workload):
     return "train_step_samples_per_sec" if workload == "train" else "inference_clips_per_sec"
 
@@ -181,7 +336,9 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="infer", choices=["infer", "train"])
+    ap.add_argument("--workload", default="infer", choices=["infer", "train", "points256", "stream"],
+                    help="infer = configs[1] (default, the headline); train = configs[2]; points256 = configs[3] "
+                         "(landmarks-only, T=256); stream = configs[4] (sliding-window streams, 1,250 per GPU)")
     ap.add_argument("--batch", type=int, default=0, help="clips per GPU (default 4096 infer / 128 train)")
     ap.add_argument("--lengths", default="full", choices=["full", "uniform"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -193,6 +350,9 @@ def main():
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.workload in ("points256", "stream"):
+        run_extra(args, rank, world, local)
         return
 
     import torch.distributed as dist
