@@ -326,7 +326,7 @@ def workload_config(workload, B):
     if workload == "train":
         return {"workload": "configs[2]: full train step (fwd+bwd+clip+Adam) points+ROI model", "clips_per_gpu": B,
                 "frames": T_FRAMES, "lengths": "all=T", "l2": "inputs larger than L2"}
-    return {"workload": "configs[1]: batched inference word_model_points_roi, fp32", "clips_per_gpu": B,
+    return {"workload": "configs[1]: batched inference word_model_points_roi", "clips_per_gpu": B,
             "frames": T_FRAMES, "lengths": "all=T", "l2": "inputs (1.96 GB/step) larger than L2"}
 
 
@@ -343,9 +343,14 @@ def main():
     ap.add_argument("--lengths", default="full", choices=["full", "uniform"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-chunk", type=int, default=512, help="clips per pipelined host->device chunk in the e2e arm")
-    ap.add_argument("--precision", default="tc3", choices=["fp32", "tc3", "fp16"],
-                    help="fp32 = CUDA-core FMA; tc3 = tcgen05 split-fp16 (fp32-parity grade); fp16 = tcgen05 single pass")
+    ap.add_argument("--precision", default="", choices=["", "fp32", "tc3", "fp16"],
+                    help="fp16 = tcgen05 single pass, f16 operands / f32 accumulate (inference default; stated tolerance: logits "
+                         "within 1e-3 of max|logit| of the fp32 CPU reference, identical argmax -- tests/test_gpu_tensorcore.py); "
+                         "tc3 = tcgen05 split-fp16 x3, fp32-parity grade 1e-4 (training default; also measured and reported "
+                         "beside the inference headline); fp32 = CUDA-core FMA")
     args = ap.parse_args()
+    if not args.precision:
+        args.precision = "tc3" if args.workload == "train" else "fp16"
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
@@ -464,6 +469,27 @@ def main():
                 "note": "K2 (fused ROI CNN), algorithmic 5,309,952 FLOP/frame; step-level: %.1f TFLOP/s over %.0f MFLOP/clip" % (
                     FWD_FLOP_PER_FRAME * frames * world * args.steps / (ms / 1e3) / 1e12, FWD_FLOP_PER_FRAME * T_FRAMES / 1e6)}
 
+    # ---- the same batch in the fp32-parity mode (tc3), reported beside the fp16 headline
+    parity_mode = None
+    if args.workload == "infer" and args.precision == "fp16":
+        model.precision = "tc3"
+        for _ in range(2):
+            step()
+        barrier()
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n_par = max(2, min(args.steps, 4))
+        p0.record()
+        for _ in range(n_par):
+            step()
+        p1.record()
+        barrier()
+        t = torch.tensor([p0.elapsed_time(p1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        model.precision = "fp16"
+        parity_mode = {"precision": "tc3 (f16 hi/lo split x3, logits within 1e-4 of the fp32 CPU reference)",
+                       "value": B * world * n_par / (float(t.item()) / 1e3), "unit": "clips/s", "ms_per_step": float(t.item()) / n_par}
+
     clk.rows += clk2.rows                   # clocks sampled over both timed regions (device-resident and e2e)
     clocks = clk.summary()
     if rank == 0:
@@ -481,6 +507,8 @@ def main():
                 "clocks": clocks,
                 "e2e": {"value": e2e_val, "unit": "clips/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+        if parity_mode:
+            line["fp32_parity_mode"] = parity_mode
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

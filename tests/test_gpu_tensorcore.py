@@ -75,11 +75,12 @@ def test_gru_tc_recurrence_vs_fp32_kernel(B, T):
             assert eg < tol * 5, (passes, eg)
 
 
-@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("tc3", 1e-4), ("fp16", 2e-3)])
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("tc3", 1e-4), ("fp16", 1e-3)])
 @pytest.mark.parametrize("use_roi,B,T,mode", [(True, 150, 90, "uniform"), (False, 260, 64, "uniform")])
 def test_model_logits_by_precision(precision, tol, use_roi, B, T, mode):
     """fp32 and tc3 (split-bf16 on the tensor cores) must meet the 1e-4 logits bar with identical argmax;
-    fp16 (single pass) is the fast mode with its own stated tolerance: 2e-3 of max |logit|, >= 99 % argmax agreement."""
+    fp16 (single pass, the inference bench default) has its own stated tolerance: 1e-3 of max |logit| and identical
+    argmax on this batch (measured ~3e-4)."""
     import os
     dev = _cuda()
     from oracle import ref_model
@@ -100,7 +101,7 @@ def test_model_logits_by_precision(precision, tol, use_roi, B, T, mode):
     agree = (logits.argmax(1).cpu() == ref.argmax(1)).float().mean().item()
     print(f"precision={precision} roi={use_roi} rel_err={e:.3e} argmax_agree={agree:.4f}")
     assert e < tol, e
-    assert agree == 1.0 if precision != "fp16" else agree >= 0.99
+    assert agree == 1.0
 
 
 @pytest.mark.parametrize("version", [1, 2, 3])
