@@ -9,7 +9,8 @@
 //   dgi[t]  = (dr~, dz~, dn~)                  -> feeds dW_ih, db_ih, d(input) as GEMMs
 //   dgh[t]  = (dr~, dz~, dn~ r)                -> feeds dW_hh, db_hh as GEMMs (with h_prev[t])
 //   dh_carry = dh z + dgh[t] W_hh              <- the only serial part, done here
-// Work split as in the forward kernel: one CTA = 64 clips x one direction, 512 threads, thread
+// Work split: one CTA = BT clips x one direction, 8 BT threads (BT = 64, 16 or 8, picked so that the grid covers
+// the SMs: the serial product is FMA-issue-bound per CTA, so small batches want MANY small tiles), thread
 // (cg, ug) owns units 3ug..3ug+2 of clips 8cg..8cg+7; dh stays in registers; dgh of the step is
 // shared through smem; W_hh^T streams from L2 in k chunks (cp.async double buffer).
 #include "common.cuh"
@@ -18,10 +19,11 @@ namespace ssb {
 namespace gru {
 
 constexpr int H = kHidden, G3 = 3 * H;
-constexpr int BT = 64, THREADS = 512, KC = 16, WLD = KC + 4;
+constexpr int KC = 16, WLD = KC + 4;
 constexpr int DLD = G3 + 4;            // padded dgh row
 constexpr int NCHUNK_B = G3 / KC;      // 36
 
+template <int BT>
 struct SmemB {
   float dgh[BT][DLD];
   float w[2][H][WLD];
@@ -35,6 +37,7 @@ __device__ __forceinline__ void cp_async16b(void* smem, const void* gmem) {
 }
 
 // whhT: [H][G3] (transposed recurrent weights): chunk = rows j (192) x 16 k
+template <int THREADS>
 __device__ __forceinline__ void stage_wT(float (*dst)[WLD], const float* __restrict__ whhT, int chunk, int tid) {
   for (int p = tid; p < H * (KC / 4); p += THREADS) {
     const int row = p >> 2, q = p & 3;
@@ -42,13 +45,15 @@ __device__ __forceinline__ void stage_wT(float (*dst)[WLD], const float* __restr
   }
 }
 
-__global__ void __launch_bounds__(THREADS, 1)
+template <int BT>
+__global__ void __launch_bounds__(BT * 8, 1)
 gru_rec_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ out, const float* __restrict__ gates,
                    const float* __restrict__ whhT_f, const float* __restrict__ whhT_r,
                    const int64_t* __restrict__ lengths, int B, int T,
                    float* __restrict__ dgi, float* __restrict__ dghn, float* __restrict__ hprev) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  SmemB& s = *reinterpret_cast<SmemB*>(smem_raw);
+  constexpr int THREADS = BT * 8;
+  SmemB<BT>& s = *reinterpret_cast<SmemB<BT>*>(smem_raw);
   const int tid = threadIdx.x, dir = blockIdx.y, b0 = blockIdx.x * BT;
   const float* __restrict__ whhT = dir ? whhT_r : whhT_f;
   const int ug = tid & 63, cg = tid >> 6, j0 = ug * 3, c0 = cg * 8;
@@ -111,12 +116,12 @@ gru_rec_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ out
     for (int u = 0; u < 3; ++u)
 #pragma unroll
       for (int c = 0; c < 8; ++c) acc[u][c] = 0.f;
-    stage_wT(s.w[0], whhT, 0, tid);
+    stage_wT<THREADS>(s.w[0], whhT, 0, tid);
     asm volatile("cp.async.commit_group;\n" ::);
 #pragma unroll 1
     for (int ch = 0; ch < NCHUNK_B; ++ch) {
       if (ch + 1 < NCHUNK_B) {
-        stage_wT(s.w[(ch + 1) & 1], whhT, ch + 1, tid);
+        stage_wT<THREADS>(s.w[(ch + 1) & 1], whhT, ch + 1, tid);
         asm volatile("cp.async.commit_group;\n" ::);
         asm volatile("cp.async.wait_group 1;\n" ::);
       } else {
@@ -205,10 +210,19 @@ extern "C" int ssb_gru_layer_bwd(const float* dout, const float* out, const floa
   SSB_REQUIRE(hidden == H, "hidden must be 192");
   SSB_REQUIRE(((uintptr_t)whhT_f & 15) == 0 && ((uintptr_t)whhT_r & 15) == 0, "W_hh^T must be 16-byte aligned");
   if (B == 0) return SSB_OK;
-  SSB_CUDA(cudaFuncSetAttribute(gru_rec_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemB)));
-  dim3 grid(cdiv(B, BT), 2), block(THREADS);
-  gru_rec_bwd_kernel<<<grid, block, sizeof(SmemB), (cudaStream_t)stream>>>(
-      dout, out, gates, whhT_f, whhT_r, lengths, (int)B, (int)T, dgi, dghn, hprev);
+  // tile size: the largest one whose grid still covers the SMs (smaller tiles = more CTAs sharing the serial FMA work)
+#define SSB_LAUNCH_GRUBWD(BT_)                                                                                         \
+  do {                                                                                                                  \
+    SSB_CUDA(cudaFuncSetAttribute(gru_rec_bwd_kernel<BT_>, cudaFuncAttributeMaxDynamicSharedMemorySize,                 \
+                                  (int)sizeof(SmemB<BT_>)));                                                            \
+    dim3 grid(cdiv(B, BT_), 2), block(BT_ * 8);                                                                         \
+    gru_rec_bwd_kernel<BT_><<<grid, block, sizeof(SmemB<BT_>), (cudaStream_t)stream>>>(                                 \
+        dout, out, gates, whhT_f, whhT_r, lengths, (int)B, (int)T, dgi, dghn, hprev);                                   \
+  } while (0)
+  if (cdiv(B, 64) * 2 >= kSMs) SSB_LAUNCH_GRUBWD(64);
+  else if (cdiv(B, 16) * 2 >= kSMs) SSB_LAUNCH_GRUBWD(16);
+  else SSB_LAUNCH_GRUBWD(8);
+#undef SSB_LAUNCH_GRUBWD
   SSB_LAUNCH_CHECK();
   return SSB_OK;
 }
