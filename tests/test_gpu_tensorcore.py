@@ -44,7 +44,7 @@ def test_gemm_tc_vs_fp64(M, N, K1, K2):
         assert rel_err(C, A[:Mr].double() @ W.double().T + 1.0) < 2e-5
 
 
-@pytest.mark.parametrize("B,T", [(5, 7), (200, 23)])
+@pytest.mark.parametrize("B,T", [(5, 7), (200, 23), (700, 40)])
 def test_gru_tc_recurrence_vs_fp32_kernel(B, T):
     dev = _cuda()
     from oracle import ref_model

@@ -43,6 +43,26 @@ if a.stage == "cnn":
     best, mean = timeit(lambda: ops.roi_cnn_fwd(R, L, w, passes=passes))
     fl = 5_309_952 * int(L.sum())
     print(f"cnn {a.precision} B={B}: best {best:.3f} ms mean {mean:.3f} ms  {fl / best / 1e9:.1f} TFLOP/s algorithmic")
+elif a.stage == "features":
+    from silent_speech_b200 import extract_features
+    lm_h, present_h = synth.landmarks(min(B, 64), T, seed=1)
+    reps = (B + lm_h.shape[0] - 1) // lm_h.shape[0]
+    lm = torch.from_numpy(lm_h).to(dev).repeat(reps, 1, 1, 1)[:B].contiguous()
+    present = torch.from_numpy(present_h).to(dev).repeat(reps, 1)[:B].contiguous()
+    best, mean = timeit(lambda: extract_features(lm, synth.FRAME_W, synth.FRAME_H, present=present))
+    fr = B * T
+    print(f"features B={B}: best {best:.3f} ms mean {mean:.3f} ms  {fr * 1424 / best / 1e6:.0f} GB/s algorithmic (1,424 B/frame), "
+          f"{fr * (478 * 12 + 720 + 13) / best / 1e6:.0f} GB/s of touched rows (5,736 B landmark row + outputs)")
+elif a.stage == "crop":
+    from silent_speech_b200 import crop_rois
+    N = min(B, 2048)
+    frames = torch.randint(0, 256, (N, 720, 1280, 3), dtype=torch.uint8, device=dev)
+    g = torch.Generator().manual_seed(0)
+    centers = torch.stack([torch.rand(N, generator=g) * 900 + 190, torch.rand(N, generator=g) * 400 + 160], 1).to(dev)
+    mw = (torch.rand(N, generator=g, dtype=torch.float64) * 90 + 60).to(dev)
+    best, mean = timeit(lambda: crop_rois(frames, centers, mw, flavor="live"))
+    by = float((2.4 * mw * 2.0 * mw * 3).sum()) + N * 4608
+    print(f"crop N={N}: best {best:.3f} ms mean {mean:.3f} ms  {by / best / 1e6:.0f} GB/s algorithmic (3 x crop area in + 4,608 B out), {N / best * 1e3:.0f} crops/s")
 elif a.stage == "proj":
     K1, K2 = (180, 32) if a.layer == 0 else (384, 0)
     A1 = torch.randn(B * T, K1, device=dev)
