@@ -11,15 +11,17 @@
 //   LINEAR 11-bit fixed point: rows = S[x0] c0 + S[x1] c1; out = ((b0 (r0>>4))>>16 + (b1 (r1>>4))>>16 + 2) >> 2;
 //          x fractions forced to 0 outside the image, y keeps the fraction and clips the row index; exact 2x
 //          shrinking is routed to AREA.
-// One CTA per crop: the gray crop is staged in shared memory (coalesced BGR row reads, each source byte read from
-// HBM once), then one thread per output pixel.  HBM-bound: 3 x crop area bytes in, 4,608 bytes out.
+// Four CTAs per crop (12 output rows each, so that ~5 CTAs are resident per SM and hide each other's latency): the
+// band of gray source rows a CTA needs is staged in shared memory (each source byte read about once), then one
+// thread per output pixel.  HBM-bound: 3 x crop area bytes in, 4,608 bytes out.
 #include "common.cuh"
 
 namespace ssb {
 namespace crop {
 
 constexpr int DW = 96, DH = 48, THREADS = 256;
-constexpr int STAGE_MAX = 160 * 1024;                      // gray crop staged in smem up to this many pixels
+constexpr int SPLIT = 4, ROWS = DH / SPLIT;                 // a crop is shared by 4 CTAs of 12 output rows each
+constexpr int STAGE_MAX = 40 * 1024;                       // gray band staged in smem up to this many pixels (else global reads)
 
 struct Tab {                                               // one axis of the resize
   // area (shrinking): source cell of destination index d: [optional left partial] full cells [optional right partial]
@@ -86,6 +88,7 @@ __global__ void __launch_bounds__(THREADS) roi_crop_kernel(
   Sh& sh = *reinterpret_cast<Sh*>(smem);
   unsigned char* gray_s = smem + sizeof(Sh);
   const int n = blockIdx.x, tid = threadIdx.x;
+  const int dy0 = blockIdx.y * ROWS, dy1 = dy0 + ROWS;   // this CTA's output rows
   const unsigned char* frame = frames + (size_t)(frame_index ? frame_index[n] : n) * Hf * Wf * 3;
   unsigned char* o = out + (size_t)n * DW * DH;
 
@@ -115,11 +118,11 @@ __global__ void __launch_bounds__(THREADS) roi_crop_kernel(
       else mode = (sw == 2 * DW && shh == 2 * DH) ? 1 : 2;
       sh.mode = mode; sh.ix = ix; sh.iy = iy;
     }
-    if (ok_out) ok_out[n] = (unsigned char)ok;
+    if (ok_out && blockIdx.y == 0) ok_out[n] = (unsigned char)ok;
   }
   __syncthreads();
   if (!sh.ok) {                                            // the callers substitute a zero frame (live:290-293)
-    for (int i = tid; i < DW * DH / 4; i += THREADS) reinterpret_cast<uint32_t*>(o)[i] = 0u;
+    for (int i = tid; i < DW * ROWS / 4; i += THREADS) reinterpret_cast<uint32_t*>(o + dy0 * DW)[i] = 0u;
     return;
   }
   const int x1 = sh.box[0], y1 = sh.box[1], sw = sh.box[2] - sh.box[0], shh = sh.box[3] - sh.box[1];
@@ -133,19 +136,50 @@ __global__ void __launch_bounds__(THREADS) roi_crop_kernel(
     if (mode == 0) area_entry(sh.y, d, shh, 1.0 / ((double)DH / shh));
     else if (mode == 2) linear_entry(sh.y, d, shh, DH, false, flavor == 0);
   }
-  // ---- gray crop -> shared memory (each source byte is read once, rows are contiguous 3*sw-byte runs)
-  const bool staged = sw * shh <= STAGE_MAX;
+  __syncthreads();
+  // ---- band of source rows this CTA's output rows read
+  int ylo, yhi;
+  if (mode == 0) { ylo = sh.y.s0[dy0]; yhi = sh.y.s0[dy1 - 1] + sh.y.n[dy1 - 1]; }
+  else if (mode == 1) { ylo = dy0 * sh.iy; yhi = dy1 * sh.iy; }
+  else {
+    ylo = shh; yhi = 0;
+    for (int d = dy0; d < dy1; ++d) { ylo = min(ylo, min(sh.y.i0[d], sh.y.i1[d])); yhi = max(yhi, max(sh.y.i0[d], sh.y.i1[d]) + 1); }
+  }
+  const int band = yhi - ylo;
+  // ---- gray band -> shared memory (rows are contiguous 3*sw-byte runs; a warp takes two rows per pass, a lane four
+  // pixels per row: 24 independent byte loads in flight per thread)
+  const bool staged = sw * band <= STAGE_MAX;
   if (staged) {
-    for (int y = tid / 32; y < shh; y += THREADS / 32) {
-      const unsigned char* row = frame + ((size_t)(y1 + y) * Wf + x1) * 3;
-      for (int x = tid % 32; x < sw; x += 32) gray_s[y * sw + x] = (unsigned char)gray_of(row + 3 * x);
+    constexpr int NW = THREADS / 32;
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int y = warp; y < band; y += 2 * NW) {
+      const int yb = y + NW;
+      const unsigned char* row_a = frame + ((size_t)(y1 + ylo + y) * Wf + x1) * 3;
+      const unsigned char* row_b = frame + ((size_t)(y1 + ylo + min(yb, band - 1)) * Wf + x1) * 3;
+      for (int xs = 0; xs < sw; xs += 128) {
+        int ga[4], gb[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int x = min(xs + lane + 32 * u, sw - 1);
+          ga[u] = gray_of(row_a + 3 * x);
+          gb[u] = gray_of(row_b + 3 * x);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int x = xs + lane + 32 * u;
+          if (x < sw) {
+            gray_s[y * sw + x] = (unsigned char)ga[u];
+            if (yb < band) gray_s[yb * sw + x] = (unsigned char)gb[u];
+          }
+        }
+      }
     }
   }
   __syncthreads();
   auto G = [&](int y, int x) -> int {
-    return staged ? (int)gray_s[y * sw + x] : gray_of(frame + ((size_t)(y1 + y) * Wf + x1 + x) * 3);
+    return staged ? (int)gray_s[(y - ylo) * sw + x] : gray_of(frame + ((size_t)(y1 + y) * Wf + x1 + x) * 3);
   };
-  for (int p = tid; p < DW * DH; p += THREADS) {
+  for (int p = dy0 * DW + tid; p < dy1 * DW; p += THREADS) {
     const int dy = p / DW, dx = p % DW;
     int res;
     if (mode == 1) {
@@ -199,7 +233,7 @@ extern "C" int ssb_roi_crop(const uint8_t* frames, const int32_t* frame_index, i
   if (N == 0) return SSB_OK;
   const size_t smem = sizeof(Sh) + STAGE_MAX;
   SSB_CUDA(cudaFuncSetAttribute(roi_crop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  roi_crop_kernel<<<(unsigned)N, THREADS, smem, (cudaStream_t)stream>>>(frames, frame_index, (int)Hf, (int)Wf, centers, mouth_w,
+  roi_crop_kernel<<<dim3((unsigned)N, SPLIT), THREADS, smem, (cudaStream_t)stream>>>(frames, frame_index, (int)Hf, (int)Wf, centers, mouth_w,
                                                                       flavor, out, ok);
   SSB_LAUNCH_CHECK();
   return SSB_OK;
