@@ -18,6 +18,11 @@ H = ops.HIDDEN
 G3 = 3 * H
 
 
+def _passes(model):
+    """(CNN passes, GRU passes) of a precision mode: 0 = fp32 CUDA cores, 1 = single fp16 pass, 3 = hi/lo split."""
+    return {"fp32": (0, 0), "tc3": (3, 3), "fp16": (1, 1), "cnn16": (1, 3), "gru16": (3, 1)}[getattr(model, "precision", "fp32")]
+
+
 class Workspace:
     """Per-call buffers (allocated by PyTorch's caching allocator; the library owns nothing)."""
 
@@ -53,14 +58,13 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
     elif R is not None:
         R = R.to(dev).contiguous()
         emb = ops.roi_cnn_fwd(R, lengths, model.roi_cnn.tensors(), standardize=model.standardize_roi,
-                              passes={"fp32": 0, "tc3": 3, "fp16": 1}[getattr(model, "precision", "fp32")])
+                              passes=_passes(model)[0])
         ctx["R"] = R
         ctx["emb"] = emb
     gi = torch.empty(B, T, 2 * G3, device=dev, dtype=torch.float32)
     gi2d = gi.view(B * T, 2 * G3)
     p0, p1 = model.gru.layer(0), model.gru.layer(1)
-    prec = getattr(model, "precision", "fp32")
-    passes = {"fp32": 0, "tc3": 3, "fp16": 1}[prec]
+    passes = _passes(model)[1]
     order = None
     if passes and B > 128:      # homogeneous 128-clip tiles: each cluster runs max(len in tile) steps
         order = torch.argsort(lengths, descending=True).to(torch.int32)

@@ -93,7 +93,7 @@ class StreamScheduler:
             emb = None
             if self.de:
                 Rs = R if all_found else R[torch.from_numpy(sel).to(R.device)]
-                passes = {"fp32": 0, "tc3": 3, "fp16": 1}[self.model.precision]
+                passes = F_ssb._passes(self.model)[0]
                 emb = ops.roi_cnn_fwd(Rs.view(a.size, 1, *Rs.shape[1:]).contiguous(), None, self.model.roi_cnn.tensors(),
                                       standardize=self.model.standardize_roi, passes=passes).view(a.size, self.de)
             ops.ring_push(self.ring, self._i32(a), self._i32(pos), Xs.contiguous().float(), emb)
