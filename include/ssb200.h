@@ -193,6 +193,16 @@ int ssb_ring_gather(const float* ring, int64_t W, int64_t D, const int32_t* sid,
                     const int32_t* count, int64_t m, float* Xw, int64_t dx, float* Ew, int64_t de,
                     int64_t T, int64_t* lengths, void* stream);
 
+/* Training augmentation of the point features on the device: the policy of NPZWordDataset.__getitem__
+ * (train_model_official.py:143-152): N(0, noise_std) noise with probability p_noise; if T > 12, with probability p_drop
+ * 1..drop_max frames from [1, T-2] are removed from X; the ROI clip is only cut to the new length (the reference does
+ * not thin it).  Counter-based RNG in (seed, clip); decisions i32 [B,4] = {noise, k, drop_0, drop_1} (nullable).
+ * Xo must not alias X; R (nullable) is modified in place. */
+int ssb_augment_clips(const float* X, const int64_t* lengths, int64_t B, int64_t T, int64_t D,
+                      uint8_t* R, int64_t roi_frame_bytes, uint64_t seed, float p_noise, float noise_std,
+                      float p_drop, int32_t drop_max, float* Xo, int64_t* lengths_out, int32_t* decisions,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif

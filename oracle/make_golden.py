@@ -196,6 +196,39 @@ def golden_roi_crop_many(live, record):
     print("roi_crop_many.npz", int(np.sum(ok_live)), int(np.sum(ok_rec)))
 
 
+def golden_augment(train):
+    """NPZWordDataset.__getitem__ (train:133-172) on temporary .npz clips with its random calls scripted, so that the
+    decisions are known: (noise?, drops) per clip.  Stores inputs, decisions, the injected noise and the outputs."""
+    import random as pyrandom
+    rng = np.random.default_rng(13)
+    tmp = tempfile.mkdtemp()
+    cases = [(30, False, []), (30, True, [5]), (40, True, [1, 38]), (12, True, []), (90, False, [44, 45]), (20, False, [18])]
+    rec = {"X": [], "R": [], "T": [], "noise_on": [], "noise": [], "drops": [], "X_out": [], "T_out": [], "R_out": []}
+    real = (pyrandom.random, pyrandom.randint, np.random.normal, np.random.choice)
+    try:
+        for i, (T, noise_on, drops) in enumerate(cases):
+            X = rng.normal(0, 0.3, (T, 180)).astype(np.float32)
+            R = ((np.arange(T)[:, None, None] * 7 + np.arange(48)[None, :, None] + 3 * np.arange(96)[None, None, :]) % 256).astype(np.uint8)
+            path = os.path.join(tmp, f"c{i}.npz")
+            np.savez(path, X=X, roi=R, label="w")
+            noise = rng.normal(0, 0.01, (T, 180))
+            seq = iter([0.0 if noise_on else 0.99, 0.0 if drops else 0.99])
+            pyrandom.random = lambda: next(seq)
+            pyrandom.randint = lambda a, b, k=len(drops): k
+            np.random.normal = lambda m, s_, size, nz=noise: nz
+            np.random.choice = lambda a, size, replace, d=drops: np.array(d)
+            ds = train.NPZWordDataset([path], {"w": 0}, max_t=90, augment=True, use_roi=True)
+            Xo, To, Ro, _ = ds[0]
+            rec["X"].append(np.pad(X, ((0, 90 - T), (0, 0)))); rec["R"].append(np.pad(R, ((0, 90 - T), (0, 0), (0, 0))))
+            rec["T"].append(T); rec["noise_on"].append(noise_on); rec["noise"].append(np.pad(noise.astype(np.float32), ((0, 90 - T), (0, 0))))
+            rec["drops"].append(drops + [-1] * (2 - len(drops)))
+            rec["X_out"].append(Xo.numpy()); rec["T_out"].append(int(To)); rec["R_out"].append(Ro.numpy())
+    finally:
+        pyrandom.random, pyrandom.randint, np.random.normal, np.random.choice = real
+    np.savez_compressed(os.path.join(OUT, "augment.npz"), **{k: np.array(v) for k, v in rec.items()})
+    print("augment.npz", rec["T_out"])
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     train, live, record = import_reference()
@@ -206,6 +239,7 @@ def main():
     golden_model(train, live, "roi_hot", True, B=3, T=10, lens=[7, 10, 3], seed=103, scale=2.0)
     golden_roi_crop(live, record)
     golden_roi_crop_many(live, record)
+    golden_augment(train)
 
 
 if __name__ == "__main__":

@@ -327,3 +327,23 @@ def ring_gather(ring: torch.Tensor, sid: torch.Tensor, start: torch.Tensor, coun
     check(_lib.lib().ssb_ring_gather(ptr(ring), i64(W), i64(D), ptr(sid), ptr(start), ptr(count), i64(m), ptr(Xw), i64(dx),
                                      ptr(Ew), i64(de), i64(T), ptr(lengths), stream_ptr()))
     return Xw, Ew, lengths
+
+
+# ----------------------------------------------------------------------------- augmentation
+def augment_clips(X: torch.Tensor, lengths: torch.Tensor, R: Optional[torch.Tensor], seed: int, p_noise: float = 0.7,
+                  noise_std: float = 0.01, p_drop: float = 0.35, drop_max: int = 2):
+    """NPZWordDataset's augmentation (train_model_official.py:143-152) for a whole batch on the device.
+    -> (X_aug f32 [B,T,D], lengths_out i64 [B], decisions i32 [B,4]); R (u8 [B,T,48,96] or None) is cut in place."""
+    _need(X, torch.float32, "X"); _need(lengths, torch.int64, "lengths")
+    B, T, D = X.shape
+    fb = 0
+    if R is not None:
+        _need(R, torch.uint8, "R")
+        fb = R[0, 0].numel()
+    Xo = torch.empty_like(X)
+    lo = torch.empty_like(lengths)
+    dec = torch.empty(B, 4, device=X.device, dtype=torch.int32)
+    check(_lib.lib().ssb_augment_clips(ptr(X), ptr(lengths), i64(B), i64(T), i64(D), ptr(R), i64(fb), u64(seed & 0xFFFFFFFFFFFFFFFF),
+                                       f32(p_noise), f32(noise_std), f32(p_drop), i32(drop_max), ptr(Xo), ptr(lo), ptr(dec),
+                                       stream_ptr()))
+    return Xo, lo, dec

@@ -99,9 +99,14 @@ class Trainer:
         backward_impl(model, ctx, self.buckets.grads, y=y, label_smoothing=self.ls, grad_scale=1.0 / gb)
         return out["loss"], out["logits"]
 
-    def step(self, X, lengths, R, y, global_batch: Optional[int] = None):
-        """One full train step on this rank's shard; returns the local per-clip losses."""
+    def step(self, X, lengths, R, y, global_batch: Optional[int] = None, augment_seed: Optional[int] = None):
+        """One full train step on this rank's shard; returns the local per-clip losses.
+        augment_seed: apply NPZWordDataset's augmentation (train_model_official.py:143-152: noise p=0.7, 1-2 dropped
+        frames p=0.35) to the batch on the device first; R is then cut in place to the new lengths."""
         c0 = _lib.launch_count()
+        if augment_seed is not None:
+            lengths = lengths.to(device=X.device, dtype=torch.int64).contiguous()
+            X, lengths, _ = ops.augment_clips(X.contiguous().float(), lengths, R if self.model.use_roi else None, augment_seed)
         loss, _ = self.forward_backward(X, lengths, R, y, global_batch)
         if self.world > 1:
             dist.all_reduce(self.buckets.grad, op=dist.ReduceOp.SUM)       # 4.76 MB over NVLink / NVSwitch

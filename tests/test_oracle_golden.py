@@ -115,3 +115,18 @@ def test_roi_crop_oracle_matches_cv2_on_seeded_sizes():
         src = np.ascontiguousarray(g[y:y + h, x:x + w])
         assert np.array_equal(cv2.resize(src, (96, 48), interpolation=cv2.INTER_AREA), rc.resize_area(src)), (w, h)
         assert np.array_equal(cv2.resize(src, (96, 48)), rc.resize_linear(src)), (w, h)
+
+
+# ------------------------------------------------------------------ augmentation
+def test_augment_oracle_matches_reference_getitem(golden_dir):
+    """oracle/ref_augment.py against NPZWordDataset.__getitem__ run with scripted random decisions."""
+    from oracle import ref_augment as ra
+    g = _load(golden_dir, "augment.npz")
+    for i in range(len(g["T"])):
+        T = int(g["T"][i])
+        drops = [int(d) for d in g["drops"][i] if d >= 0]
+        noise = g["noise"][i][:T] if g["noise_on"][i] else None
+        Xo, To, Ro = ra.augment_clip(g["X"][i][:T], g["R"][i][:T], 90, noise, drops)
+        assert To == int(g["T_out"][i])
+        assert np.array_equal(Xo, g["X_out"][i])
+        assert np.array_equal(Ro, g["R_out"][i])
