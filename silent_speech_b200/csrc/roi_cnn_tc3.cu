@@ -100,9 +100,10 @@ __device__ __forceinline__ void build_weights(uint8_t* w1op, uint8_t* w2op, uint
       const float w = (dy >= 0 && dy < 3 && dx >= 0 && dx < 3) ? g.w1[co * 9 + dy * 3 + dx] : 0.f;
       tc::split_bf16(w, hi[e], lo[e]);
     }
-    const uint32_t off = kc * W1_CHUNK + (n >> 3) * 128 + (n & 7) * 16;
+    // split mode: rows [0,32) of a k-chunk = hi, rows [32,64) = lo, so that A_hi . [B_hi | B_lo] is ONE MMA with N = 64
+    const uint32_t off = kc * (L::P * W1_CHUNK) + (n >> 3) * 128 + (n & 7) * 16;
     *reinterpret_cast<uint4*>(w1op + off) = pack8(hi);
-    if (kSplit) *reinterpret_cast<uint4*>(w1op + W1_BYTES + off) = pack8(lo);
+    if (kSplit) *reinterpret_cast<uint4*>(w1op + W1_CHUNK + off) = pack8(lo);
   }
   // conv2: row n = sub*16 + co, k-chunk = patch element r*4 + c, 8 input channels per chunk
   for (int idx = tid; idx < 64 * 16; idx += nthreads) {
@@ -112,9 +113,9 @@ __device__ __forceinline__ void build_weights(uint8_t* w1op, uint8_t* w2op, uint
     float hi[8], lo[8];
 #pragma unroll
     for (int ci = 0; ci < 8; ++ci) tc::split_bf16(in ? g.w2[(co * C1 + ci) * 9 + dy * 3 + dx] : 0.f, hi[ci], lo[ci]);
-    const uint32_t off = kc * W2_CHUNK + (n >> 3) * 128 + (n & 7) * 16;
+    const uint32_t off = kc * (L::P * W2_CHUNK) + (n >> 3) * 128 + (n & 7) * 16;     // split: rows [0,64) hi, [64,128) lo
     *reinterpret_cast<uint4*>(w2op + off) = pack8(hi);
-    if (kSplit) *reinterpret_cast<uint4*>(w2op + W2_BYTES + off) = pack8(lo);
+    if (kSplit) *reinterpret_cast<uint4*>(w2op + W2_CHUNK + off) = pack8(lo);
   }
   // conv3: chunk = tap*2 + channel plane; rows co (hi), co + 32 (lo, kSplit); other rows zero
   for (int idx = tid; idx < L::W3_ROWS * 18; idx += nthreads) {
@@ -137,8 +138,9 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   constexpr int NWG = ST / 128;                        // warps per TMEM lane quarter
   constexpr int WPT = (NPIX / 4 + ST - 1) / ST;        // 4-pixel words per thread: 9 (ST=128) or 5 (ST=256)
   constexpr int TMEM_PER_SLOT = 512 / kSlots;
-  constexpr bool kPipe2 = TMEM_PER_SLOT < 192;         // conv2's three 64-column tiles do not fit: commit tile by tile
-  static_assert(TMEM_PER_SLOT >= 128, "a slot needs 128 TMEM columns");
+  constexpr bool kPipe2 = TMEM_PER_SLOT < 3 * (kSplit ? 128 : 64);   // conv2's three tiles do not fit: commit tile by tile
+  static_assert(TMEM_PER_SLOT >= 2 * (kSplit ? 128 : 64), "a slot needs two conv2 tiles of TMEM columns");
+  static_assert(kPipe2, "the non-pipelined conv2 path was removed");
   constexpr int GIT = L::STRIP_TILES * 256 / ST;       // gather items per thread in a full conv1 round
   constexpr int E1 = (L::STRIP_TILES + NWG - 1) / NWG; // conv1 epilogue tiles per thread in a full round
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -170,6 +172,8 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   const uint32_t r0_u = tc::smem_u32(r0), a1_u = tc::smem_u32(a1);
   const uint32_t w1_u = tc::smem_u32(w1op), w2_u = tc::smem_u32(w2op), w3_u = tc::smem_u32(w3op);
   constexpr uint32_t idesc1 = tc::make_idesc_bf16(128, 32), idesc2 = tc::make_idesc_bf16(128, 64);
+  constexpr uint32_t idesc1s = tc::make_idesc_bf16(128, 64), idesc2s = tc::make_idesc_bf16(128, 128);   // hi|lo stacked along N
+  constexpr int C1W = kSplit ? 64 : 32, C2W = kSplit ? 128 : 64;        // TMEM columns per conv1 / conv2 tile
   constexpr uint32_t idesc3_hi = tc::make_idesc_bf16(128, kSplit ? 64 : 32), idesc3_lo = tc::make_idesc_bf16(128, 32);
   constexpr int COLS3 = kSplit ? 64 : 32;
   uint32_t ph0 = 0, ph1 = 0;
@@ -365,13 +369,14 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         tc::fence_after_sync();
         for (int tl = 0; tl < ntiles; ++tl) {
           const uint64_t ah = tc::make_desc(r0_u + L::OFF_PATCH + tl * 2048, L::PATCH_CHUNK, 128);
-          const uint64_t bh = tc::make_desc(w1_u, W1_CHUNK, 128);
-          tc::mma_bf16(tmem + tl * 32, ah, bh, idesc1, false);
+          const uint64_t bh = tc::make_desc(w1_u, L::P * W1_CHUNK, 128);
           if (kSplit) {
+            // columns [0,32) = A_hi.B_hi (+ A_lo.B_hi), columns [32,64) = A_hi.B_lo; the epilogue adds the halves
             const uint64_t al = tc::make_desc(r0_u + L::OFF_PATCH + L::PATCH_BYTES + tl * 2048, L::PATCH_CHUNK, 128);
-            const uint64_t bl = tc::make_desc(w1_u + W1_BYTES, W1_CHUNK, 128);
-            tc::mma_bf16(tmem + tl * 32, ah, bl, idesc1, true);
-            tc::mma_bf16(tmem + tl * 32, al, bh, idesc1, true);
+            tc::mma_bf16(tmem + tl * C1W, ah, bh, idesc1s, false);
+            tc::mma_bf16(tmem + tl * C1W, al, bh, idesc1, true);
+          } else {
+            tc::mma_bf16(tmem + tl * C1W, ah, bh, idesc1, false);
           }
         }
         tc::mma_commit(&mz.bar[0]);
@@ -384,8 +389,16 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         const int tl = wg + k * NWG;
         if (tl < ntiles) {
           float v[32];
-          tc::tmem_ld32(tq + tl * 32, v);
-          tc::tmem_ld_wait();
+          tc::tmem_ld32(tq + tl * C1W, v);
+          if (kSplit) {
+            float w[32];
+            tc::tmem_ld32(tq + tl * C1W + 32, w);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] += w[i];
+          } else {
+            tc::tmem_ld_wait();
+          }
           float hi[8], lo[8];
 #pragma unroll
           for (int co = 0; co < 8; ++co) {
@@ -421,48 +434,67 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         for (int h = 0; h < 2; ++h) {
           // patch elements (r, 2h) and (r, 2h+1): column-parity planes 0 and 1 of row-parity plane r&1
           const uint32_t a_off = (r & 1) * 2 * P1_PLANE + ((r >> 1) * P1_COLS + h) * 16 + tl * 2048;
-          const uint32_t b_off = (r * 4 + 2 * h) * W2_CHUNK;
+          const uint32_t b_off = (r * 4 + 2 * h) * (L::P * W2_CHUNK);
           const uint64_t ah = tc::make_desc(a1_u + a_off, P1_PLANE, 128);
-          const uint64_t bh = tc::make_desc(w2_u + b_off, W2_CHUNK, 128);
-          tc::mma_bf16(tmem + dcol, ah, bh, idesc2, (r | h) != 0);
+          const uint64_t bh = tc::make_desc(w2_u + b_off, L::P * W2_CHUNK, 128);
           if (kSplit) {
+            // columns [0,64) = A_hi.B_hi + A_lo.B_hi, columns [64,128) = A_hi.B_lo
             const uint64_t al = tc::make_desc(a1_u + A1_BYTES + a_off, P1_PLANE, 128);
-            const uint64_t bl = tc::make_desc(w2_u + W2_BYTES + b_off, W2_CHUNK, 128);
-            tc::mma_bf16(tmem + dcol, ah, bl, idesc2, true);
+            tc::mma_bf16(tmem + dcol, ah, bh, idesc2s, (r | h) != 0);
             tc::mma_bf16(tmem + dcol, al, bh, idesc2, true);
+          } else {
+            tc::mma_bf16(tmem + dcol, ah, bh, idesc2, (r | h) != 0);
           }
         }
     };
     auto conv2_epilogue = [&](int tl, uint32_t dcol) {
-      float v[32], w[32];
-      tc::tmem_ld32(tq + dcol, v);
-      tc::tmem_ld32(tq + dcol + 32, w);
-      tc::tmem_ld_wait();
-      if (a2off[tl] >= 0) {
-        float hi[16], lo[16];
+      if (kSplit) {
+        // 256-thread slots: warpgroup wg owns output channels 8wg..8wg+7 (= channel plane wg of a2); per sub-position
+        // it adds the A_hi.B_lo half (columns 64..) to the main half, then max / bias / ReLU / hi-lo split
+        float m4[8];
 #pragma unroll
-        for (int co = 0; co < 16; ++co) {
-          const float m4 = fmaxf(fmaxf(v[co], v[16 + co]), fmaxf(w[co], w[16 + co]));
-          hi[co] = fmaxf(m4 + sh.b2[co], 0.f);
-          if (kSplit) tc::split_bf16(hi[co], hi[co], lo[co]);
+        for (int sub = 0; sub < 4; ++sub) {
+          float a[8], bq[8];
+          tc::tmem_ld8(tq + dcol + sub * 16 + wg * 8, a);
+          tc::tmem_ld8(tq + dcol + 64 + sub * 16 + wg * 8, bq);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 8; ++i) m4[i] = sub == 0 ? a[i] + bq[i] : fmaxf(m4[i], a[i] + bq[i]);
         }
-        const uint32_t off = (uint32_t)a2off[tl];
-        *reinterpret_cast<uint4*>(r0 + off) = pack8(hi);
-        *reinterpret_cast<uint4*>(r0 + PLANE2 + off) = pack8(hi + 8);
-        if (kSplit) {
+        if (a2off[tl] >= 0) {
+          float hi[8], lo[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) tc::split_bf16(fmaxf(m4[i] + sh.b2[wg * 8 + i], 0.f), hi[i], lo[i]);
+          const uint32_t off = (uint32_t)a2off[tl] + wg * PLANE2;
+          *reinterpret_cast<uint4*>(r0 + off) = pack8(hi);
           *reinterpret_cast<uint4*>(r0 + A2_BYTES + off) = pack8(lo);
-          *reinterpret_cast<uint4*>(r0 + A2_BYTES + PLANE2 + off) = pack8(lo + 8);
+        }
+      } else {
+        float v[32], w[32];
+        tc::tmem_ld32(tq + dcol, v);
+        tc::tmem_ld32(tq + dcol + 32, w);
+        tc::tmem_ld_wait();
+        if (a2off[tl] >= 0) {
+          float hi[16];
+#pragma unroll
+          for (int co = 0; co < 16; ++co) {
+            const float m4 = fmaxf(fmaxf(v[co], v[16 + co]), fmaxf(w[co], w[16 + co]));
+            hi[co] = fmaxf(m4 + sh.b2[co], 0.f);
+          }
+          const uint32_t off = (uint32_t)a2off[tl];
+          *reinterpret_cast<uint4*>(r0 + off) = pack8(hi);
+          *reinterpret_cast<uint4*>(r0 + PLANE2 + off) = pack8(hi + 8);
         }
       }
     };
-    if (kPipe2) {
-      // 128 TMEM columns: tiles 0 and 1 in flight, tile 2 re-uses tile 0's columns once its epilogue is done;
-      // every tile has its own commit, so an epilogue overlaps the next tile's MMAs
+    {
+      // two tiles of TMEM columns: tiles 0 and 1 in flight, tile 2 re-uses tile 0's columns once its epilogue is
+      // done; every tile has its own commit, so an epilogue overlaps the next tile's MMAs
       if (tid == 0) {
         tc::fence_after_sync();
         conv2_issue(0, 0);
         tc::mma_commit(&mz.bar[0]);
-        conv2_issue(1, 64);
+        conv2_issue(1, C2W);
         tc::mma_commit(&mz.bar[1]);
       }
       tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1;
@@ -477,21 +509,10 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       }
       tc::mbar_wait_bounded(&mz.bar[1], ph1); ph1 ^= 1;
       tc::fence_after_sync();
-      conv2_epilogue(1, 64);
+      conv2_epilogue(1, C2W);
       tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1;
       tc::fence_after_sync();
       conv2_epilogue(2, 0);
-    } else {
-      if (tid == 0) {
-        tc::fence_after_sync();
-        for (int tl = 0; tl < 3; ++tl) conv2_issue(tl, tl * 64);
-        tc::mma_commit(&mz.bar[0]);
-      }
-      tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1;
-      tc::fence_after_sync();
-#pragma unroll
-      for (int tl = 0; tl < 3; ++tl)
-        if (tl % NWG == wg) conv2_epilogue(tl, tl * 64);
     }
     tc::fence_async_smem();
     tc::fence_before_sync();
