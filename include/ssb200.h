@@ -141,21 +141,10 @@ int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_t* lengths,
                          const float* whh_f, const float* bhh_f, const float* whh_r, const float* bhh_r,
                          float* out, float* gates, int32_t passes, void* stream);
 
-/* K2 on the tensor cores: same contract as ssb_roi_cnn_fwd; conv2/conv3 run as implicit GEMMs on
- * tcgen05 (bf16 operands, fp32 accumulators in TMEM).  passes = 1 (bf16) or 3 (split-bf16, fp32 grade). */
-int ssb_roi_cnn_fwd_tc(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
-                       int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
-                       float* out, int64_t out_stride, int32_t passes, void* stream);
-
-/* K2 v2: all three convolutions on tcgen05; the 2x2 max-pools are folded into the GEMM's N dimension
- * (one 4x4-patch GEMM per pooled layer), two frame slots per CTA.  Same arguments as ssb_roi_cnn_fwd_tc. */
-int ssb_roi_cnn_fwd_tc2(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
-                        int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
-                        float* out, int64_t out_stride, int32_t passes, void* stream);
-
-/* K2 v3 (the default): v2's formulation re-organised for latency hiding -- passes = 1: four 128-thread frame
- * slots per CTA with one MMA issuer each; frames handed out by an atomic counter; next frame prefetched;
- * conv2 tiles committed one by one.  Same arguments as ssb_roi_cnn_fwd_tc. */
+/* K2 on the tensor cores: same contract as ssb_roi_cnn_fwd plus `passes` (1 = single fp16 pass, 3 = hi/lo split,
+ * fp32-parity grade).  All three convolutions are tcgen05 GEMMs with the 2x2 max-pools folded into N; passes = 1 runs
+ * four 128-thread frame slots per CTA with one MMA issuer each; frames are handed out by an atomic counter, the next
+ * frame is prefetched, conv2 tiles are committed one by one.  (Third generation of this kernel) */
 int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
                         int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
                         float* out, int64_t out_stride, int32_t passes, void* stream);

@@ -66,7 +66,7 @@ def features_fwd(landmarks: torch.Tensor, ids: torch.Tensor, anchor_ids: Sequenc
 # ----------------------------------------------------------------------------- K2
 def roi_cnn_fwd(R: torch.Tensor, lengths: Optional[torch.Tensor], weights: Sequence[torch.Tensor],
                 standardize: bool = True, out: Optional[torch.Tensor] = None, out_col: int = 0,
-                passes: int = 0, version: int = 3) -> torch.Tensor:
+                passes: int = 0) -> torch.Tensor:
     """R u8 [B,T,48,96] -> embedding f32 [B,T,32] (or written into out[..., out_col:out_col+32])."""
     _need(R, torch.uint8, "R")
     B, T, Hh, Ww = R.shape
@@ -82,8 +82,7 @@ def roi_cnn_fwd(R: torch.Tensor, lengths: Optional[torch.Tensor], weights: Seque
     base = out.data_ptr() + 4 * out_col
     import ctypes
     if passes:
-        fn = {1: _lib.lib().ssb_roi_cnn_fwd_tc, 2: _lib.lib().ssb_roi_cnn_fwd_tc2, 3: _lib.lib().ssb_roi_cnn_fwd_tc3}[version]
-        check(fn(ptr(R), ptr(lengths), i64(B), i64(T), i32(Hh), i32(Ww), ptr_array(weights),
+        check(_lib.lib().ssb_roi_cnn_fwd_tc3(ptr(R), ptr(lengths), i64(B), i64(T), i32(Hh), i32(Ww), ptr_array(weights),
                                             i32(1 if standardize else 0), ctypes.c_void_p(base), i64(stride),
                                             i32(passes), stream_ptr()))
         return out

@@ -104,10 +104,9 @@ def test_model_logits_by_precision(precision, tol, use_roi, B, T, mode):
     assert agree == 1.0
 
 
-@pytest.mark.parametrize("version", [1, 2, 3])
 @pytest.mark.parametrize("passes,tol", [(3, 1e-4), (1, 3e-3)])
 @pytest.mark.parametrize("standardize", [True, False])
-def test_roi_cnn_tc_vs_oracle(passes, tol, standardize, version):
+def test_roi_cnn_tc_vs_oracle(passes, tol, standardize):
     import numpy as np
     dev = _cuda()
     from oracle import ref_model
@@ -122,13 +121,13 @@ def test_roi_cnn_tc_vs_oracle(passes, tol, standardize, version):
              "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
     w = [p[n].to(dev).contiguous() for n in names]
     Rd, Ld = torch.from_numpy(R).to(dev), torch.from_numpy(L).to(dev)
-    emb = ops.roi_cnn_fwd(Rd, Ld, w, standardize=standardize, passes=passes, version=version)
+    emb = ops.roi_cnn_fwd(Rd, Ld, w, standardize=standardize, passes=passes)
     torch.cuda.synchronize()
     ref32 = ops.roi_cnn_fwd(Rd, Ld, w, standardize=standardize)
     ref = ref_model.roi_cnn(p, ref_model.roi_prepare(torch.from_numpy(R), standardize))
     mask = torch.arange(T)[None, :] < torch.from_numpy(L)[:, None]
     ref = ref * mask[..., None]
-    print(f"cnn v{version} passes={passes} std={standardize} vs oracle {rel_err(emb, ref):.3e} vs fp32 kernel {rel_err(emb, ref32):.3e}")
+    print(f"cnn passes={passes} std={standardize} vs oracle {rel_err(emb, ref):.3e} vs fp32 kernel {rel_err(emb, ref32):.3e}")
     assert rel_err(emb, ref) < tol
     assert torch.all(emb.cpu()[~mask] == 0)
 
@@ -149,8 +148,8 @@ def test_roi_cnn_tc3_many_frames_dynamic_handout(passes, tol):
     w = [p[n].to(dev).contiguous() for n in names]
     Rd, Ld = torch.from_numpy(d["R"]).to(dev), torch.from_numpy(d["lengths"]).to(dev)
     ref32 = ops.roi_cnn_fwd(Rd, Ld, w, passes=0)
-    a = ops.roi_cnn_fwd(Rd, Ld, w, passes=passes, version=3)
-    b = ops.roi_cnn_fwd(Rd, Ld, w, passes=passes, version=3)
+    a = ops.roi_cnn_fwd(Rd, Ld, w, passes=passes)
+    b = ops.roi_cnn_fwd(Rd, Ld, w, passes=passes)
     torch.cuda.synchronize()
     assert torch.equal(a, b)
     assert rel_err(a, ref32) < tol
