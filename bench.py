@@ -462,7 +462,7 @@ def main():
     torch.cuda.synchronize()
     cnn_ms = k0.elapsed_time(k1) / 5
     achieved = CNN_FLOP_PER_FRAME * frames / (cnn_ms / 1e3) / 1e12
-    roofline = {"kernel": "roi_cnn_tc_kernel" if cnn_passes else "roi_cnn_fwd_kernel", "bound": "tensor", "achieved": achieved, "peak": peaks["tensor_burst"],
+    roofline = {"kernel": {0: "roi_cnn_fwd_kernel", 1: "roi_cnn_tc3_kernel<false,4,128>", 3: "roi_cnn_tc3_kernel<true,2,256>"}[cnn_passes], "bound": "tensor", "achieved": achieved, "peak": peaks["tensor_burst"],
                 "unit": "TFLOP/s", "frac": achieved / peaks["tensor_burst"],
                 "traffic": ncu_traffic(args.precision, B, args.lengths),
                 "peak_src": f"{peaks['src']} bf16 burst", "ms_per_launch": cnn_ms,

@@ -66,7 +66,7 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(THREADS, 1)
 gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
                   const float* __restrict__ whh_f, const float* __restrict__ whh_r,
                   const float* __restrict__ bhn_f, const float* __restrict__ bhn_r,
-                  const int64_t* __restrict__ lengths, const int32_t* __restrict__ order, int B, int T, int dbg,
+                  const int64_t* __restrict__ lengths, const int32_t* __restrict__ order, int B, int T,
                   float* __restrict__ out, float* __restrict__ gates) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* a_hi = smem;
@@ -145,12 +145,12 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
     for (int s = 1; s < maxlen; ++s) {
       tc::mbar_wait_bounded(&ctl.ready, (s - 1) & 1);
       if (lane == 0) {
-        tc::mbar_arrive_expect_tx(&ctl.full, (dbg & 1) ? (CL - 1) * 16u * (kSplit ? 2 : 1) : kTxBytes);
+        tc::mbar_arrive_expect_tx(&ctl.full, kTxBytes);
         for (uint32_t p = 1; p < CL; ++p) {
           const uint32_t peer = (rank + p) % CL;
           const uint32_t bar = tc::mapa(tc::smem_u32(&ctl.full), peer);
-          tc::bulk_copy_to_peer(tc::mapa(src_hi, peer), src_hi, (dbg & 1) ? 16u : SLICE, bar);
-          if (kSplit) tc::bulk_copy_to_peer(tc::mapa(src_lo, peer), src_lo, (dbg & 1) ? 16u : SLICE, bar);
+          tc::bulk_copy_to_peer(tc::mapa(src_hi, peer), src_hi, SLICE, bar);
+          if (kSplit) tc::bulk_copy_to_peer(tc::mapa(src_lo, peer), src_lo, SLICE, bar);
         }
       }
       tc::mbar_wait_bounded(&ctl.full, (s - 1) & 1);            // all four h slices of step s-1 are in place
@@ -223,6 +223,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
 #pragma unroll
           for (int v = 0; v < 12; ++v) g4[v] = gstage[v * EPI_THREADS + tid];
         }
+        if (!kSplit) prefetch_gi(s + 1);   // slots are in registers now: a whole step of prefetch distance
       }
       if (s >= 1) {
         tc::mbar_wait_bounded(&ctl.mma_done, (s - 1) & 1);
@@ -292,7 +293,6 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
         for (int v = 0; v < UT / 4; ++v)
           reinterpret_cast<float4*>(orow)[v] = make_float4(h[4 * v], h[4 * v + 1], h[4 * v + 2], h[4 * v + 3]);
       }
-      if (!kSplit) prefetch_gi(s + 1);                           // staging slots were consumed above; lands during the exchange
     }
     // zeros past each clip's length (pad_packed_sequence semantics)
     if (b >= 0) {
@@ -348,14 +348,13 @@ extern "C" int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_
   SSB_REQUIRE(passes == 1 || passes == 3, "passes must be 1 or 3");
   if (B == 0) return SSB_OK;
   dim3 grid(CL * cdiv(B, BM), 2), block(THREADS);
-  static const int dbg = getenv("SSB_GRU_DBG") ? atoi(getenv("SSB_GRU_DBG")) : 0;   // timing experiments only (wrong results)
   cudaStream_t st = (cudaStream_t)stream;
 #define SSB_LAUNCH_GRUTC(SPLIT, SAVE)                                                                          \
   do {                                                                                                          \
     SSB_CUDA(cudaFuncSetAttribute(gru_tc_fwd_kernel<SPLIT, SAVE>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
                                   (int)smem_bytes<SPLIT>()));                                                   \
     gru_tc_fwd_kernel<SPLIT, SAVE><<<grid, block, smem_bytes<SPLIT>(), st>>>(                                   \
-        gi, gi_ld, whh_f, whh_r, bhh_f + 2 * H, bhh_r + 2 * H, lengths, order, (int)B, (int)T, dbg, out, gates);\
+        gi, gi_ld, whh_f, whh_r, bhh_f + 2 * H, bhh_r + 2 * H, lengths, order, (int)B, (int)T, out, gates);\
   } while (0)
   if (passes == 3) { if (gates) SSB_LAUNCH_GRUTC(true, true); else SSB_LAUNCH_GRUTC(true, false); }
   else             { if (gates) SSB_LAUNCH_GRUTC(false, true); else SSB_LAUNCH_GRUTC(false, false); }
