@@ -182,6 +182,27 @@ int ssb_ring_gather(const float* ring, int64_t W, int64_t D, const int32_t* sid,
                     const int32_t* count, int64_t m, float* Xw, int64_t dx, float* Ew, int64_t de,
                     int64_t T, int64_t* lengths, void* stream);
 
+/* K7: GRU recurrence for small hidden sizes (H = 32/64/96/128, W_hh resident in one SM) with the time-mean pooling fused:
+ * the earlier model generation GRUClassifier (inactive/train_reduced.py:129-145, weights inactive/word_model_5.pt).
+ * gi f32 [B,T,gi_ld] = x W_ih^T + b_ih, direction d in columns [d*3H,(d+1)*3H), gates (r,z,n); lengths NULL = every clip
+ * runs all T steps (the reference's un-packed call); out f32 [B,T,ndir*H] or NULL; pooled f32 [B,ndir*H] or NULL. */
+int ssb_gru_small_fwd(const float* gi, int64_t gi_ld, const float* whh_f, const float* bhh_f,
+                      const float* whh_r, const float* bhh_r, const int64_t* lengths,
+                      int64_t B, int64_t T, int64_t H, int32_t ndir, float* out, float* pooled, void* stream);
+
+/* Mouth-open EMA + hysteresis of important_landmarks.py:130-144 for S independent streams x F frames, in double.
+ * lm f32 [S,F,n_lm,3]; valid u8 [S,F] or NULL (frame without a face: state untouched); ema_state f64 [S] / open_state
+ * u8 [S] in-out; ema_out f64 [S,F] / open_out u8 [S,F] nullable. */
+int ssb_mouth_open_ema(const float* lm, const uint8_t* valid, int64_t S, int64_t F, int64_t n_lm,
+                       double alpha, double open_thr, double close_thr, double* ema_state, uint8_t* open_state,
+                       double* ema_out, uint8_t* open_out, void* stream);
+
+/* Device-resident clip store (".npz ingestion"): dst[i,:] = src[index[i],:], rows of row_bytes.
+ * Replaces the per-item np.load + clip_pad_trim / roi_pad_trim + torch.stack of NPZWordDataset.__getitem__ and
+ * collate_fn (train_model_official.py:93-117, 134-204) for clips ingested once into HBM.  index i64 [n] on the device,
+ * every value in [0, rows of src). */
+int ssb_gather_rows(const void* src, int64_t row_bytes, const int64_t* index, int64_t n, void* dst, void* stream);
+
 /* Training augmentation of the point features on the device: the policy of NPZWordDataset.__getitem__
  * (train_model_official.py:143-152): N(0, noise_std) noise with probability p_noise; if T > 12, with probability p_drop
  * 1..drop_max frames from [1, T-2] are removed from X; the ROI clip is only cut to the new length (the reference does

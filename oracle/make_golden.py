@@ -229,6 +229,120 @@ def golden_augment(train):
     print("augment.npz", rec["T_out"])
 
 
+def golden_dataset(train):
+    """The ingestion path on a small synthetic clip directory (schema train:1-9): ragged lengths around max_t, a ROI
+    shorter than X, a clip without ROI, a clip of another feature dim (dropped by the most-common-dim rule, train:338-351).
+    Expected values come from the reference's own split_by_label, NPZWordDataset(augment=False) + collate_fn and
+    torch's WeightedRandomSampler."""
+    from collections import Counter
+    from torch.utils.data import WeightedRandomSampler
+    rng = np.random.default_rng(29)
+    tmp = tempfile.mkdtemp()
+    words = ["water"] * 6 + ["hello"] * 4 + ["apple"] * 3 + ["water"]
+    Ts = [5, 30, 90, 95, 100, 13, 44, 89, 91, 7, 60, 61, 12, 20]
+    rec, names = {}, []
+    for i, (w, T) in enumerate(zip(words, Ts)):
+        D = 120 if i == 13 else 180
+        X = (rng.integers(-64, 64, (T, D)) / 64.0).astype(np.float32)          # low-entropy: keeps the fixture small
+        Tr = T - 3 if i in (1, 4) else (T + 2 if i == 6 else T)
+        R = ((np.arange(Tr)[:, None, None] * 5 + i * 11 + np.arange(48)[None, :, None] + 2 * np.arange(96)[None, None, :]) % 256).astype(np.uint8)
+        name = f"clip_{i:02d}.npz"
+        kw = dict(X=X, ts=np.arange(T, dtype=np.int32), label=w, speaker="s0", idxs=np.arange(88, dtype=np.int32))
+        if i != 9:
+            kw["roi"] = R
+        np.savez(os.path.join(tmp, name), **kw)
+        names.append(name)
+        rec[f"X_{i}"] = X; rec[f"label_{i}"] = np.array(w)
+        rec[f"roi_tr_{i}"] = np.array(Tr if i != 9 else -1)
+    files = [os.path.join(tmp, n) for n in names if n != "clip_13.npz"]
+    labels = [w for n, w in zip(names, words) if n != "clip_13.npz"]
+    uniq = sorted(set(labels))
+    l2i = {lab: k for k, lab in enumerate(uniq)}
+    import io, contextlib
+    with contextlib.redirect_stdout(io.StringIO()):
+        tr, va = train.split_by_label(list(files), list(labels), 0.15, seed=42)
+    ds = train.NPZWordDataset(files, l2i, max_t=90, augment=False, use_roi=True)
+    X, T, R, y = train.collate_fn([ds[k] for k in range(len(files))])
+    tl = [str(np.load(f, allow_pickle=True)["label"]) for f in tr]
+    cnt = Counter(tl)
+    w8 = torch.tensor([1.0 / cnt[lab] for lab in tl], dtype=torch.double)
+    g = torch.Generator(); g.manual_seed(123)
+    order = list(iter(WeightedRandomSampler(w8, num_samples=len(w8), replacement=True, generator=g)))
+    rec.update(names=np.array(names), kept=np.array([os.path.basename(f) for f in files]), classes=np.array(uniq),
+               train=np.array([os.path.basename(f) for f in tr]), val=np.array([os.path.basename(f) for f in va]),
+               X=X.numpy(), T=T.numpy(), R=R.numpy(), y=y.numpy(), weights=w8.numpy(), order=np.array(order, np.int64))
+    np.savez_compressed(os.path.join(OUT, "dataset.npz"), **rec)
+    print("dataset.npz", T.tolist(), [os.path.basename(f) for f in va], order)
+
+
+def golden_legacy():
+    """(1) the reference's GRUClassifier (inactive/train_reduced.py:129-145) with the shipped trained
+    weights inactive/word_model_5.pt on synthetic zero-padded clips -> out / pooled / logits; the weights travel in the
+    fixture because /root/reference does not.  (2) the mouth-open EMA + hysteresis loop of important_landmarks.py:118-144,
+    re-run here with the reference's own dist2d and constants (the loop body is inline in its main(), not callable)."""
+    sys.path.insert(0, os.path.join(REF, "inactive"))
+    cwd = os.getcwd()
+    os.chdir(tempfile.mkdtemp())
+    try:
+        import train_reduced as tr5
+        import important_landmarks as il
+    finally:
+        os.chdir(cwd)
+    ck = torch.load(os.path.join(REF, "inactive", "word_model_5.pt"), map_location="cpu")
+    model = tr5.GRUClassifier(int(ck["input_dim"]), len(ck["words"]), hidden=64)
+    model.load_state_dict(ck["model"])
+    model.eval()
+    rng = np.random.default_rng(31)
+    B, T, D = 7, int(ck["max_t"]), int(ck["input_dim"])
+    lens = [60, 41, 7, 60, 23, 1, 55]
+    x = (rng.integers(-96, 96, (B, T, D)) / 64.0).astype(np.float32)
+    for b, n in enumerate(lens):
+        x[b, n:] = 0.0                                           # pad_or_trim's zero rows (the GRU still runs over them)
+    with torch.no_grad():
+        xt = torch.from_numpy(x)
+        out, _ = model.gru(xt)
+        pooled = out.mean(dim=1)
+        logits = model(xt)
+    rec = {"sd_" + k: v.numpy() for k, v in ck["model"].items()}
+    rec.update(x=x, out=out.numpy(), pooled=pooled.numpy(), logits=logits.numpy(), max_t=np.array(T),
+               words=np.array(ck["words"]))
+    # ---- mouth-open detector: S streams x F frames of 478 landmarks; only ids 13, 14, 33, 263 matter
+    S, F = 5, 80
+    lm = np.zeros((S, F, 478, 3), np.float32)
+    lm[..., :2] = rng.uniform(0.3, 0.7, (S, F, 478, 2)).astype(np.float32)
+    tt = np.arange(F)[None, :] / 9.0 + np.arange(S)[:, None]
+    gap = (0.012 + 0.012 * np.sin(tt) + rng.normal(0, 0.002, (S, F))).astype(np.float32)      # straddles 0.02 * eye span
+    lm[:, :, il.LEFT_EYE_CORNER, 0] = 0.40; lm[:, :, il.RIGHT_EYE_CORNER, 0] = 0.60
+    lm[:, :, il.LEFT_EYE_CORNER, 1] = 0.45; lm[:, :, il.RIGHT_EYE_CORNER, 1] = 0.46
+    lm[:, :, il.MOUTH_TOP, 1] = 0.60
+    lm[:, :, il.MOUTH_BOTTOM, 1] = 0.60 + gap * 0.4
+    valid = (rng.uniform(size=(S, F)) > 0.1).astype(np.uint8)
+    ema_tr, open_tr = np.zeros((S, F)), np.zeros((S, F), np.uint8)
+    for s_ in range(S):
+        mouth_state_open, mouth_ema = False, 0.0                 # important_landmarks.py:108-109
+        for f in range(F):
+            if valid[s_, f]:
+                face = as_face(lm[s_, f])
+                lip_gap = abs(face[il.MOUTH_BOTTOM].y - face[il.MOUTH_TOP].y)
+                eye_span = il.dist2d(face[il.LEFT_EYE_CORNER], face[il.RIGHT_EYE_CORNER]) + 1e-6
+                openness = lip_gap / eye_span
+                mouth_ema = (1 - il.EMA_ALPHA) * mouth_ema + il.EMA_ALPHA * openness
+                if mouth_state_open:
+                    if mouth_ema < il.CLOSE_THR:
+                        mouth_state_open = False
+                else:
+                    if mouth_ema > il.OPEN_THR:
+                        mouth_state_open = True
+            ema_tr[s_, f], open_tr[s_, f] = mouth_ema, mouth_state_open
+    rec.update(m_lm4=lm[:, :, [il.MOUTH_TOP, il.MOUTH_BOTTOM, il.LEFT_EYE_CORNER, il.RIGHT_EYE_CORNER], :2].copy(),
+               m_ids=np.array([il.MOUTH_TOP, il.MOUTH_BOTTOM, il.LEFT_EYE_CORNER, il.RIGHT_EYE_CORNER]),
+               m_valid=valid, m_ema=ema_tr, m_open=open_tr,
+               m_const=np.array([il.EMA_ALPHA, il.OPEN_THR, il.CLOSE_THR]))
+    np.savez_compressed(os.path.join(OUT, "legacy.npz"), **rec)
+    print("legacy.npz logits", logits.numpy().round(3).tolist()[:2], "open frames", int(open_tr.sum()), "of", S * F,
+          "toggles", int(np.abs(np.diff(open_tr.astype(int), axis=1)).sum()))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     train, live, record = import_reference()
@@ -240,6 +354,8 @@ def main():
     golden_roi_crop(live, record)
     golden_roi_crop_many(live, record)
     golden_augment(train)
+    golden_dataset(train)
+    golden_legacy()
 
 
 if __name__ == "__main__":

@@ -6,5 +6,10 @@ The package never falls back to eager PyTorch or the CPU: if libssb200.so is mis
 or the tensors are not on a B200 the calls raise."""
 from .landmarks import FIXED_IDXS, crop_rois, extract_feature, extract_features  # noqa: F401
 from .model import BiGRUClassifier, load_classifier  # noqa: F401
+from .dataset import ClipStore, scan_clips, split_by_label  # noqa: F401
+from .legacy import GRUClassifier, MouthOpenDetector, load_word_model  # noqa: F401
+from .streaming import StreamScheduler  # noqa: F401
 
-__all__ = ["BiGRUClassifier", "load_classifier", "extract_features", "extract_feature", "crop_rois", "FIXED_IDXS"]
+__all__ = ["BiGRUClassifier", "load_classifier", "extract_features", "extract_feature", "crop_rois", "FIXED_IDXS",
+           "ClipStore", "scan_clips", "split_by_label", "StreamScheduler", "GRUClassifier", "MouthOpenDetector",
+           "load_word_model"]

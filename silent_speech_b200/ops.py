@@ -328,6 +328,52 @@ def ring_gather(ring: torch.Tensor, sid: torch.Tensor, start: torch.Tensor, coun
     return Xw, Ew, lengths
 
 
+# ----------------------------------------------------------------------------- K7 (small-hidden GRU), mouth-open EMA
+def gru_small_fwd(gi: torch.Tensor, whh_f, bhh_f, whh_r=None, bhh_r=None, lengths: Optional[torch.Tensor] = None,
+                  hidden: int = 64, want_out: bool = False):
+    """gi f32 [B,T,ndir*3H] -> (pooled f32 [B,ndir*H] = time mean, out f32 [B,T,ndir*H] or None)."""
+    _need(gi, torch.float32, "gi")
+    B, T, ld = gi.shape
+    ndir = 1 if whh_r is None else 2
+    if lengths is not None:
+        _need(lengths, torch.int64, "lengths")
+    pooled = torch.empty(B, ndir * hidden, device=gi.device, dtype=torch.float32)
+    out = torch.empty(B, T, ndir * hidden, device=gi.device, dtype=torch.float32) if want_out else None
+    check(_lib.lib().ssb_gru_small_fwd(ptr(gi), i64(ld), ptr(whh_f), ptr(bhh_f), ptr(whh_r), ptr(bhh_r), ptr(lengths),
+                                       i64(B), i64(T), i64(hidden), i32(ndir), ptr(out), ptr(pooled), stream_ptr()))
+    return pooled, out
+
+
+def mouth_open_ema(lm: torch.Tensor, valid: Optional[torch.Tensor], ema_state: torch.Tensor, open_state: torch.Tensor,
+                   alpha: float = 0.25, open_thr: float = 0.02, close_thr: float = 0.02, want_trace: bool = True):
+    """lm f32 [S,F,n_lm,3]; updates ema_state f64 [S] / open_state u8 [S] in place -> (ema f64 [S,F], open u8 [S,F]) or None."""
+    import ctypes
+    _need(lm, torch.float32, "lm"); _need(ema_state, torch.float64, "ema_state"); _need(open_state, torch.uint8, "open_state")
+    S, F, n_lm, _ = lm.shape
+    if valid is not None:
+        _need(valid, torch.uint8, "valid")
+    ema = torch.empty(S, F, device=lm.device, dtype=torch.float64) if want_trace else None
+    opn = torch.empty(S, F, device=lm.device, dtype=torch.uint8) if want_trace else None
+    f64 = ctypes.c_double
+    check(_lib.lib().ssb_mouth_open_ema(ptr(lm), ptr(valid), i64(S), i64(F), i64(n_lm), f64(alpha), f64(open_thr), f64(close_thr),
+                                        ptr(ema_state), ptr(open_state), ptr(ema), ptr(opn), stream_ptr()))
+    return (ema, opn) if want_trace else None
+
+
+# ----------------------------------------------------------------------------- clip store
+def gather_rows(src: torch.Tensor, index: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out[i] = src[index[i]] along dim 0 (whole contiguous rows; index i64 on the device, values validated by the caller)."""
+    if not src.is_cuda or not src.is_contiguous():
+        raise _lib.SsbError("gather_rows: src must be a contiguous CUDA tensor")
+    _need(index, torch.int64, "index")
+    n = index.shape[0]
+    if out is None:
+        out = torch.empty((n,) + tuple(src.shape[1:]), device=src.device, dtype=src.dtype)
+    row_bytes = (src[0].numel() if src.shape[0] else 1) * src.element_size()
+    check(_lib.lib().ssb_gather_rows(ptr(src), i64(row_bytes), ptr(index), i64(n), ptr(out), stream_ptr()))
+    return out
+
+
 # ----------------------------------------------------------------------------- augmentation
 def augment_clips(X: torch.Tensor, lengths: torch.Tensor, R: Optional[torch.Tensor], seed: int, p_noise: float = 0.7,
                   noise_std: float = 0.01, p_drop: float = 0.35, drop_max: int = 2):
