@@ -65,7 +65,7 @@ struct SlotMisc {
   float part[9][C3P];                                  // conv3 channel sums per (tile, lane quarter): fixed-order reduction
 
   uint32_t red[16];
-  uint64_t bar[2];
+  uint64_t bar[3];
   long long next;                                      // next frame of this slot (dynamic hand-out)
 };
 
@@ -163,7 +163,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   if (threadIdx.x < E) sh.bfc[threadIdx.x] = gw.bfc[threadIdx.x];
   for (int i = tid; i < L::A1_ALLOC / 16; i += ST) reinterpret_cast<uint4*>(a1)[i] = make_uint4(0, 0, 0, 0);
   if (threadIdx.x < 32) tc::tmem_alloc<512>(&sh.tmem_base);
-  if (tid == 32) { tc::mbar_init(&mz.bar[0], 1); tc::mbar_init(&mz.bar[1], 1); tc::mbar_fence_init(); }
+  if (tid == 32) { tc::mbar_init(&mz.bar[0], 1); tc::mbar_init(&mz.bar[1], 1); tc::mbar_init(&mz.bar[2], 1); tc::mbar_fence_init(); }
   tc::fence_async_smem();
   tc::fence_before_sync();
   __syncthreads();
@@ -176,7 +176,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   constexpr int C1W = kSplit ? 64 : 32, C2W = kSplit ? 128 : 64;        // TMEM columns per conv1 / conv2 tile
   constexpr uint32_t idesc3_hi = tc::make_idesc_bf16(128, kSplit ? 64 : 32), idesc3_lo = tc::make_idesc_bf16(128, 32);
   constexpr int COLS3 = kSplit ? 64 : 32;
-  uint32_t ph0 = 0, ph1 = 0;
+  uint32_t ph0 = 0, ph1 = 0, ph2 = 0;
   const int q = warp & 3, wg = warp >> 2;
   const int row = q * 32 + lane;                       // this thread's row of every 128-row tile (= TMEM lane)
   const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16);
@@ -519,8 +519,11 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     slot_sync<ST>(slot);
 
     // ================= conv3 + ReLU + mean: 3 tiles of 16 rows x 8 columns (12 rows real), 9 taps
+    // every tile has its own commit (bar[0..2]): the channel sums of tile i are taken while tiles i+1.. are still in the
+    // tensor core
     if (tid == 0) {
       tc::fence_after_sync();
+#pragma unroll
       for (int tx = 0; tx < 3; ++tx) {
 #pragma unroll
         for (int tap = 0; tap < 9; ++tap) {
@@ -530,17 +533,20 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           tc::mma_bf16(tmem + tx * COLS3, tc::make_desc(r0_u + a_off, PLANE2, PITCH2 * 16), db, idesc3_hi, tap > 0);
           if (kSplit) tc::mma_bf16(tmem + tx * COLS3, tc::make_desc(r0_u + A2_BYTES + a_off, PLANE2, PITCH2 * 16), db, idesc3_lo, true);
         }
+        tc::mma_commit(&mz.bar[tx]);
       }
-      tc::mma_commit(&mz.bar[0]);
     }
-    tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1;
-    tc::fence_after_sync();
-    if (q < 3) {
-      float acc[C3P];
+    float acc[C3P];
 #pragma unroll
-      for (int c = 0; c < C3P; ++c) acc[c] = 0.f;
-#pragma unroll 1
-      for (int tx = wg; tx < 3; tx += NWG) {
+    for (int c = 0; c < C3P; ++c) acc[c] = 0.f;
+#pragma unroll
+    for (int tx = 0; tx < 3; ++tx) {
+      // every thread follows all three barriers (phase bookkeeping), only the tile's owners read its columns
+      if (tx == 0) { tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1; }
+      if (tx == 1) { tc::mbar_wait_bounded(&mz.bar[1], ph1); ph1 ^= 1; }
+      if (tx == 2) { tc::mbar_wait_bounded(&mz.bar[2], ph2); ph2 ^= 1; }
+      tc::fence_after_sync();
+      if (q < 3 && tx % NWG == wg) {
         float v[32];
         tc::tmem_ld32(tq + tx * COLS3, v);
         if (kSplit) {
@@ -555,6 +561,8 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 #pragma unroll
         for (int c = 0; c < C3; ++c) acc[c] += fmaxf(v[c] + sh.b3[c], 0.f);
       }
+    }
+    if (q < 3) {
       // one transposing reduction per warp: lane c ends with channel c's sum over the warp's pixels
 #pragma unroll
       for (int off = 16, n = 16; off >= 1; off >>= 1, n >>= 1) {
