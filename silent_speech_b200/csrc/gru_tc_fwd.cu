@@ -38,15 +38,18 @@ constexpr int UT = 16;                     // hidden units per gate thread
 constexpr int TMEM_COLS = 256;
 
 struct Ctl {
-  uint64_t full, mma_done, empty, ready;
+  uint64_t full, mma_done, empty, ready, gi_full;
   uint32_t tmem_base;
   int maxlen;
 };
 
-// single-pass mode has shared memory to spare: the next step's input projections (48 floats per gate thread) are
-// prefetched with cp.async into a thread-private staging area, so their HBM latency never sits on the step's
-// critical path; split mode (two operand copies resident) prefetches into L2 only.
-constexpr int GI_STAGE_BYTES = 12 * EPI_THREADS * 16;        // [12 float4][384 threads]: conflict-free 16-byte accesses
+// single-pass mode has shared memory to spare: the next step's input projections are staged in shared memory so
+// their HBM latency never sits on the step's critical path.  Every gate thread issues ONE 192-byte bulk copy (its
+// row's 48 units of gate `ug`) that completes on the `gi_full` mbarrier -- 12 LDGSTS + 12 address bumps per thread
+// were a fifth of the step's issue slots.  Rows are padded to 208 B so that a quarter-warp's LDS.128 of eight
+// consecutive rows hits eight different bank groups.  Split mode (two operand copies resident) prefetches into L2 only.
+constexpr int GROW = 52;                                     // floats per staged row: 48 + 4 pad
+constexpr int GI_STAGE_BYTES = 3 * BM * GROW * 4;            // [3 gates][128 rows][52]: 79,872
 template <bool kSplit>
 constexpr size_t smem_bytes() { return (kSplit ? 2 : 1) * (A_BYTES + B_BYTES) + (kSplit ? 0 : GI_STAGE_BYTES) + sizeof(Ctl); }
 
@@ -73,7 +76,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   uint8_t* b_hi = smem + A_BYTES;
   uint8_t* a_lo = smem + A_BYTES + B_BYTES;                 // only when kSplit
   uint8_t* b_lo = smem + 2 * A_BYTES + B_BYTES;
-  float4* gstage = reinterpret_cast<float4*>(smem + (kSplit ? 2 : 1) * (A_BYTES + B_BYTES));   // !kSplit only
+  float* gstage = reinterpret_cast<float*>(smem + (kSplit ? 2 : 1) * (A_BYTES + B_BYTES));     // !kSplit only
   Ctl& ctl = *reinterpret_cast<Ctl*>(smem + (kSplit ? 2 : 1) * (A_BYTES + B_BYTES) + (kSplit ? 0 : GI_STAGE_BYTES));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -108,6 +111,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
     tc::mbar_init(&ctl.full, 1);
     tc::mbar_init(&ctl.mma_done, 1);
     tc::mbar_init(&ctl.ready, EPI_THREADS);
+    tc::mbar_init(&ctl.gi_full, EPI_THREADS);     // every gate thread arrives once per step, with or without bytes
     tc::mbar_init(&ctl.empty, CL);                 // one multicast tcgen05.commit arrive per CTA of the cluster (incl. this one)
     tc::mbar_fence_init();
     ctl.maxlen = 0;
@@ -182,25 +186,24 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
     const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     const uint32_t a_row_off = (m >> 3) * 128 + (m & 7) * 16;
 
-    // gi of step s2 for this thread: 3 gates x 16 units.  !kSplit: cp.async into the private staging slots;
-    // kSplit: L2 prefetch of the three 64-byte segments.
+    // gi of step s2.  !kSplit: this thread fetches gate `ug` of its row (48 units, 192 B) into the staging area with one
+    // bulk copy; kSplit: L2 prefetch of the thread's three 64-byte segments.
     auto prefetch_gi = [&](int s2) {
-      if (s2 < len) {
-        const int t2 = dir ? (len - 1 - s2) : s2;
-        const float* gp = gi + ((int64_t)b * T + t2) * gi_ld + dir * G3 + j0;
+      if (kSplit) {
+        if (s2 < len) {
+          const int t2 = dir ? (len - 1 - s2) : s2;
+          const float* gp = gi + ((int64_t)b * T + t2) * gi_ld + dir * G3 + j0;
 #pragma unroll
-        for (int g = 0; g < 3; ++g) {
-          if (kSplit) {
-            asm volatile("prefetch.global.L2 [%0];\n" ::"l"(gp + g * H));
-          } else {
-#pragma unroll
-            for (int v = 0; v < 4; ++v)
-              asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(tc::smem_u32(gstage + (g * 4 + v) * EPI_THREADS + tid)),
-                           "l"(gp + g * H + v * 4) : "memory");
-          }
+          for (int g = 0; g < 3; ++g) asm volatile("prefetch.global.L2 [%0];\n" ::"l"(gp + g * H));
         }
+      } else if (s2 < len) {
+        const int t2 = dir ? (len - 1 - s2) : s2;
+        const float* gp = gi + ((int64_t)b * T + t2) * gi_ld + dir * G3 + ug * H + (int)rank * U;
+        tc::mbar_arrive_expect_tx(&ctl.gi_full, U * 4);
+        tc::bulk_copy_g2s(tc::smem_u32(gstage + (ug * BM + m) * GROW), gp, U * 4, &ctl.gi_full);
+      } else {
+        tc::mbar_arrive(&ctl.gi_full);
       }
-      if (!kSplit) asm volatile("cp.async.commit_group;\n" ::: "memory");
     };
     prefetch_gi(0);
     for (int s = 0; s < maxlen; ++s) {
@@ -218,12 +221,16 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
         }
         prefetch_gi(s + 1);
       } else {
-        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        tc::mbar_wait_bounded(&ctl.gi_full, s & 1);
         if (act) {
 #pragma unroll
-          for (int v = 0; v < 12; ++v) g4[v] = gstage[v * EPI_THREADS + tid];
+          for (int g = 0; g < 3; ++g)
+#pragma unroll
+            for (int v = 0; v < 4; ++v)
+              g4[g * 4 + v] = *reinterpret_cast<const float4*>(gstage + (g * BM + m) * GROW + ug * UT + v * 4);
         }
-        if (!kSplit) prefetch_gi(s + 1);   // slots are in registers now: a whole step of prefetch distance
+        asm volatile("bar.sync 1, %0;\n" ::"n"(EPI_THREADS) : "memory");   // every row of the staging area has been read
+        if (s + 1 < maxlen) prefetch_gi(s + 1);                    // a whole step of prefetch distance
       }
       if (s >= 1) {
         tc::mbar_wait_bounded(&ctl.mma_done, (s - 1) & 1);
