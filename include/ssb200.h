@@ -133,13 +133,16 @@ int ssb_gemm_tc(const float* A1, int64_t lda1, int64_t K1, const float* A2, int6
 /* K3b on the tensor cores (cluster of 4 CTAs, W_hh resident in shared memory as bf16, tcgen05.mma per
  * step, h slices exchanged by bulk DSMEM copies).  Same semantics/layouts as ssb_gru_layer_fwd, except that
  * gi must already include b_ih + (b_hr, b_hz, 0) -- build that bias with ssb_gru_fold_bias and pass it to the
- * projection GEMM.  order (nullable) = clip index per batch slot (e.g. sorted by length). passes = 1 or 3. */
+ * projection GEMM.  order (nullable) = clip index per batch slot (e.g. sorted by length). passes = 1 or 3.
+ * gi_layout 0: gi columns [dir][gate][192] (nn.GRU's row order of weight_ih); gi_layout 1 (passes = 1, gates = NULL):
+ * GRU-blocked columns [dir][rank][gate][48] written through ssb_proj_prepack / ssb_gru_fold_bias with gru_blocked = 1,
+ * staged per step by a producer warp with one 576-byte bulk copy per clip. */
 int ssb_gru_fold_bias(const float* bih_f, const float* bhh_f, const float* bih_r, const float* bhh_r,
-                      float* out1152, void* stream);
+                      float* out1152, int32_t gru_blocked, void* stream);
 int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_t* lengths, const int32_t* order,
                          int64_t B, int64_t T, int32_t hidden,
                          const float* whh_f, const float* bhh_f, const float* whh_r, const float* bhh_r,
-                         float* out, float* gates, int32_t passes, void* stream);
+                         float* out, float* gates, int32_t passes, int32_t gi_layout, void* stream);
 
 /* K2 on the tensor cores: same contract as ssb_roi_cnn_fwd plus `passes` (1 = single fp16 pass, 3 = hi/lo split,
  * fp32-parity grade).  All three convolutions are tcgen05 GEMMs with the 2x2 max-pools folded into N; passes = 1 runs
@@ -153,10 +156,13 @@ int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int64_t B, int
  * C[M, N] = [A1 | A2] . [W_a ; W_b]^T + bias (nn.GRU's x W_ih^T + b_ih, train_model_official.py:261-267, forward and
  * reverse direction stacked: N = 2 x 576).  ssb_proj_prepack converts the weights once into fp16 blocks that the GEMM
  * streams with bulk async copies (a derived cache of the state-dict tensors; rebuild when they change);
- * `packed` is caller-owned, ssb_proj_packed_bytes(N, K1, K2) bytes.  Rows of padded frames are not written. */
+ * `packed` is caller-owned, ssb_proj_packed_bytes(N, K1, K2) bytes.  Rows of padded frames are not written.
+ * gru_blocked = 1 permutes the output columns from [dir][gate][192] to [dir][rank 0..3][gate][48], the order in which
+ * one CTA of the recurrence cluster reads them (ssb_gru_layer_fwd_tc gi_layout = 1); the bias must be in the same order
+ * (ssb_gru_fold_bias gru_blocked = 1). */
 int64_t ssb_proj_packed_bytes(int64_t N, int64_t K1, int64_t K2);
 int ssb_proj_prepack(const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int64_t K1, int64_t K2,
-                     void* packed, void* stream);
+                     int32_t gru_blocked, void* packed, void* stream);
 int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
                   const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
                   const int64_t* lengths, int64_t T, void* stream);

@@ -40,7 +40,7 @@ __host__ __device__ constexpr int kp_of(int K1, int K2) { return round_up(round_
 
 // packed[(nt * nkb + kb) * W_BLOCK + (k/8) * CHUNK + (r/8) * 128 + (r%8) * 16 + (k%8) * 2]  for row nt*128 + r, column kb*64 + k
 __global__ void prepack_kernel(const float* __restrict__ Wa, const float* __restrict__ Wb, int64_t ldw, int n_each,
-                               int K1, int K2, int N, uint8_t* __restrict__ packed) {
+                               int K1, int K2, int N, int gru_blocked, uint8_t* __restrict__ packed) {
   const int K1p = round_up(K1, 8), Kp = kp_of(K1, K2), nkb = Kp / KB;
   const int items = round_up(N, BN) * (Kp / 8);          // one item = 8 consecutive k of one row
   for (int it = blockIdx.x * blockDim.x + threadIdx.x; it < items; it += gridDim.x * blockDim.x) {
@@ -53,7 +53,14 @@ __global__ void prepack_kernel(const float* __restrict__ Wa, const float* __rest
       if (kk < K1p) { if (kk < K1) col = kk; }
       else if (kk - K1p < K2) col = K1 + (kk - K1p);
       float v = 0.f;
-      if (n < N && col >= 0) v = n < n_each ? Wa[(int64_t)n * ldw + col] : Wb[(int64_t)(n - n_each) * ldw + col];
+      if (n < N && col >= 0) {
+        int r = n % n_each;                                   // source row inside its direction's matrix
+        if (gru_blocked) {                                    // packed row [rank][gate][u] <- W row gate * hid + rank * (hid/4) + u
+          const int hid = n_each / 3, u4 = hid / 4;
+          r = ((r % (3 * u4)) / u4) * hid + (r / (3 * u4)) * u4 + r % u4;
+        }
+        v = n < n_each ? Wa[(int64_t)r * ldw + col] : Wb[(int64_t)r * ldw + col];
+      }
       x[j] = v;
     }
     const int nt = n / BN, r = n % BN, kb = c / (KB / 8), kc = c % (KB / 8);
@@ -252,17 +259,21 @@ extern "C" int64_t ssb_proj_packed_bytes(int64_t N, int64_t K1, int64_t K2) {
 
 // Packs [W_a ; W_b] (n_each rows each, row stride ldw, K1+K2 columns; W_b may be NULL with N = n_each) into the
 // fp16 block layout ssb_proj_gemm streams.  A derived cache of the state-dict tensors: rebuild after they change.
+// gru_blocked = 1 (n_each = 3 * hidden, hidden % 4 == 0): output column order becomes [dir][rank 0..3][gate r,z,n][hidden/4]
+// instead of [dir][gate][hidden], so that the 3 x 48 values one GRU cluster CTA needs of a row are contiguous
+// (ssb_gru_layer_fwd_tc gi_layout = 1); the bias passed to ssb_proj_gemm must use the same order (ssb_gru_fold_bias).
 extern "C" int ssb_proj_prepack(const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int64_t K1, int64_t K2,
-                                void* packed, void* stream) {
+                                int32_t gru_blocked, void* packed, void* stream) {
   using namespace ssb;
   using namespace ssb::gemm2;
   SSB_REQUIRE(W_a && packed, "null pointer");
   SSB_REQUIRE(K1 > 0 && K2 >= 0 && n_each > 0, "bad shape");
   SSB_REQUIRE(((uintptr_t)packed & 15) == 0, "packed must be 16-byte aligned");
+  SSB_REQUIRE(!gru_blocked || n_each % 12 == 0, "GRU-blocked order needs n_each = 3 * hidden with hidden % 4 == 0");
   const int N = (int)(W_b ? 2 * n_each : n_each);
   SSB_REQUIRE(kp_of((int)K1, (int)K2) <= MAX_KP && N <= MAX_N, "K > 384 or N > 1152 not supported");
   const int items = round_up(N, BN) * (kp_of((int)K1, (int)K2) / 8);
-  prepack_kernel<<<cdiv(items, 256), 256, 0, (cudaStream_t)stream>>>(W_a, W_b ? W_b : W_a, ldw, (int)n_each, (int)K1, (int)K2, N,
+  prepack_kernel<<<cdiv(items, 256), 256, 0, (cudaStream_t)stream>>>(W_a, W_b ? W_b : W_a, ldw, (int)n_each, (int)K1, (int)K2, N, gru_blocked,
                                                                    reinterpret_cast<uint8_t*>(packed));
   SSB_LAUNCH_CHECK();
   return SSB_OK;

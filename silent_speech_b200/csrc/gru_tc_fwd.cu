@@ -38,18 +38,25 @@ constexpr int UT = 16;                     // hidden units per gate thread
 constexpr int TMEM_COLS = 256;
 
 struct Ctl {
-  uint64_t full, mma_done, empty, ready, gi_full;
+  uint64_t full, mma_done, empty, ready, gi_full, gi_rd[4];
   uint32_t tmem_base;
   int maxlen;
 };
 
-// single-pass mode has shared memory to spare: the next step's input projections are staged in shared memory so
-// their HBM latency never sits on the step's critical path.  Every gate thread issues ONE 192-byte bulk copy (its
-// row's 48 units of gate `ug`) that completes on the `gi_full` mbarrier -- 12 LDGSTS + 12 address bumps per thread
-// were a fifth of the step's issue slots.  Rows are padded to 208 B so that a quarter-warp's LDS.128 of eight
-// consecutive rows hits eight different bank groups.  Split mode (two operand copies resident) prefetches into L2 only.
-constexpr int GROW = 52;                                     // floats per staged row: 48 + 4 pad
-constexpr int GI_STAGE_BYTES = 3 * BM * GROW * 4;            // [3 gates][128 rows][52]: 79,872
+// single-pass mode has shared memory to spare: the next step's input projections are staged in shared memory by bulk
+// copies that complete on the `gi_full` mbarrier, so their HBM latency never sits on the step's critical path.  A bulk
+// copy costs its issuing warp ~90 cycles whatever its size (the per-lane UBLKCP loop), so the fewer the better:
+//   kBlk (gi written by the projection GEMM in the "GRU-blocked" column order [dir][rank][gate][48 units], see
+//        ssb_proj_prepack): a row's 144 values for this CTA are ONE contiguous 576-byte segment.  The three gate warps
+//        of a TMEM lane quarter share 32 rows: once all three have read step s (a 96-thread named barrier) each issues
+//        the copies of every third row for step s+1 -- 128 copies per step and CTA, ~11 per warp.
+//   !kBlk (standard column order [dir][gate][192]): every gate thread issues one 192-byte copy (gate `ug` of its row),
+//        384 per step, 32 per warp, after a barrier over all gate threads.
+// Rows are padded (592 B / 208 B) so that a quarter-warp's LDS.128 of eight consecutive rows hits eight different bank
+// groups.  Split mode (two operand copies resident) prefetches into L2 only.
+constexpr int GROW = 52;                                     // !kBlk: floats per staged (gate,row): 48 + 4 pad
+constexpr int GROWB = 148;                                   // kBlk: floats per staged row: 144 + 4 pad
+constexpr int GI_STAGE_BYTES = 3 * BM * GROW * 4;            // 79,872 (>= 128 * 148 * 4 = 75,776)
 template <bool kSplit>
 constexpr size_t smem_bytes() { return (kSplit ? 2 : 1) * (A_BYTES + B_BYTES) + (kSplit ? 0 : GI_STAGE_BYTES) + sizeof(Ctl); }
 
@@ -64,7 +71,7 @@ __device__ __forceinline__ float tanh_fast(float x) {
   return copysignf(__fdividef(1.0f - e, 1.0f + e), x);
 }
 
-template <bool kSplit, bool kSave>
+template <bool kSplit, bool kSave, bool kBlk>
 __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(THREADS, 1)
 gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
                   const float* __restrict__ whh_f, const float* __restrict__ whh_r,
@@ -112,6 +119,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
     tc::mbar_init(&ctl.mma_done, 1);
     tc::mbar_init(&ctl.ready, EPI_THREADS);
     tc::mbar_init(&ctl.gi_full, EPI_THREADS);     // every gate thread arrives once per step, with or without bytes
+    for (int i = 0; i < 4; ++i) tc::mbar_init(&ctl.gi_rd[i], 96);   // kBlk: the three gate warps of a TMEM lane quarter
     tc::mbar_init(&ctl.empty, CL);                 // one multicast tcgen05.commit arrive per CTA of the cluster (incl. this one)
     tc::mbar_fence_init();
     ctl.maxlen = 0;
@@ -196,6 +204,19 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
 #pragma unroll
           for (int g = 0; g < 3; ++g) asm volatile("prefetch.global.L2 [%0];\n" ::"l"(gp + g * H));
         }
+      } else if (kBlk) {
+        // rows of this lane quarter are dealt out to its three warps: lane l of warp `ug` fetches row m when l % 3 == ug
+        if (lane % 3 == ug && s2 < len) {
+          const int t2 = dir ? (len - 1 - s2) : s2;
+          const float* gp = gi + ((int64_t)b * T + t2) * gi_ld + dir * G3 + (int)rank * NG;
+          // all three readers of the row are done with step s2-1.  Their reads were generic-proxy LDS, the refill is an
+          // async-proxy write: without the proxy fence the copy can overtake them (seen as a rare stale-row race).
+          if (s2 >= 1) { tc::mbar_wait_bounded(&ctl.gi_rd[warp & 3], (s2 - 1) & 1); tc::fence_async_smem(); }
+          tc::mbar_arrive_expect_tx(&ctl.gi_full, NG * 4);
+          tc::bulk_copy_g2s(tc::smem_u32(gstage + m * GROWB), gp, NG * 4, &ctl.gi_full);
+        } else {
+          tc::mbar_arrive(&ctl.gi_full);
+        }
       } else if (s2 < len) {
         const int t2 = dir ? (len - 1 - s2) : s2;
         const float* gp = gi + ((int64_t)b * T + t2) * gi_ld + dir * G3 + ug * H + (int)rank * U;
@@ -227,9 +248,23 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
           for (int g = 0; g < 3; ++g)
 #pragma unroll
             for (int v = 0; v < 4; ++v)
-              g4[g * 4 + v] = *reinterpret_cast<const float4*>(gstage + (g * BM + m) * GROW + ug * UT + v * 4);
+              g4[g * 4 + v] = kBlk ? *reinterpret_cast<const float4*>(gstage + m * GROWB + g * U + ug * UT + v * 4)
+                                   : *reinterpret_cast<const float4*>(gstage + (g * BM + m) * GROW + ug * UT + v * 4);
         }
-        asm volatile("bar.sync 1, %0;\n" ::"n"(EPI_THREADS) : "memory");   // every row of the staging area has been read
+        // The staging rows are refilled by OTHER threads right after the barrier below, and a bulk copy of an L2-resident
+        // row can land while this warp's LDS are still queued in the memory pipe (BAR does not drain loads): make the
+        // loaded registers a dependency of the barrier, so the reads have been performed when the warp arrives.
+        if (act) {
+#pragma unroll
+          for (int v = 0; v < 12; ++v) asm volatile("" : "+f"(g4[v].x), "+f"(g4[v].y), "+f"(g4[v].z), "+f"(g4[v].w));
+        }
+        if (kBlk) {
+          tc::mbar_arrive(&ctl.gi_rd[warp & 3]);                   // non-blocking; only the lanes that refill a row wait on it
+        } else {
+          __syncwarp();
+          asm volatile("bar.sync 1, %0;\n" ::"n"(EPI_THREADS) : "memory");
+          tc::fence_async_smem();                                  // generic reads above -> async-proxy refill below
+        }
         if (s + 1 < maxlen) prefetch_gi(s + 1);                    // a whole step of prefetch distance
       }
       if (s >= 1) {
@@ -317,10 +352,12 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
 
 // gi_bias[d*576 + i] = b_ih_d[i] + (i < 384 ? b_hh_d[i] : 0)
 __global__ void fold_bias_kernel(const float* __restrict__ bih_f, const float* __restrict__ bhh_f,
-                                 const float* __restrict__ bih_r, const float* __restrict__ bhh_r, float* __restrict__ o) {
+                                 const float* __restrict__ bih_r, const float* __restrict__ bhh_r, float* __restrict__ o, int blocked) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= 2 * G3) return;
-  const int d = i / G3, k = i % G3;
+  const int d = i / G3;
+  int k = i % G3;
+  if (blocked) k = ((k % NG) / U) * H + (k / NG) * U + k % U;        // [rank][gate][48] -> gate * 192 + rank * 48 + u
   const float* bi = d ? bih_r : bih_f;
   const float* bh = d ? bhh_r : bhh_f;
   o[i] = bi[k] + (k < 2 * H ? bh[k] : 0.f);
@@ -330,10 +367,10 @@ __global__ void fold_bias_kernel(const float* __restrict__ bih_f, const float* _
 }  // namespace ssb
 
 extern "C" int ssb_gru_fold_bias(const float* bih_f, const float* bhh_f, const float* bih_r, const float* bhh_r,
-                                 float* out1152, void* stream) {
+                                 float* out1152, int32_t gru_blocked, void* stream) {
   using namespace ssb;
   SSB_REQUIRE(bih_f && bhh_f && bih_r && bhh_r && out1152, "null pointer");
-  grutc::fold_bias_kernel<<<cdiv(2 * grutc::G3, 256), 256, 0, (cudaStream_t)stream>>>(bih_f, bhh_f, bih_r, bhh_r, out1152);
+  grutc::fold_bias_kernel<<<cdiv(2 * grutc::G3, 256), 256, 0, (cudaStream_t)stream>>>(bih_f, bhh_f, bih_r, bhh_r, out1152, gru_blocked);
   SSB_LAUNCH_CHECK();
   return SSB_OK;
 }
@@ -342,10 +379,12 @@ extern "C" int ssb_gru_fold_bias(const float* bih_f, const float* bhh_f, const f
 // b_ih + (b_hr, b_hz, 0) (ssb_gru_fold_bias); bhh_* are the full b_hh vectors (the n part is read).
 // order (nullable) = clip index per batch slot, e.g. sorted by length so that tiles are homogeneous.
 // passes = 1 (bf16) or 3 (split-bf16).  Output / gates layouts as ssb_gru_layer_fwd.
+// gi_layout: 0 = columns [dir][gate][192]; 1 = GRU-blocked [dir][rank][gate][48] as written through
+// ssb_proj_prepack(.., gru_blocked = 1) + ssb_gru_fold_bias(.., gru_blocked = 1) (passes = 1, gates = NULL only).
 extern "C" int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_t* lengths, const int32_t* order,
                                     int64_t B, int64_t T, int32_t hidden,
                                     const float* whh_f, const float* bhh_f, const float* whh_r, const float* bhh_r,
-                                    float* out, float* gates, int32_t passes, void* stream) {
+                                    float* out, float* gates, int32_t passes, int32_t gi_layout, void* stream) {
   using namespace ssb;
   using namespace ssb::grutc;
   SSB_REQUIRE(gi && lengths && whh_f && bhh_f && whh_r && bhh_r && out, "null pointer");
@@ -353,18 +392,20 @@ extern "C" int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_
   SSB_REQUIRE(gi_ld >= 2 * G3 && gi_ld % 4 == 0 && ((uintptr_t)gi & 15) == 0, "gi must be 16-byte aligned rows of >= 1152");
   SSB_REQUIRE(((uintptr_t)whh_f & 15) == 0 && ((uintptr_t)whh_r & 15) == 0 && ((uintptr_t)out & 15) == 0, "alignment");
   SSB_REQUIRE(passes == 1 || passes == 3, "passes must be 1 or 3");
+  SSB_REQUIRE(gi_layout == 0 || (gi_layout == 1 && passes == 1 && !gates), "GRU-blocked gi: single-pass inference only");
   if (B == 0) return SSB_OK;
   dim3 grid(CL * cdiv(B, BM), 2), block(THREADS);
   cudaStream_t st = (cudaStream_t)stream;
-#define SSB_LAUNCH_GRUTC(SPLIT, SAVE)                                                                          \
-  do {                                                                                                          \
-    SSB_CUDA(cudaFuncSetAttribute(gru_tc_fwd_kernel<SPLIT, SAVE>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
-                                  (int)smem_bytes<SPLIT>()));                                                   \
-    gru_tc_fwd_kernel<SPLIT, SAVE><<<grid, block, smem_bytes<SPLIT>(), st>>>(                                   \
-        gi, gi_ld, whh_f, whh_r, bhh_f + 2 * H, bhh_r + 2 * H, lengths, order, (int)B, (int)T, out, gates);\
+#define SSB_LAUNCH_GRUTC(SPLIT, SAVE, BLK)                                                                          \
+  do {                                                                                                               \
+    SSB_CUDA(cudaFuncSetAttribute(gru_tc_fwd_kernel<SPLIT, SAVE, BLK>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                  (int)smem_bytes<SPLIT>()));                                                        \
+    gru_tc_fwd_kernel<SPLIT, SAVE, BLK><<<grid, block, smem_bytes<SPLIT>(), st>>>(                                   \
+        gi, gi_ld, whh_f, whh_r, bhh_f + 2 * H, bhh_r + 2 * H, lengths, order, (int)B, (int)T, out, gates);          \
   } while (0)
-  if (passes == 3) { if (gates) SSB_LAUNCH_GRUTC(true, true); else SSB_LAUNCH_GRUTC(true, false); }
-  else             { if (gates) SSB_LAUNCH_GRUTC(false, true); else SSB_LAUNCH_GRUTC(false, false); }
+  if (passes == 3)    { if (gates) SSB_LAUNCH_GRUTC(true, true, false); else SSB_LAUNCH_GRUTC(true, false, false); }
+  else if (gi_layout) { SSB_LAUNCH_GRUTC(false, false, true); }
+  else                { if (gates) SSB_LAUNCH_GRUTC(false, true, false); else SSB_LAUNCH_GRUTC(false, false, false); }
 #undef SSB_LAUNCH_GRUTC
   SSB_LAUNCH_CHECK();
   return SSB_OK;

@@ -74,12 +74,15 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
             _project(A2d, pl["weight_ih"], pl["bias_ih"], gi2d, lengths, T, extra=extra)
             return ops.gru_layer_fwd(gi, lengths, pl["weight_hh"][0], pl["bias_hh"][0], pl["weight_hh"][1],
                                      pl["bias_hh"][1], gates=gates)
-        fold = ops.gru_fold_bias(pl["bias_ih"][0], pl["bias_hh"][0], pl["bias_ih"][1], pl["bias_hh"][1])
+        # single-pass inference: the GEMM writes gi in the GRU-blocked column order (a CTA's 144 values of a row contiguous)
+        blk = passes == 1 and gates is None
+        fold = ops.gru_fold_bias(pl["bias_ih"][0], pl["bias_hh"][0], pl["bias_ih"][1], pl["bias_hh"][1], gru_blocked=blk)
         if passes == 1:                  # single-pass fp16: one persistent GEMM for both directions, packed weights
-            packed = ops.proj_prepack(pl["weight_ih"][0], pl["weight_ih"][1], A2d.shape[1], 0 if extra is None else extra.shape[1])
+            packed = ops.proj_prepack(pl["weight_ih"][0], pl["weight_ih"][1], A2d.shape[1], 0 if extra is None else extra.shape[1],
+                                      gru_blocked=blk)
             ops.proj_gemm(A2d, packed, fold, gi2d, 2 * G3, A2=extra, lengths=lengths, T=T)
             return ops.gru_layer_fwd_tc(gi, lengths, pl["weight_hh"][0], pl["bias_hh"][0], pl["weight_hh"][1],
-                                        pl["bias_hh"][1], passes=passes, order=order, gates=gates)
+                                        pl["bias_hh"][1], passes=passes, order=order, gates=gates, gi_blocked=blk)
         for d in (0, 1):
             ops.gemm_tc(A2d, pl["weight_ih"][d], fold[d * G3:(d + 1) * G3], gi2d, A2=extra, passes=passes,
                         lengths=lengths, T=T, c_col0=d * G3)

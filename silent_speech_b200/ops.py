@@ -238,7 +238,7 @@ def gemm_tc(A1: torch.Tensor, W: torch.Tensor, bias, C2d: torch.Tensor, A2: Opti
     return C2d
 
 
-def proj_prepack(W_a: torch.Tensor, W_b: Optional[torch.Tensor], K1: int, K2: int = 0) -> torch.Tensor:
+def proj_prepack(W_a: torch.Tensor, W_b: Optional[torch.Tensor], K1: int, K2: int = 0, gru_blocked: bool = False) -> torch.Tensor:
     """[W_a ; W_b] (each [n_each, K1+K2] fp32) -> fp16 block layout streamed by proj_gemm (a derived cache)."""
     _need(W_a, torch.float32, "W_a")
     if W_b is not None:
@@ -249,7 +249,8 @@ def proj_prepack(W_a: torch.Tensor, W_b: Optional[torch.Tensor], K1: int, K2: in
     L.ssb_proj_packed_bytes.restype = i64
     nbytes = L.ssb_proj_packed_bytes(i64(N), i64(K1), i64(K2))
     packed = torch.empty(nbytes, device=W_a.device, dtype=torch.uint8)
-    check(L.ssb_proj_prepack(ptr(W_a), ptr(W_b), i64(W_a.stride(0)), i64(n_each), i64(K1), i64(K2), ptr(packed), stream_ptr()))
+    check(L.ssb_proj_prepack(ptr(W_a), ptr(W_b), i64(W_a.stride(0)), i64(n_each), i64(K1), i64(K2),
+                             i32(1 if gru_blocked else 0), ptr(packed), stream_ptr()))
     return packed
 
 
@@ -264,13 +265,13 @@ def proj_gemm(A1: torch.Tensor, packed: torch.Tensor, bias, C2d: torch.Tensor, N
     return C2d
 
 
-def gru_fold_bias(bih_f, bhh_f, bih_r, bhh_r) -> torch.Tensor:
+def gru_fold_bias(bih_f, bhh_f, bih_r, bhh_r, gru_blocked: bool = False) -> torch.Tensor:
     out = torch.empty(2 * 3 * HIDDEN, device=bih_f.device, dtype=torch.float32)
-    check(_lib.lib().ssb_gru_fold_bias(ptr(bih_f), ptr(bhh_f), ptr(bih_r), ptr(bhh_r), ptr(out), stream_ptr()))
+    check(_lib.lib().ssb_gru_fold_bias(ptr(bih_f), ptr(bhh_f), ptr(bih_r), ptr(bhh_r), ptr(out), i32(1 if gru_blocked else 0), stream_ptr()))
     return out
 
 
-def gru_layer_fwd_tc(gi, lengths, whh_f, bhh_f, whh_r, bhh_r, passes=3, order=None, out=None, gates=None):
+def gru_layer_fwd_tc(gi, lengths, whh_f, bhh_f, whh_r, bhh_r, passes=3, order=None, out=None, gates=None, gi_blocked=False):
     """Tensor-core recurrence; gi must include the folded bias (gru_fold_bias)."""
     _need(gi, torch.float32, "gi")
     _need(lengths, torch.int64, "lengths")
@@ -281,7 +282,7 @@ def gru_layer_fwd_tc(gi, lengths, whh_f, bhh_f, whh_r, bhh_r, passes=3, order=No
         _need(order, torch.int32, "order")
     check(_lib.lib().ssb_gru_layer_fwd_tc(ptr(gi), i64(ld), ptr(lengths), ptr(order), i64(B), i64(T), i32(HIDDEN),
                                           ptr(whh_f), ptr(bhh_f), ptr(whh_r), ptr(bhh_r), ptr(out), ptr(gates),
-                                          i32(passes), stream_ptr()))
+                                          i32(passes), i32(1 if gi_blocked else 0), stream_ptr()))
     return out
 
 

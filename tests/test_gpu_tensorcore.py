@@ -73,6 +73,15 @@ def test_gru_tc_recurrence_vs_fp32_kernel(B, T):
             assert torch.all(out[~mask] == 0)
             eg = rel_err(gates * mask[..., None, None, None], gates_ref * mask[..., None, None, None])
             assert eg < tol * 5, (passes, eg)
+    # GRU-blocked gi (columns [dir][rank][gate][48], fed by the producer warp): same arithmetic on the same values,
+    # so the result must equal the standard-layout single-pass result bit for bit
+    perm = torch.arange(1152).view(2, 3, 4, 48).permute(0, 2, 1, 3).reshape(-1).to(dev)     # blocked col -> standard col
+    gi_b = gi_f[:, :, perm].contiguous()
+    for od in (None, order):
+        std = ops.gru_layer_fwd_tc(gi_f, Ld, *w, passes=1, order=od)
+        blk = ops.gru_layer_fwd_tc(gi_b, Ld, *w, passes=1, order=od, gi_blocked=True)
+        torch.cuda.synchronize()
+        assert torch.equal(std, blk)
 
 
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("tc3", 1e-4), ("fp16", 1e-3)])
@@ -196,3 +205,12 @@ def test_proj_gemm_vs_fp64(M, n_each, K1, K2, T):
         live = torch.ones(M, dtype=torch.bool)
     assert rel_err(out[live][:, :N], ref16[live]) < 2e-6
     assert rel_err(out[live][:, :N], ref[live]) < 3e-3
+    if n_each % 12 == 0:
+        # GRU-blocked column order [dir][rank][gate][n_each/12]: the same numbers, permuted columns (bit for bit)
+        u4 = n_each // 12
+        perm = torch.arange(N).view(2, 3, 4, u4).permute(0, 2, 1, 3).reshape(-1)           # blocked col -> standard col
+        C2 = torch.full((M, N), -7.0, device=dev)
+        packed_b = ops.proj_prepack(Wa.to(dev), Wb.to(dev), K1, K2, gru_blocked=True)
+        ops.proj_gemm(A1.to(dev), packed_b, b[perm].to(dev), C2, N, A2=None if A2 is None else A2.to(dev), lengths=L, T=T)
+        torch.cuda.synchronize()
+        assert torch.equal(C2.cpu()[live], out[live][:, :N][:, perm])

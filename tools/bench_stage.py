@@ -13,6 +13,7 @@ ap.add_argument("--batch", type=int, default=4096)
 ap.add_argument("--layer", type=int, default=1)
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--lengths", default="full")
+ap.add_argument("--standard-gi", action="store_true", help="gru: feed the single-pass kernel gi in nn.GRU column order (per-thread bulk copies) instead of the GRU-blocked order")
 a = ap.parse_args()
 dev = torch.device("cuda")
 B, T, G3, H = a.batch, 90, 576, 192
@@ -87,5 +88,5 @@ elif a.stage == "gru":
     w = [p["gru.weight_hh" + sfx], p["gru.bias_hh" + sfx], p["gru.weight_hh" + sfx + "_reverse"], p["gru.bias_hh" + sfx + "_reverse"]]
     order = torch.argsort(L, descending=True).to(torch.int32)
     out = torch.empty(B, T, 2 * H, device=dev)
-    best, mean = timeit(lambda: ops.gru_layer_fwd_tc(gi, L, *w, passes=passes, order=order, out=out))
+    best, mean = timeit(lambda: ops.gru_layer_fwd_tc(gi, L, *w, passes=passes, order=order, out=out, gi_blocked=(passes == 1 and not a.standard_gi)))
     print(f"gru layer {a.precision} B={B}: best {best:.3f} ms mean {mean:.3f} ms  {best * 1e3 / T:.2f} us per step")

@@ -52,3 +52,23 @@ for passes in (3, 1):
         del junk
     torch.cuda.synchronize()
     print(f"passes={passes}: {reps} reps, gemm mismatches {bad_g}, gru mismatches {bad_r}")
+
+# single-pass recurrence fed through the GRU-blocked gi layout (bulk-copy staging): run-to-run AND against the standard layout
+perm = torch.arange(2 * G3, device=dev).view(2, 3, 4, 48).permute(0, 2, 1, 3).reshape(-1)
+for Bs, Ts in ((128, 3), (129, 5), (260, 64), (700, 40)):
+    g = torch.Generator().manual_seed(Bs)
+    Ls = torch.randint(1, Ts + 1, (Bs,), generator=g); Ls[0] = Ts
+    Ls = Ls.to(dev)
+    gi_s = (torch.randn(Bs, Ts, 2 * G3, generator=g) * 0.7).to(dev)
+    gi_b = gi_s[:, :, perm].contiguous()
+    od = torch.argsort(Ls, descending=True).to(torch.int32)
+    bad = 0
+    for o in (None, od):
+        std = ops.gru_layer_fwd_tc(gi_s, Ls, whh[0], bhh[0], whh[1], bhh[1], passes=1, order=o)
+        for it in range(reps):
+            which = it & 1
+            out = ops.gru_layer_fwd_tc(gi_b if which else gi_s, Ls, whh[0], bhh[0], whh[1], bhh[1], passes=1, order=o, gi_blocked=bool(which))
+            if not torch.equal(out, std):
+                bad += 1
+    torch.cuda.synchronize()
+    print(f"gi staging B={Bs} T={Ts}: {2 * reps} runs (standard / blocked alternating), mismatches {bad}")
