@@ -278,10 +278,12 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         uint32_t t1 = 0, t2 = 0;
 #pragma unroll
         for (int i = 0; i < ST / 32; ++i) { t1 += mz.red[i]; t2 += mz.red[8 + i]; }
-        const double S1 = (double)t1, S2 = (double)t2;
-        const double var_u = fmax(S2 - S1 * S1 / (double)NPIX, 0.0) / (double)(NPIX - 1);
-        mean_u = (float)(S1 / (double)NPIX);
-        inv_s = (float)(1.0 / fmax(sqrt(var_u), 255.0e-6));
+        // N*S2 - S1^2 is an exact 64-bit integer (< 2^41), so the cancellation happens before any rounding and the rest
+        // is fp32: unbiased variance in raw pixel units, std clamped at 1e-6 * 255 (train_model_official.py:289-291)
+        const unsigned long long d = (unsigned long long)NPIX * t2 - (unsigned long long)t1 * t1;
+        const float var_u = (float)d * (1.0f / ((float)NPIX * (float)(NPIX - 1)));
+        mean_u = (float)t1 * (1.0f / (float)NPIX);               // t1 < 2^24 and NPIX = 9 * 2^9: one rounding
+        inv_s = 1.0f / fmaxf(sqrtf(var_u), 255.0e-6f);
       }
       uint32_t carry_hi = 0, carry_lo = 0;             // lane 31's last pixel of the previous iteration (kRowWarp)
 #pragma unroll
