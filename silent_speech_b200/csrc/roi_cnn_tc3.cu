@@ -285,6 +285,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         mean_u = (float)t1 * (1.0f / (float)NPIX);               // t1 < 2^24 and NPIX = 9 * 2^9: one rounding
         inv_s = 1.0f / fmaxf(sqrtf(var_u), 255.0e-6f);
       }
+      const float nmean = -mean_u * inv_s;
       uint32_t carry_hi = 0, carry_lo = 0;             // lane 31's last pixel of the previous iteration (kRowWarp)
 #pragma unroll
       for (int j = 0; j < WPT; ++j) {
@@ -292,7 +293,9 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           float hi[4], lo[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            hi[k] = ((float)((wv[j] >> (8 * k)) & 0xffu) - mean_u) * inv_s;
+            // byte k -> float through the 2^23 + b bit pattern (one PRMT, one exact FADD), then one FFMA
+            const float xf = __uint_as_float(__byte_perm(wv[j], 0x4B000000u, 0x7440 + k)) - 8388608.0f;
+            hi[k] = fmaf(xf, inv_s, nmean);
             if (kSplit) tc::split_bf16(hi[k], hi[k], lo[k]);
           }
           uint8_t* d = r0 + pixoff[j];
@@ -335,18 +338,21 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       const int ntiles = min(L::STRIP_TILES, 9 - tile0);
       if (9 % L::STRIP_TILES == 0) {                   // full rounds only: hoisted addressing (+16 frame rows per round)
         const uint32_t radd = rnd * (16 * PIX_LD * 2);
+        // all loads first, then all stores: source and destination live in the same buffer, so the compiler would
+        // otherwise keep every load behind the previous store and expose the LDS latency once per item
 #pragma unroll
-        for (int k = 0; k < GIT; ++k) {
+        for (int p = 0; p < L::P; ++p) {
+          uint4 v[GIT];
 #pragma unroll
-          for (int p = 0; p < L::P; ++p) {
+          for (int k = 0; k < GIT; ++k) {
             const uint8_t* src = r0 + p * PIX_BYTES + gsrc[k] + radd;
-            uint4 v;
-            v.x = *reinterpret_cast<const uint32_t*>(src);
-            v.y = *reinterpret_cast<const uint32_t*>(src + 4);
-            v.z = *reinterpret_cast<const uint32_t*>(src + PIX_LD * 2);
-            v.w = *reinterpret_cast<const uint32_t*>(src + PIX_LD * 2 + 4);
-            *reinterpret_cast<uint4*>(r0 + p * L::PATCH_BYTES + gdst[k]) = v;
+            v[k].x = *reinterpret_cast<const uint32_t*>(src);
+            v[k].y = *reinterpret_cast<const uint32_t*>(src + 4);
+            v[k].z = *reinterpret_cast<const uint32_t*>(src + PIX_LD * 2);
+            v[k].w = *reinterpret_cast<const uint32_t*>(src + PIX_LD * 2 + 4);
           }
+#pragma unroll
+          for (int k = 0; k < GIT; ++k) *reinterpret_cast<uint4*>(r0 + p * L::PATCH_BYTES + gdst[k]) = v[k];
         }
       } else {
         // gather the 4x4 patches: item = (k-chunk, pooled pixel); chunk kc holds patch rows 2kc, 2kc+1
