@@ -70,7 +70,9 @@ struct SlotMisc {
 };
 
 struct Shared {                                        // one per CTA, after the slots and the weight operands
-  float b1[C1], b2[C2], b3[C3P];
+  alignas(16) float b1[C1];
+  alignas(16) float b2[C2];
+  alignas(16) float b3[C3P];
   float wfc[E][C3];
   float bfc[E];
   uint32_t tmem_base;
@@ -407,11 +409,14 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           } else {
             tc::tmem_ld_wait();
           }
-          float hi[8], lo[8];
+          float hi[8], lo[8], bb[8];
+          // biases as 16-byte broadcast loads (a scalar LDS per use made them a tenth of the kernel's shared-memory wavefronts)
+          *reinterpret_cast<float4*>(bb) = *reinterpret_cast<const float4*>(sh.b1);
+          *reinterpret_cast<float4*>(bb + 4) = *reinterpret_cast<const float4*>(sh.b1 + 4);
 #pragma unroll
           for (int co = 0; co < 8; ++co) {
             const float m4 = fmaxf(fmaxf(v[co], v[8 + co]), fmaxf(v[16 + co], v[24 + co]));
-            hi[co] = fmaxf(m4 + sh.b1[co], 0.f);
+            hi[co] = fmaxf(m4 + bb[co], 0.f);
             if (kSplit) tc::split_bf16(hi[co], hi[co], lo[co]);          // single pass: pack8 rounds once
           }
           uint32_t off;
@@ -472,7 +477,11 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         if (a2off[tl] >= 0) {
           float hi[8], lo[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) tc::split_bf16(fmaxf(m4[i] + sh.b2[wg * 8 + i], 0.f), hi[i], lo[i]);
+          float bb[8];
+          *reinterpret_cast<float4*>(bb) = *reinterpret_cast<const float4*>(sh.b2 + wg * 8);
+          *reinterpret_cast<float4*>(bb + 4) = *reinterpret_cast<const float4*>(sh.b2 + wg * 8 + 4);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) tc::split_bf16(fmaxf(m4[i] + bb[i], 0.f), hi[i], lo[i]);
           const uint32_t off = (uint32_t)a2off[tl] + wg * PLANE2;
           *reinterpret_cast<uint4*>(r0 + off) = pack8(hi);
           *reinterpret_cast<uint4*>(r0 + A2_BYTES + off) = pack8(lo);
@@ -483,11 +492,13 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         tc::tmem_ld32(tq + dcol + 32, w);
         tc::tmem_ld_wait();
         if (a2off[tl] >= 0) {
-          float hi[16];
+          float hi[16], bb[16];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) *reinterpret_cast<float4*>(bb + 4 * i) = *reinterpret_cast<const float4*>(sh.b2 + 4 * i);
 #pragma unroll
           for (int co = 0; co < 16; ++co) {
             const float m4 = fmaxf(fmaxf(v[co], v[16 + co]), fmaxf(w[co], w[16 + co]));
-            hi[co] = fmaxf(m4 + sh.b2[co], 0.f);
+            hi[co] = fmaxf(m4 + bb[co], 0.f);
           }
           const uint32_t off = (uint32_t)a2off[tl];
           *reinterpret_cast<uint4*>(r0 + off) = pack8(hi);
@@ -567,7 +578,13 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           tc::tmem_ld_wait();
         }
 #pragma unroll
-        for (int c = 0; c < C3; ++c) acc[c] += fmaxf(v[c] + sh.b3[c], 0.f);
+        for (int c4 = 0; c4 < C3 / 4; ++c4) {
+          const float4 bq = *reinterpret_cast<const float4*>(sh.b3 + 4 * c4);
+          acc[4 * c4 + 0] += fmaxf(v[4 * c4 + 0] + bq.x, 0.f);
+          acc[4 * c4 + 1] += fmaxf(v[4 * c4 + 1] + bq.y, 0.f);
+          acc[4 * c4 + 2] += fmaxf(v[4 * c4 + 2] + bq.z, 0.f);
+          acc[4 * c4 + 3] += fmaxf(v[4 * c4 + 3] + bq.w, 0.f);
+        }
       }
     }
     if (q < 3) {
