@@ -112,3 +112,23 @@ def test_gather_rows_shapes(shape, dtype):
     torch.cuda.synchronize()
     assert torch.equal(out.cpu(), src.cpu()[idx])
     assert ops.gather_rows(src, idx[:0].cuda()).shape[0] == 0
+
+
+@pytest.mark.gpu
+def test_train_from_clip_store_reduces_loss(clip_dir):
+    """The whole training data path on the device: ingest -> class-balanced epoch -> augmentation -> fused train step."""
+    from silent_speech_b200 import BiGRUClassifier
+    from silent_speech_b200.train import Trainer
+    path, _ = clip_dir
+    idx = D.scan_clips(path)
+    store = D.ClipStore.from_files(idx.files, idx.label_to_id, 90, True, device="cuda")
+    torch.manual_seed(0)
+    model = BiGRUClassifier(idx.x_dim, len(idx.label_to_id), use_roi=True).cuda()
+    tr = Trainer(model, lr=3e-3, dropout=False)
+    gen = torch.Generator().manual_seed(1)
+    losses = []
+    for ep in range(12):
+        for X, L, R, y in store.epoch(13, weighted=True, generator=gen, augment_seed=100 * ep):
+            losses.append(float(tr.step(X, L, R, y).mean()))
+    assert all(np.isfinite(losses))
+    assert np.mean(losses[-3:]) < 0.7 * np.mean(losses[:3]), losses
