@@ -17,7 +17,6 @@
 // (ssb_gru_fold_bias); b_hn stays separate because it sits inside r * (W_hn h + b_hn).
 #include "common.cuh"
 #include "tc.cuh"
-#include <stdlib.h>
 
 namespace ssb {
 namespace grutc {
@@ -48,10 +47,11 @@ struct Ctl {
 // copy costs its issuing warp ~90 cycles whatever its size (the per-lane UBLKCP loop), so the fewer the better:
 //   kBlk (gi written by the projection GEMM in the "GRU-blocked" column order [dir][rank][gate][48 units], see
 //        ssb_proj_prepack): a row's 144 values for this CTA are ONE contiguous 576-byte segment.  The three gate warps
-//        of a TMEM lane quarter share 32 rows: once all three have read step s (a 96-thread named barrier) each issues
-//        the copies of every third row for step s+1 -- 128 copies per step and CTA, ~11 per warp.
+//        of a TMEM lane quarter share 32 rows: once all three have read step s (the `gi_rd` mbarrier of the quarter,
+//        96 arrivals; only the refilling lanes wait on it, then fence.proxy.async) each issues the copies of every
+//        third row for step s+1 -- 128 copies per step and CTA, ~11 per warp.
 //   !kBlk (standard column order [dir][gate][192]): every gate thread issues one 192-byte copy (gate `ug` of its row),
-//        384 per step, 32 per warp, after a barrier over all gate threads.
+//        384 per step, 32 per warp, after a named barrier over all gate threads + fence.proxy.async.
 // Rows are padded (592 B / 208 B) so that a quarter-warp's LDS.128 of eight consecutive rows hits eight different bank
 // groups.  Split mode (two operand copies resident) prefetches into L2 only.
 constexpr int GROW = 52;                                     // !kBlk: floats per staged (gate,row): 48 + 4 pad
@@ -251,9 +251,8 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
               g4[g * 4 + v] = kBlk ? *reinterpret_cast<const float4*>(gstage + m * GROWB + g * U + ug * UT + v * 4)
                                    : *reinterpret_cast<const float4*>(gstage + (g * BM + m) * GROW + ug * UT + v * 4);
         }
-        // The staging rows are refilled by OTHER threads right after the barrier below, and a bulk copy of an L2-resident
-        // row can land while this warp's LDS are still queued in the memory pipe (BAR does not drain loads): make the
-        // loaded registers a dependency of the barrier, so the reads have been performed when the warp arrives.
+        // The staging rows are refilled by OTHER threads once this thread has signalled below: make the loaded registers
+        // a dependency of that signal, so the reads have been performed (not merely issued) when it is given.
         if (act) {
 #pragma unroll
           for (int v = 0; v < 12; ++v) asm volatile("" : "+f"(g4[v].x), "+f"(g4[v].y), "+f"(g4[v].z), "+f"(g4[v].w));
