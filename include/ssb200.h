@@ -136,10 +136,11 @@ int ssb_gemm_tc(const float* A1, int64_t lda1, int64_t K1, const float* A2, int6
  * projection GEMM.  order (nullable) = clip index per batch slot (e.g. sorted by length). passes = 1 or 3.
  * gi_layout 0: gi columns [dir][gate][192] (nn.GRU's row order of weight_ih); gi_layout 1 (passes = 1, gates = NULL):
  * GRU-blocked columns [dir][rank][gate][48] written through ssb_proj_prepack / ssb_gru_fold_bias with gru_blocked = 1,
- * staged per step by a producer warp with one 576-byte bulk copy per clip. */
+ * staged per step with one 576-byte bulk copy per clip; gi_layout 2: the same column order stored as fp16
+ * (ssb_proj_gemm out_half = 1, gi_ld in fp16 elements), 288-byte copies into two staging buffers, two steps ahead. */
 int ssb_gru_fold_bias(const float* bih_f, const float* bhh_f, const float* bih_r, const float* bhh_r,
                       float* out1152, int32_t gru_blocked, void* stream);
-int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_t* lengths, const int32_t* order,
+int ssb_gru_layer_fwd_tc(const void* gi, int64_t gi_ld, const int64_t* lengths, const int32_t* order,
                          int64_t B, int64_t T, int32_t hidden,
                          const float* whh_f, const float* bhh_f, const float* whh_r, const float* bhh_r,
                          float* out, float* gates, int32_t passes, int32_t gi_layout, void* stream);
@@ -163,9 +164,10 @@ int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int64_t B, int
 int64_t ssb_proj_packed_bytes(int64_t N, int64_t K1, int64_t K2);
 int ssb_proj_prepack(const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int64_t K1, int64_t K2,
                      int32_t gru_blocked, void* packed, void* stream);
+/* out_half = 1: C is fp16 (ldc counts fp16 elements; N, ldc multiples of 8) -- gi for ssb_gru_layer_fwd_tc gi_layout = 2. */
 int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
-                  const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
-                  const int64_t* lengths, int64_t T, void* stream);
+                  const void* packed, const float* bias, void* C, int64_t ldc, int64_t M, int64_t N,
+                  const int64_t* lengths, int64_t T, int32_t out_half, void* stream);
 
 /* K6: batched mouth-ROI crop + BGR->gray + resize to 96x48, bit-exact with OpenCV 4.13.
  * Replaces crop_roi_gray (live_infer_official.py:171-187; flavor 0: INTER_AREA, box in double arithmetic) and

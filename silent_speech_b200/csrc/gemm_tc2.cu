@@ -74,8 +74,8 @@ struct Args {
   const float* A1; int64_t lda1; int K1;
   const float* A2; int64_t lda2; int K2;
   const uint8_t* Wp; const float* bias;
-  float* C; int64_t ldc;
-  int M, N;
+  float* C; int64_t ldc;                                   // out_half: C points at fp16 elements, ldc counts them
+  int M, N, out_half;
   const int64_t* lengths; int T;
 };
 
@@ -219,6 +219,27 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
           for (int i = 0; i < 8; ++i)
             *reinterpret_cast<float4*>(tile + lane * TILE_LD + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
           __syncwarp();
+          if (a.out_half) {
+            // fp16 output: 8 columns (16 bytes) per lane, 8 rows x 4 chunks per store instruction
+            const int r8 = lane >> 2, c8 = lane & 3;
+            const int n8 = nt * BN + cg * 32 + c8 * 8;
+            if (n8 < a.N) {                                  // N is a multiple of 8
+              const float4 b0 = *reinterpret_cast<const float4*>(bias_s + n8), b1 = *reinterpret_cast<const float4*>(bias_s + n8 + 4);
+              uint16_t* c = reinterpret_cast<uint16_t*>(a.C) + (int64_t)row0 * a.ldc + n8;
+#pragma unroll
+              for (int it = 0; it < 4; ++it) {
+                const int r = it * 8 + r8;
+                const float4 o0 = *reinterpret_cast<const float4*>(tile + r * TILE_LD + 8 * c8);
+                const float4 o1 = *reinterpret_cast<const float4*>(tile + r * TILE_LD + 8 * c8 + 4);
+                if ((live_mask >> r) & 1u)
+                  *reinterpret_cast<uint4*>(c + (int64_t)r * a.ldc) =
+                      make_uint4(tc::pack_bf16(o0.x + b0.x, o0.y + b0.y), tc::pack_bf16(o0.z + b0.z, o0.w + b0.w),
+                                 tc::pack_bf16(o1.x + b1.x, o1.y + b1.y), tc::pack_bf16(o1.z + b1.z, o1.w + b1.w));
+              }
+            }
+            __syncwarp();
+            continue;
+          }
           const int n = nt * BN + cg * 32 + cch * 4;
           if (n < a.N) {                                     // N is a multiple of 4
             const float4 bv = *reinterpret_cast<const float4*>(bias_s + n);
@@ -281,9 +302,11 @@ extern "C" int ssb_proj_prepack(const float* W_a, const float* W_b, int64_t ldw,
 
 // C[M, N] = [A1 | A2] . packed^T + bias (fp16 operands, fp32 accumulation in TMEM).  lengths/T (optional): rows of
 // padded frames (m % T >= lengths[m / T]) are not written.  K1, K2, lda1, lda2 multiples of 4; 16-byte aligned bases.
+// out_half = 1: C is an fp16 matrix (ldc in fp16 elements; N, ldc multiples of 8) -- the single-pass recurrence reads gi
+// in fp16 (ssb_gru_layer_fwd_tc gi_layout = 2), which halves this kernel's dominant HBM stream.
 extern "C" int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
-                             const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
-                             const int64_t* lengths, int64_t T, void* stream) {
+                             const void* packed, const float* bias, void* C, int64_t ldc, int64_t M, int64_t N,
+                             const int64_t* lengths, int64_t T, int32_t out_half, void* stream) {
   using namespace ssb;
   using namespace ssb::gemm2;
   SSB_REQUIRE(A1 && packed && C, "null pointer");
@@ -292,12 +315,13 @@ extern "C" int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const fl
   SSB_REQUIRE(((uintptr_t)A1 & 15) == 0 && ((uintptr_t)A2 & 15) == 0 && ((uintptr_t)packed & 15) == 0, "operands must be 16-byte aligned");
   SSB_REQUIRE(!lengths || T > 0, "row mask needs T");
   SSB_REQUIRE(N % 4 == 0 && ldc % 4 == 0 && ((uintptr_t)C & 15) == 0, "N, ldc multiples of 4 and C 16-byte aligned");
+  SSB_REQUIRE(!out_half || (N % 8 == 0 && ldc % 8 == 0), "fp16 output: N, ldc multiples of 8");
   if (!A2) K2 = 0;
   const int Kp = kp_of((int)K1, (int)K2);
   SSB_REQUIRE(Kp <= MAX_KP && N <= MAX_N && N > 0, "K > 384 or N > 1152 not supported");
   SSB_REQUIRE(M < (int64_t)1 << 31, "M too large");
   if (M == 0) return SSB_OK;
-  Args a{A1, lda1, (int)K1, A2, lda2, (int)K2, reinterpret_cast<const uint8_t*>(packed), bias, C, ldc, (int)M, (int)N, lengths, (int)T};
+  Args a{A1, lda1, (int)K1, A2, lda2, (int)K2, reinterpret_cast<const uint8_t*>(packed), bias, reinterpret_cast<float*>(C), ldc, (int)M, (int)N, out_half ? 1 : 0, lengths, (int)T};
   const int nnt = cdiv(N, BN);
   const size_t smem = smem_bytes(Kp, nnt);
   const int m_tiles = cdiv(M, BM);

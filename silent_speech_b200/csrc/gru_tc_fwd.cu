@@ -17,6 +17,7 @@
 // (ssb_gru_fold_bias); b_hn stays separate because it sits inside r * (W_hn h + b_hn).
 #include "common.cuh"
 #include "tc.cuh"
+#include <cuda_fp16.h>
 
 namespace ssb {
 namespace grutc {
@@ -37,7 +38,7 @@ constexpr int UT = 16;                     // hidden units per gate thread
 constexpr int TMEM_COLS = 256;
 
 struct Ctl {
-  uint64_t full, mma_done, empty, ready, gi_full, gi_rd[4];
+  uint64_t full, mma_done, empty, ready, gi_full[2], gi_rd[4];
   uint32_t tmem_base;
   int maxlen;
 };
@@ -57,6 +58,11 @@ struct Ctl {
 constexpr int GROW = 52;                                     // !kBlk: floats per staged (gate,row): 48 + 4 pad
 constexpr int GROWB = 148;                                   // kBlk: floats per staged row: 144 + 4 pad
 constexpr int GI_STAGE_BYTES = 3 * BM * GROW * 4;            // 79,872 (>= 128 * 148 * 4 = 75,776)
+// kGi == 2: gi stored in fp16 (GRU-blocked): a row is 288 B, padded to 304 B in the staging area; two buffers of 38,912 B
+// fit where one fp32 buffer did, so the copies for step s+2 are issued during step s and a whole step of HBM latency is
+// covered (with one fp32 buffer 14 % of the gate warps' time was spent waiting for the bytes of the next step).
+constexpr int GI16_ROW = NG * 2 + 16, GI16_BUF = BM * GI16_ROW;
+static_assert(2 * GI16_BUF <= GI_STAGE_BYTES, "fp16 staging buffers");
 template <bool kSplit>
 constexpr size_t smem_bytes() { return (kSplit ? 2 : 1) * (A_BYTES + B_BYTES) + (kSplit ? 0 : GI_STAGE_BYTES) + sizeof(Ctl); }
 
@@ -71,13 +77,15 @@ __device__ __forceinline__ float tanh_fast(float x) {
   return copysignf(__fdividef(1.0f - e, 1.0f + e), x);
 }
 
-template <bool kSplit, bool kSave, bool kBlk>
+template <bool kSplit, bool kSave, int kGi>
 __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(THREADS, 1)
 gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
                   const float* __restrict__ whh_f, const float* __restrict__ whh_r,
                   const float* __restrict__ bhn_f, const float* __restrict__ bhn_r,
                   const int64_t* __restrict__ lengths, const int32_t* __restrict__ order, int B, int T,
                   float* __restrict__ out, float* __restrict__ gates) {
+  constexpr bool kBlk = kGi != 0;                           // 0: standard fp32 columns, 1: GRU-blocked fp32, 2: GRU-blocked fp16
+  static_assert(kGi == 0 || !kSplit, "blocked gi staging exists in single-pass mode only");
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* a_hi = smem;
   uint8_t* b_hi = smem + A_BYTES;
@@ -118,7 +126,8 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
     tc::mbar_init(&ctl.full, 1);
     tc::mbar_init(&ctl.mma_done, 1);
     tc::mbar_init(&ctl.ready, EPI_THREADS);
-    tc::mbar_init(&ctl.gi_full, EPI_THREADS);     // every gate thread arrives once per step, with or without bytes
+    tc::mbar_init(&ctl.gi_full[0], EPI_THREADS);     // every gate thread arrives once per step, with or without bytes
+    tc::mbar_init(&ctl.gi_full[1], EPI_THREADS);     // kGi == 2: second staging buffer
     for (int i = 0; i < 4; ++i) tc::mbar_init(&ctl.gi_rd[i], 96);   // kBlk: the three gate warps of a TMEM lane quarter
     tc::mbar_init(&ctl.empty, CL);                 // one multicast tcgen05.commit arrive per CTA of the cluster (incl. this one)
     tc::mbar_fence_init();
@@ -204,6 +213,18 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
 #pragma unroll
           for (int g = 0; g < 3; ++g) asm volatile("prefetch.global.L2 [%0];\n" ::"l"(gp + g * H));
         }
+      } else if (kGi == 2) {
+        // fp16 rows, two staging buffers: step s2 lives in buffer s2 & 1 and is requested during step s2 - 2
+        const int buf = s2 & 1;
+        if (lane % 3 == ug && s2 < len) {
+          const int t2 = dir ? (len - 1 - s2) : s2;
+          const uint16_t* gp = reinterpret_cast<const uint16_t*>(gi) + ((int64_t)b * T + t2) * gi_ld + dir * G3 + (int)rank * NG;
+          if (s2 >= 2) { tc::mbar_wait_bounded(&ctl.gi_rd[warp & 3], (s2 - 2) & 1); tc::fence_async_smem(); }
+          tc::mbar_arrive_expect_tx(&ctl.gi_full[buf], NG * 2);
+          tc::bulk_copy_g2s(tc::smem_u32(reinterpret_cast<uint8_t*>(gstage) + buf * GI16_BUF + m * GI16_ROW), gp, NG * 2, &ctl.gi_full[buf]);
+        } else {
+          tc::mbar_arrive(&ctl.gi_full[buf]);
+        }
       } else if (kBlk) {
         // rows of this lane quarter are dealt out to its three warps: lane l of warp `ug` fetches row m when l % 3 == ug
         if (lane % 3 == ug && s2 < len) {
@@ -212,21 +233,22 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
           // all three readers of the row are done with step s2-1.  Their reads were generic-proxy LDS, the refill is an
           // async-proxy write: without the proxy fence the copy can overtake them (seen as a rare stale-row race).
           if (s2 >= 1) { tc::mbar_wait_bounded(&ctl.gi_rd[warp & 3], (s2 - 1) & 1); tc::fence_async_smem(); }
-          tc::mbar_arrive_expect_tx(&ctl.gi_full, NG * 4);
-          tc::bulk_copy_g2s(tc::smem_u32(gstage + m * GROWB), gp, NG * 4, &ctl.gi_full);
+          tc::mbar_arrive_expect_tx(&ctl.gi_full[0], NG * 4);
+          tc::bulk_copy_g2s(tc::smem_u32(gstage + m * GROWB), gp, NG * 4, &ctl.gi_full[0]);
         } else {
-          tc::mbar_arrive(&ctl.gi_full);
+          tc::mbar_arrive(&ctl.gi_full[0]);
         }
       } else if (s2 < len) {
         const int t2 = dir ? (len - 1 - s2) : s2;
         const float* gp = gi + ((int64_t)b * T + t2) * gi_ld + dir * G3 + ug * H + (int)rank * U;
-        tc::mbar_arrive_expect_tx(&ctl.gi_full, U * 4);
-        tc::bulk_copy_g2s(tc::smem_u32(gstage + (ug * BM + m) * GROW), gp, U * 4, &ctl.gi_full);
+        tc::mbar_arrive_expect_tx(&ctl.gi_full[0], U * 4);
+        tc::bulk_copy_g2s(tc::smem_u32(gstage + (ug * BM + m) * GROW), gp, U * 4, &ctl.gi_full[0]);
       } else {
-        tc::mbar_arrive(&ctl.gi_full);
+        tc::mbar_arrive(&ctl.gi_full[0]);
       }
     };
     prefetch_gi(0);
+    if (kGi == 2 && maxlen > 1) prefetch_gi(1);
     for (int s = 0; s < maxlen; ++s) {
       const bool act = s < len;
       const int t = dir ? (len - 1 - s) : s;
@@ -241,8 +263,34 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
             for (int v = 0; v < 4; ++v) g4[g * 4 + v] = __ldg(reinterpret_cast<const float4*>(gp + g * H) + v);
         }
         prefetch_gi(s + 1);
+      } else if (kGi == 2) {
+        tc::mbar_wait_bounded(&ctl.gi_full[s & 1], (s >> 1) & 1);
+        if (act) {
+          const uint8_t* rowp = reinterpret_cast<const uint8_t*>(gstage) + (s & 1) * GI16_BUF + m * GI16_ROW + ug * (UT * 2);
+          uint4 raw[6];
+#pragma unroll
+          for (int g = 0; g < 3; ++g) {
+            raw[2 * g] = *reinterpret_cast<const uint4*>(rowp + g * (U * 2));
+            raw[2 * g + 1] = *reinterpret_cast<const uint4*>(rowp + g * (U * 2) + 16);
+          }
+#pragma unroll
+          for (int i = 0; i < 6; ++i) {                            // 8 halfs -> two float4
+            const float2 p0 = __half22float2(*reinterpret_cast<const __half2*>(&raw[i].x));
+            const float2 p1 = __half22float2(*reinterpret_cast<const __half2*>(&raw[i].y));
+            const float2 p2 = __half22float2(*reinterpret_cast<const __half2*>(&raw[i].z));
+            const float2 p3 = __half22float2(*reinterpret_cast<const __half2*>(&raw[i].w));
+            g4[2 * i] = make_float4(p0.x, p0.y, p1.x, p1.y);
+            g4[2 * i + 1] = make_float4(p2.x, p2.y, p3.x, p3.y);
+          }
+        }
+        if (act) {                                                 // reads performed (not merely issued) before the hand-back
+#pragma unroll
+          for (int v = 0; v < 12; ++v) asm volatile("" : "+f"(g4[v].x), "+f"(g4[v].y), "+f"(g4[v].z), "+f"(g4[v].w));
+        }
+        tc::mbar_arrive(&ctl.gi_rd[warp & 3]);
+        if (s + 2 < maxlen) prefetch_gi(s + 2);
       } else {
-        tc::mbar_wait_bounded(&ctl.gi_full, s & 1);
+        tc::mbar_wait_bounded(&ctl.gi_full[0], s & 1);
         if (act) {
 #pragma unroll
           for (int g = 0; g < 3; ++g)
@@ -379,19 +427,21 @@ extern "C" int ssb_gru_fold_bias(const float* bih_f, const float* bhh_f, const f
 // order (nullable) = clip index per batch slot, e.g. sorted by length so that tiles are homogeneous.
 // passes = 1 (bf16) or 3 (split-bf16).  Output / gates layouts as ssb_gru_layer_fwd.
 // gi_layout: 0 = columns [dir][gate][192]; 1 = GRU-blocked [dir][rank][gate][48] as written through
-// ssb_proj_prepack(.., gru_blocked = 1) + ssb_gru_fold_bias(.., gru_blocked = 1) (passes = 1, gates = NULL only).
-extern "C" int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_t* lengths, const int32_t* order,
+// ssb_proj_prepack(.., gru_blocked = 1) + ssb_gru_fold_bias(.., gru_blocked = 1) (passes = 1, gates = NULL only);
+// 2 = the same order stored as fp16 (ssb_proj_gemm out_half = 1), double-buffered staging.
+extern "C" int ssb_gru_layer_fwd_tc(const void* gi_, int64_t gi_ld, const int64_t* lengths, const int32_t* order,
                                     int64_t B, int64_t T, int32_t hidden,
                                     const float* whh_f, const float* bhh_f, const float* whh_r, const float* bhh_r,
                                     float* out, float* gates, int32_t passes, int32_t gi_layout, void* stream) {
   using namespace ssb;
   using namespace ssb::grutc;
+  const float* gi = reinterpret_cast<const float*>(gi_);     // gi_layout 2: fp16 elements, gi_ld counts them
   SSB_REQUIRE(gi && lengths && whh_f && bhh_f && whh_r && bhh_r && out, "null pointer");
   SSB_REQUIRE(hidden == H, "hidden must be 192");
-  SSB_REQUIRE(gi_ld >= 2 * G3 && gi_ld % 4 == 0 && ((uintptr_t)gi & 15) == 0, "gi must be 16-byte aligned rows of >= 1152");
+  SSB_REQUIRE(gi_ld >= 2 * G3 && gi_ld % (gi_layout == 2 ? 8 : 4) == 0 && ((uintptr_t)gi & 15) == 0, "gi must be 16-byte aligned rows of >= 1152");
   SSB_REQUIRE(((uintptr_t)whh_f & 15) == 0 && ((uintptr_t)whh_r & 15) == 0 && ((uintptr_t)out & 15) == 0, "alignment");
   SSB_REQUIRE(passes == 1 || passes == 3, "passes must be 1 or 3");
-  SSB_REQUIRE(gi_layout == 0 || (gi_layout == 1 && passes == 1 && !gates), "GRU-blocked gi: single-pass inference only");
+  SSB_REQUIRE(gi_layout == 0 || ((gi_layout == 1 || gi_layout == 2) && passes == 1 && !gates), "GRU-blocked gi: single-pass inference only");
   if (B == 0) return SSB_OK;
   dim3 grid(CL * cdiv(B, BM), 2), block(THREADS);
   cudaStream_t st = (cudaStream_t)stream;
@@ -402,9 +452,10 @@ extern "C" int ssb_gru_layer_fwd_tc(const float* gi, int64_t gi_ld, const int64_
     gru_tc_fwd_kernel<SPLIT, SAVE, BLK><<<grid, block, smem_bytes<SPLIT>(), st>>>(                                   \
         gi, gi_ld, whh_f, whh_r, bhh_f + 2 * H, bhh_r + 2 * H, lengths, order, (int)B, (int)T, out, gates);          \
   } while (0)
-  if (passes == 3)    { if (gates) SSB_LAUNCH_GRUTC(true, true, false); else SSB_LAUNCH_GRUTC(true, false, false); }
-  else if (gi_layout) { SSB_LAUNCH_GRUTC(false, false, true); }
-  else                { if (gates) SSB_LAUNCH_GRUTC(false, true, false); else SSB_LAUNCH_GRUTC(false, false, false); }
+  if (passes == 3)         { if (gates) SSB_LAUNCH_GRUTC(true, true, 0); else SSB_LAUNCH_GRUTC(true, false, 0); }
+  else if (gi_layout == 2) { SSB_LAUNCH_GRUTC(false, false, 2); }
+  else if (gi_layout == 1) { SSB_LAUNCH_GRUTC(false, false, 1); }
+  else                     { if (gates) SSB_LAUNCH_GRUTC(false, true, 0); else SSB_LAUNCH_GRUTC(false, false, 0); }
 #undef SSB_LAUNCH_GRUTC
   SSB_LAUNCH_CHECK();
   return SSB_OK;

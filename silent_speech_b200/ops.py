@@ -256,12 +256,13 @@ def proj_prepack(W_a: torch.Tensor, W_b: Optional[torch.Tensor], K1: int, K2: in
 
 def proj_gemm(A1: torch.Tensor, packed: torch.Tensor, bias, C2d: torch.Tensor, N: int, A2: Optional[torch.Tensor] = None,
               lengths=None, T: int = 0):
+    # C2d may be float32 or float16 (fp16 gi for the single-pass recurrence)
     """C[:, :N] = [A1 | A2] @ packed^T + bias: both directions' input projections in one persistent tcgen05 GEMM."""
     M, K1 = A1.shape
     K2 = 0 if A2 is None else A2.shape[1]
     check(_lib.lib().ssb_proj_gemm(ptr(A1), i64(A1.stride(0)), i64(K1), ptr(A2), i64(0 if A2 is None else A2.stride(0)),
                                    i64(K2), ptr(packed), ptr(bias), ptr(C2d), i64(C2d.stride(0)), i64(M), i64(N),
-                                   ptr(lengths), i64(T), stream_ptr()))
+                                   ptr(lengths), i64(T), i32(1 if C2d.dtype == torch.float16 else 0), stream_ptr()))
     return C2d
 
 
@@ -272,8 +273,12 @@ def gru_fold_bias(bih_f, bhh_f, bih_r, bhh_r, gru_blocked: bool = False) -> torc
 
 
 def gru_layer_fwd_tc(gi, lengths, whh_f, bhh_f, whh_r, bhh_r, passes=3, order=None, out=None, gates=None, gi_blocked=False):
-    """Tensor-core recurrence; gi must include the folded bias (gru_fold_bias)."""
-    _need(gi, torch.float32, "gi")
+    """Tensor-core recurrence; gi must include the folded bias (gru_fold_bias).  A float16 gi (GRU-blocked columns,
+    written by proj_gemm into a half tensor) selects the double-buffered fp16 staging (gi_layout 2)."""
+    half = gi.dtype == torch.float16
+    if half and not gi_blocked:
+        raise _lib.SsbError("fp16 gi exists in the GRU-blocked column order only")
+    _need(gi, torch.float16 if half else torch.float32, "gi")
     _need(lengths, torch.int64, "lengths")
     B, T, ld = gi.shape
     if out is None:
@@ -282,7 +287,7 @@ def gru_layer_fwd_tc(gi, lengths, whh_f, bhh_f, whh_r, bhh_r, passes=3, order=No
         _need(order, torch.int32, "order")
     check(_lib.lib().ssb_gru_layer_fwd_tc(ptr(gi), i64(ld), ptr(lengths), ptr(order), i64(B), i64(T), i32(HIDDEN),
                                           ptr(whh_f), ptr(bhh_f), ptr(whh_r), ptr(bhh_r), ptr(out), ptr(gates),
-                                          i32(passes), i32(1 if gi_blocked else 0), stream_ptr()))
+                                          i32(passes), i32(2 if half else (1 if gi_blocked else 0)), stream_ptr()))
     return out
 
 

@@ -82,6 +82,14 @@ def test_gru_tc_recurrence_vs_fp32_kernel(B, T):
         blk = ops.gru_layer_fwd_tc(gi_b, Ld, *w, passes=1, order=od, gi_blocked=True)
         torch.cuda.synchronize()
         assert torch.equal(std, blk)
+    # fp16 storage of the blocked gi (double-buffered staging): identical to the standard kernel fed the fp16-rounded values
+    gi_r = gi_f.half().float().contiguous()
+    gi_h = gi_r[:, :, perm].half().contiguous()
+    for od in (None, order):
+        std = ops.gru_layer_fwd_tc(gi_r, Ld, *w, passes=1, order=od)
+        blk = ops.gru_layer_fwd_tc(gi_h, Ld, *w, passes=1, order=od, gi_blocked=True)
+        torch.cuda.synchronize()
+        assert torch.equal(std, blk)
 
 
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("tc3", 1e-4), ("fp16", 1e-3)])
@@ -107,6 +115,12 @@ def test_model_logits_by_precision(precision, tol, use_roi, B, T, mode):
     with torch.no_grad():
         logits = m(X.to(dev), L.to(dev), None if R is None else R.to(dev))
     e = rel_err(logits, ref)
+    if precision == "fp16":          # opt-in fp16 storage of gi: same tolerance, same argmax
+        m.gi_half = True
+        with torch.no_grad():
+            lg16 = m(X.to(dev), L.to(dev), None if R is None else R.to(dev))
+        m.gi_half = False
+        assert rel_err(lg16, ref) < tol and torch.equal(lg16.argmax(1).cpu(), ref.argmax(1))
     agree = (logits.argmax(1).cpu() == ref.argmax(1)).float().mean().item()
     print(f"precision={precision} roi={use_roi} rel_err={e:.3e} argmax_agree={agree:.4f}")
     assert e < tol, e
@@ -214,3 +228,10 @@ def test_proj_gemm_vs_fp64(M, n_each, K1, K2, T):
         ops.proj_gemm(A1.to(dev), packed_b, b[perm].to(dev), C2, N, A2=None if A2 is None else A2.to(dev), lengths=L, T=T)
         torch.cuda.synchronize()
         assert torch.equal(C2.cpu()[live], out[live][:, :N][:, perm])
+        # fp16 output: the same fp32 accumulators rounded once to fp16; dead rows untouched
+        C3 = torch.full((M, N + 8), -7.0, device=dev, dtype=torch.float16)
+        ops.proj_gemm(A1.to(dev), packed_b, b[perm].to(dev), C3[:, :N], N, A2=None if A2 is None else A2.to(dev), lengths=L, T=T)
+        torch.cuda.synchronize()
+        h = C3.cpu()
+        assert torch.all(h[:, N:] == -7.0) and torch.all(h[~live][:, :N] == -7.0)
+        assert torch.equal(h[live][:, :N], C2.cpu()[live].half())

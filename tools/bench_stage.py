@@ -13,6 +13,7 @@ ap.add_argument("--batch", type=int, default=4096)
 ap.add_argument("--layer", type=int, default=1)
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--lengths", default="full")
+ap.add_argument("--gi-half", action="store_true", help="proj/gru: fp16 gi (GRU-blocked, double-buffered staging)")
 ap.add_argument("--standard-gi", action="store_true", help="gru: feed the single-pass kernel gi in nn.GRU column order (per-thread bulk copies) instead of the GRU-blocked order")
 a = ap.parse_args()
 dev = torch.device("cuda")
@@ -71,7 +72,7 @@ elif a.stage == "proj":
     sfx = f"_l{a.layer}"
     Wa, Wb = p["gru.weight_ih" + sfx], p["gru.weight_ih" + sfx + "_reverse"]
     bias = torch.randn(2 * G3, device=dev)
-    gi = torch.empty(B * T, 2 * G3, device=dev)
+    gi = torch.empty(B * T, 2 * G3, device=dev, dtype=torch.float16 if a.gi_half else torch.float32)
     if passes == 1:
         packed = ops.proj_prepack(Wa, Wb, K1, K2)
         fn = lambda: ops.proj_gemm(A1, packed, bias, gi, 2 * G3, A2=A2, lengths=L, T=T)
@@ -84,6 +85,8 @@ elif a.stage == "proj":
     print(f"proj layer {a.layer} {a.precision} B={B}: best {best:.3f} ms mean {mean:.3f} ms  {by / best / 1e6:.0f} GB/s algorithmic (A read + C write)")
 elif a.stage == "gru":
     gi = torch.randn(B, T, 2 * G3, device=dev) * 0.5
+    if a.gi_half:
+        gi = gi.half()
     sfx = f"_l{a.layer}"
     w = [p["gru.weight_hh" + sfx], p["gru.bias_hh" + sfx], p["gru.weight_hh" + sfx + "_reverse"], p["gru.bias_hh" + sfx + "_reverse"]]
     order = torch.argsort(L, descending=True).to(torch.int32)
