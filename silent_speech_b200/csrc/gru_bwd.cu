@@ -173,6 +173,159 @@ gru_rec_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ out
   }
 }
 
+// ---- small-batch variant: 8 clips per CTA, the serial product split FOUR ways along K.
+// At B = 128 per GPU (BASELINE configs[2]) the kernel above runs 32 CTAs of 64 threads: 13.8 k dependent FMAs per thread
+// and step, 26 us per step.  Here thread (ks, ug) accumulates chunks ks, ks+4, .. of dgh . W_hh for all 8 clips, the four
+// partial sums meet in shared memory, and the element-wise part is dealt out by clip (thread (ks, ug) owns clips 2ks, 2ks+1
+// of units 3ug..3ug+2, so the carried dh stays in its registers).  Same arithmetic, different summation order.
+constexpr int KS = 4, BTK = 8, THREADS_KS = 64 * KS;
+struct SmemKS {
+  float dgh[BTK][DLD];
+  float part[KS][BTK][H];
+  float w[2][KS][H][WLD];
+  int len[BTK];
+  int maxlen;
+};
+
+__global__ void __launch_bounds__(THREADS_KS, 1)
+gru_rec_bwd_ks_kernel(const float* __restrict__ dout, const float* __restrict__ out, const float* __restrict__ gates,
+                      const float* __restrict__ whhT_f, const float* __restrict__ whhT_r,
+                      const int64_t* __restrict__ lengths, int B, int T,
+                      float* __restrict__ dgi, float* __restrict__ dghn, float* __restrict__ hprev) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  SmemKS& s = *reinterpret_cast<SmemKS*>(smem_raw);
+  const int tid = threadIdx.x, dir = blockIdx.y, b0 = blockIdx.x * BTK;
+  const float* __restrict__ whhT = dir ? whhT_r : whhT_f;
+  const int ug = tid & 63, ks = tid >> 6, j0 = ug * 3, cA = 2 * ks;      // element-wise clips cA, cA + 1
+
+  if (tid < BTK) {
+    const int b = b0 + tid;
+    int l = b < B ? (int)lengths[b] : 0;
+    s.len[tid] = max(0, min(l, T));
+  }
+  if (tid == 0) s.maxlen = 0;
+  __syncthreads();
+  if (tid < BTK) atomicMax(&s.maxlen, s.len[tid]);
+  __syncthreads();
+  const int maxlen = s.maxlen;
+
+  auto stage_round = [&](int buf, int r) {                    // chunks 4r .. 4r+3, one per K slice
+    for (int p = tid; p < KS * H * (KC / 4); p += THREADS_KS) {
+      const int k = p / (H * (KC / 4)), rem = p % (H * (KC / 4)), row = rem >> 2, q = rem & 3;
+      cp_async16b(&s.w[buf][k][row][q * 4], whhT + (int64_t)row * G3 + (r * KS + k) * KC + q * 4);
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+  };
+
+  float dh[3][2];
+#pragma unroll
+  for (int u = 0; u < 3; ++u) dh[u][0] = dh[u][1] = 0.f;
+
+  for (int step = maxlen - 1; step >= 0; --step) {
+    stage_round(0, 0);                                         // weights of the first round travel during the gate math
+    float dhz[3][2];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const int cl = cA + c, b = b0 + cl, len = s.len[cl];
+      const bool act = step < len;
+      const int t = dir ? (len - 1 - step) : step;
+      const int tp = dir ? t + 1 : t - 1;
+      const int64_t bt = (int64_t)b * T + t;
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        float g_r = 0.f, g_z = 0.f, g_n = 0.f;
+        dhz[u][c] = 0.f;
+        if (act) {
+          const int j = j0 + u;
+          const float* gs = gates + (bt * 2 + dir) * (4 * H) + j;
+          const float r = gs[0], z = gs[H], n = gs[2 * H], hn = gs[3 * H];
+          const float hp = step > 0 ? out[((int64_t)b * T + tp) * (2 * H) + dir * H + j] : 0.f;
+          const float d = dh[u][c] + dout[bt * (2 * H) + dir * H + j];
+          const float dn = d * (1.f - z), dz = d * (hp - n);
+          const float dnp = dn * (1.f - n * n), dzp = dz * z * (1.f - z);
+          const float drp = dnp * hn * r * (1.f - r);
+          float* gi_row = dgi + bt * (2 * G3) + dir * G3 + j;
+          gi_row[0] = drp; gi_row[H] = dzp; gi_row[2 * H] = dnp;
+          g_r = drp; g_z = dzp; g_n = dnp * r;
+          dghn[(bt * 2 + dir) * H + j] = g_n;
+          hprev[(bt * 2 + dir) * H + j] = hp;
+          dhz[u][c] = d * z;
+        }
+        s.dgh[cl][j0 + u] = g_r; s.dgh[cl][H + j0 + u] = g_z; s.dgh[cl][2 * H + j0 + u] = g_n;
+      }
+    }
+    __syncthreads();
+
+    float acc[3][BTK];
+#pragma unroll
+    for (int u = 0; u < 3; ++u)
+#pragma unroll
+      for (int c = 0; c < BTK; ++c) acc[u][c] = 0.f;
+    constexpr int ROUNDS = NCHUNK_B / KS;                      // 9
+#pragma unroll 1
+    for (int r = 0; r < ROUNDS; ++r) {
+      if (r + 1 < ROUNDS) {
+        stage_round((r + 1) & 1, r + 1);
+        asm volatile("cp.async.wait_group 1;\n" ::);
+      } else {
+        asm volatile("cp.async.wait_group 0;\n" ::);
+      }
+      __syncthreads();
+      const float (*wb)[WLD] = s.w[r & 1][ks];
+      const int k0 = (r * KS + ks) * KC;
+#pragma unroll
+      for (int kq = 0; kq < KC / 4; ++kq) {
+        float4 dv[BTK];
+#pragma unroll
+        for (int c = 0; c < BTK; ++c) dv[c] = *reinterpret_cast<const float4*>(&s.dgh[c][k0 + kq * 4]);
+#pragma unroll
+        for (int u = 0; u < 3; ++u) {
+          const float4 wv = *reinterpret_cast<const float4*>(&wb[j0 + u][kq * 4]);
+#pragma unroll
+          for (int c = 0; c < BTK; ++c) {
+            float a = acc[u][c];
+            a = fmaf(wv.x, dv[c].x, a); a = fmaf(wv.y, dv[c].y, a);
+            a = fmaf(wv.z, dv[c].z, a); a = fmaf(wv.w, dv[c].w, a);
+            acc[u][c] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+#pragma unroll
+    for (int u = 0; u < 3; ++u)
+#pragma unroll
+      for (int c = 0; c < BTK; ++c) s.part[ks][c][j0 + u] = acc[u][c];
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < 3; ++u)
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        float a = dhz[u][c];
+#pragma unroll
+        for (int k = 0; k < KS; ++k) a += s.part[k][cA + c][j0 + u];
+        dh[u][c] = a;
+      }
+    // s.part is rewritten a whole step (>= 10 barriers) later; s.dgh after the barrier that ended the last round
+  }
+
+  for (int c = 0; c < 2; ++c) {
+    const int cl = cA + c, b = b0 + cl;
+    if (b >= B) continue;
+    for (int t = s.len[cl]; t < T; ++t) {
+      const int64_t bt = (int64_t)b * T + t;
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const int j = j0 + u;
+        float* gi_row = dgi + bt * (2 * G3) + dir * G3 + j;
+        gi_row[0] = 0.f; gi_row[H] = 0.f; gi_row[2 * H] = 0.f;
+        dghn[(bt * 2 + dir) * H + j] = 0.f;
+        hprev[(bt * 2 + dir) * H + j] = 0.f;
+      }
+    }
+  }
+}
+
 __global__ void transpose_kernel(const float* __restrict__ in, float* __restrict__ outp, int rows, int cols) {
   __shared__ float tile[32][33];
   const int x = blockIdx.x * 32 + threadIdx.x, y0 = blockIdx.y * 32;
@@ -221,7 +374,12 @@ extern "C" int ssb_gru_layer_bwd(const float* dout, const float* out, const floa
   } while (0)
   if (cdiv(B, 64) * 2 >= kSMs) SSB_LAUNCH_GRUBWD(64);
   else if (cdiv(B, 16) * 2 >= kSMs) SSB_LAUNCH_GRUBWD(16);
-  else SSB_LAUNCH_GRUBWD(8);
+  else {                                                     // small batch: 8 clips per CTA, K split four ways
+    SSB_CUDA(cudaFuncSetAttribute(gru_rec_bwd_ks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemKS)));
+    dim3 grid(cdiv(B, BTK), 2), block(THREADS_KS);
+    gru_rec_bwd_ks_kernel<<<grid, block, sizeof(SmemKS), (cudaStream_t)stream>>>(
+        dout, out, gates, whhT_f, whhT_r, lengths, (int)B, (int)T, dgi, dghn, hprev);
+  }
 #undef SSB_LAUNCH_GRUBWD
   SSB_LAUNCH_CHECK();
   return SSB_OK;
