@@ -351,6 +351,10 @@ extern "C" int ssb_transpose(const float* in, float* out, int64_t rows, int64_t 
   return SSB_OK;
 }
 
+extern "C" int ssb_gru_layer_bwd_cluster_(const float* dout, const float* out, const float* gates,
+                                          const float* whhT_f, const float* whhT_r, const int64_t* lengths,
+                                          int64_t B, int64_t T, float* dgi, float* dghn, float* hprev, void* stream);
+
 // dout/out [B,T,384], gates [B,T,2,4,192] (from ssb_gru_layer_fwd), whhT_* [192,576] = W_hh^T.
 // Writes dgi [B,T,1152], dghn [B,T,2,192] (n-gate part of dgh) and hprev [B,T,2,192].
 extern "C" int ssb_gru_layer_bwd(const float* dout, const float* out, const float* gates,
@@ -363,6 +367,8 @@ extern "C" int ssb_gru_layer_bwd(const float* dout, const float* out, const floa
   SSB_REQUIRE(hidden == H, "hidden must be 192");
   SSB_REQUIRE(((uintptr_t)whhT_f & 15) == 0 && ((uintptr_t)whhT_r & 15) == 0, "W_hh^T must be 16-byte aligned");
   if (B == 0) return SSB_OK;
+  // small batches (at most two waves of 33 clusters): W_hh resident across a cluster of 4 CTAs, no weight streaming
+  if (cdiv(B, 8) * 2 <= 66) return ssb_gru_layer_bwd_cluster_(dout, out, gates, whhT_f, whhT_r, lengths, B, T, dgi, dghn, hprev, stream);
   // tile size: the largest one whose grid still covers the SMs (smaller tiles = more CTAs sharing the serial FMA work)
 #define SSB_LAUNCH_GRUBWD(BT_)                                                                                         \
   do {                                                                                                                  \

@@ -160,3 +160,70 @@ def test_dropout_statistics_and_train_mode():
     with torch.no_grad():
         le = m(*args)
     assert (lt - le).abs().max().item() > 1e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,T", [(5, 23), (128, 31), (264, 9), (300, 12), (4700, 5)])
+def test_gru_layer_backward_all_tile_sizes(B, T):
+    """ssb_gru_layer_bwd picks a kernel by batch size (cluster-resident W_hh; 16- and 64-clip streaming tiles): each must
+    give torch's packed-GRU gradients w.r.t. gi and, through dgh, w.r.t. W_hh (train_model_official.py:301-305)."""
+    from silent_speech_b200 import ops
+    Hh = 192
+    g = torch.Generator().manual_seed(B * 131 + T)
+    gru = torch.nn.GRU(7, Hh, num_layers=1, batch_first=True, bidirectional=True)
+    x = torch.randn(B, T, 7, generator=g)
+    lengths = torch.randint(1, T + 1, (B,), generator=g)
+    lengths[0] = T
+    dout = torch.randn(B, T, 2 * Hh, generator=g)
+    # torch reference: gi as a leaf so that d/dgi is visible
+    gi_leaf = []
+    outs = []
+    for d, sfx in ((0, ""), (1, "_reverse")):
+        wih, bih = getattr(gru, "weight_ih_l0" + sfx), getattr(gru, "bias_ih_l0" + sfx)
+        gi_d = (x @ wih.T + bih).detach().requires_grad_(True)
+        gi_leaf.append(gi_d)
+        whh, bhh = getattr(gru, "weight_hh_l0" + sfx), getattr(gru, "bias_hh_l0" + sfx)
+        rows = []
+        for b in range(min(B, 6)):          # the serial torch loop on a handful of clips (first tile, incl. a full-length one)
+            L = int(lengths[b]); h = torch.zeros(Hh); o = [None] * T
+            for s in range(L):
+                t = L - 1 - s if d else s
+                gh = whh @ h + bhh
+                a = gi_d[b, t]
+                r = torch.sigmoid(a[:Hh] + gh[:Hh]); z = torch.sigmoid(a[Hh:2 * Hh] + gh[Hh:2 * Hh])
+                n = torch.tanh(a[2 * Hh:] + r * gh[2 * Hh:]); h = (1 - z) * n + z * h; o[t] = h
+            rows.append(torch.stack([v if v is not None else torch.zeros(Hh) for v in o]))
+        outs.append(torch.stack(rows))
+    nb = min(B, 6)
+    ref_out = torch.cat(outs, dim=2)
+    (ref_out * dout[:nb]).sum().backward()
+    # device: forward with saved gates, then the backward under test
+    dev = "cuda"
+    gi = torch.cat([gi_leaf[0].detach(), gi_leaf[1].detach()], dim=2).contiguous().to(dev)
+    w = {k: v.detach().to(dev).contiguous() for k, v in gru.named_parameters()}
+    gates = torch.empty(B, T, 2, 4, Hh, device=dev)
+    out = ops.gru_layer_fwd(gi, lengths.to(dev), w["weight_hh_l0"], w["bias_hh_l0"], w["weight_hh_l0_reverse"],
+                            w["bias_hh_l0_reverse"], gates=gates)
+    dgi, dghn, hprev = ops.gru_layer_bwd(dout.to(dev), out, gates, ops.transpose(w["weight_hh_l0"]),
+                                         ops.transpose(w["weight_hh_l0_reverse"]), lengths.to(dev))
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(out[:nb].cpu().numpy(), ref_out.detach().numpy(), atol=2e-5)
+    for d in (0, 1):
+        got = dgi[:nb, :, d * 576:(d + 1) * 576].cpu().numpy()
+        ref = gi_leaf[d].grad[:nb].numpy()
+        np.testing.assert_allclose(got, ref, atol=2e-4 * max(1.0, np.abs(ref).max()))
+    # rows past each clip's length are zero in all three outputs, for every clip of the batch
+    mask = (torch.arange(T)[None, :] >= lengths[:, None]).to(dev)
+    assert float(dgi[mask].abs().max() if mask.any() else 0) == 0.0
+    assert float(dghn[mask].abs().max() if mask.any() else 0) == 0.0
+    assert float(hprev[mask].abs().max() if mask.any() else 0) == 0.0
+    # the kernels agree with each other over the whole batch: clip b alone (cluster kernel) == clip b inside the batch
+    pick = torch.tensor([B - 1, B // 2])
+    for b in pick.tolist():
+        sl = slice(b, b + 1)
+        d1, g1, h1 = ops.gru_layer_bwd(dout[sl].to(dev).contiguous(), out[sl].contiguous(), gates[sl].contiguous(),
+                                       ops.transpose(w["weight_hh_l0"]), ops.transpose(w["weight_hh_l0_reverse"]),
+                                       lengths[sl].to(dev))
+        np.testing.assert_allclose(d1.cpu().numpy(), dgi[sl].cpu().numpy(), atol=1e-5 * max(1.0, float(dgi[sl].abs().max())))
+        np.testing.assert_allclose(g1.cpu().numpy(), dghn[sl].cpu().numpy(), atol=1e-5 * max(1.0, float(dghn[sl].abs().max())))
+        assert torch.equal(h1, hprev[sl])
