@@ -22,6 +22,7 @@ constexpr int A3_COL0 = 2;     // interior of the saved conv3 plane starts at co
 
 struct BwdSmem {
   SmemWeights w;
+  float w2t[C2][9][C1];            // [co][tap][ci]: conv2 weights for the data gradient (B4)
   float in[IN_ROWS * IN_LD];
   float a1[C1 * A1_PLANE];
   float a2[C2 * A2_PLANE];
@@ -60,6 +61,11 @@ roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   for (int i = tid; i < C2 * A2_PLANE; i += kThreads) s.a2[i] = 0.f;
   for (int i = tid; i < C3 * A3_PLANE; i += kThreads) s.g3[i] = 0.f;
   __syncthreads();
+  for (int i = tid; i < C2 * 9 * C1; i += kThreads) {
+    const int co = i / (9 * C1), tap = (i / C1) % 9, ci = i % C1;
+    s.w2t[co][tap][ci] = s.w.w2[ci][tap][co];
+  }
+  __syncthreads();
 
   // ---- per-thread slices of the weight gradients
   const int b1_third = tid / 96, b1_cog = (tid % 96) / 16, b1_ci = tid % 16;          // dW3
@@ -72,9 +78,11 @@ roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   float acc2[9], accb2 = 0.f;
 #pragma unroll
   for (int t = 0; t < 9; ++t) acc2[t] = 0.f;
-  const int b5_q = tid / 72, b5_co = (tid % 72) / 9, b5_tap = tid % 9;                // dW1
-  float acc1 = 0.f, accb1 = 0.f, accb3 = 0.f, accfc[3] = {0.f, 0.f, 0.f};
+  const int b5_co = tid / 36, b5_grp = tid % 36;                                      // dW1: 32 pooled cells of one channel
+  float acc1[9], accb1 = 0.f, accb3 = 0.f, accfc[3] = {0.f, 0.f, 0.f};
 
+#pragma unroll
+  for (int t = 0; t < 9; ++t) acc1[t] = 0.f;
   const int64_t frames = (int64_t)B * T;
   for (int64_t f = blockIdx.x; f < frames; f += gridDim.x) {
     const int b = (int)(f / T), t = (int)(f % T);
@@ -210,54 +218,102 @@ roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       }
     }
 
-    // ================= B4: da1 = conv2^T(dc2) gathered through the argmax, masked by relu'(a1)
+    // ================= B4: da1 = conv2^T(dc2), masked by relu'(a1)
+    // dc2 (the gradient at conv2's 24x48 outputs: da2m at each pooled cell's argmax, zero elsewhere) is written out
+    // DENSE, 8 channels at a time, as zero-bordered planes in a1's layout over the dead a2/g3 region; the data gradient
+    // is then a plain 3x3 convolution with flipped taps -- one thread = one 2x2 block of positions x all 8 input
+    // channels, vector loads, no per-tap index tests.
+    {
+      const int py = tid / W2, px = tid % W2;
+      float* const dp = s.a2;                                   // [8][A1_PLANE], spills into g3
+      float acc[C1][4];
+#pragma unroll
+      for (int c = 0; c < C1; ++c) acc[c][0] = acc[c][1] = acc[c][2] = acc[c][3] = 0.f;
 #pragma unroll 1
-    for (int k = 0; k < 4; ++k) {
-      const int pos = tid + k * kThreads;
-      const int y = pos / W1, x = pos % W1;
-      float acc[C1];
-#pragma unroll
-      for (int c = 0; c < C1; ++c) acc[c] = 0.f;
-#pragma unroll 1
-      for (int tap = 0; tap < 9; ++tap) {
-        const int dy = tap / 3, dx = tap % 3;
-        const int yy = y + 1 - dy, xx = x + 1 - dx;            // conv2 output position feeding (y,x) through this tap
-        if (yy < 0 || yy >= H1 || xx < 0 || xx >= W1) continue;
-        const int cell = (yy >> 1) * W2 + (xx >> 1), sub = ((yy & 1) << 1) | (xx & 1);
-        float dv[C2];
-#pragma unroll
-        for (int co = 0; co < C2; ++co)
-          dv[co] = s.idx2[co * (H2 * W2) + cell] == sub ? s.da2m[co * (H2 * W2) + cell] : 0.f;
-#pragma unroll
-        for (int c = 0; c < C1; ++c) {
-          const float4* wp = reinterpret_cast<const float4*>(&s.w.w2[c][tap][0]);
-          float a = acc[c];
-#pragma unroll
-          for (int v = 0; v < C2 / 4; ++v) {
-            const float4 wv = wp[v];
-            a = fmaf(wv.x, dv[4 * v], a); a = fmaf(wv.y, dv[4 * v + 1], a);
-            a = fmaf(wv.z, dv[4 * v + 2], a); a = fmaf(wv.w, dv[4 * v + 3], a);
+      for (int h = 0; h < 2; ++h) {
+        __syncthreads();                                        // B2/B3 (h = 0) or the previous half's reads are done
+        if (h == 0) {
+          constexpr int BORDER = A1_PLANE - H1 * W1;            // 204 floats per plane
+          for (int i = tid; i < 8 * BORDER; i += kThreads) {
+            const int pl = i / BORDER, r = i % BORDER;
+            int off;
+            if (r < A1_LD) off = r;
+            else if (r < 2 * A1_LD) off = (A1_ROWS - 1) * A1_LD + (r - A1_LD);
+            else if (r < 2 * A1_LD + 4 * H1) { const int k = r - 2 * A1_LD, e = k & 3; off = (1 + (k >> 2)) * A1_LD + (e == 0 ? 0 : W1 + e); }
+            else off = A1_ROWS * A1_LD + (r - 2 * A1_LD - 4 * H1);
+            dp[pl * A1_PLANE + off] = 0.f;
           }
-          acc[c] = a;
+        }
+#pragma unroll
+        for (int co = 0; co < 8; ++co) {
+          const int c = h * 8 + co;
+          const float d = s.da2m[c * (H2 * W2) + tid];
+          const int id = s.idx2[c * (H2 * W2) + tid];
+          float* q = dp + co * A1_PLANE + (2 * py + 1) * A1_LD + 2 * px + 1;
+          q[0] = id == 0 ? d : 0.f; q[1] = id == 1 ? d : 0.f;
+          q[A1_LD] = id == 2 ? d : 0.f; q[A1_LD + 1] = id == 3 ? d : 0.f;
+        }
+        __syncthreads();
+#pragma unroll 1
+        for (int co = 0; co < 8; ++co) {
+          float P[4][4];
+          const float* base = dp + co * A1_PLANE + (2 * py) * A1_LD + 2 * px;
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const float2 a = *reinterpret_cast<const float2*>(base + r * A1_LD);
+            const float2 b = *reinterpret_cast<const float2*>(base + r * A1_LD + 2);
+            P[r][0] = a.x; P[r][1] = a.y; P[r][2] = b.x; P[r][3] = b.y;
+          }
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            const int dy = tap / 3, dx = tap % 3;
+            float wv[C1];
+            *reinterpret_cast<float4*>(wv) = *reinterpret_cast<const float4*>(&s.w2t[h * 8 + co][tap][0]);
+            *reinterpret_cast<float4*>(wv + 4) = *reinterpret_cast<const float4*>(&s.w2t[h * 8 + co][tap][4]);
+#pragma unroll
+            for (int c = 0; c < C1; ++c) {                      // position (a,b) of the block takes dc2 at (a+2-dy, b+2-dx)
+              acc[c][0] = fmaf(wv[c], P[2 - dy][2 - dx], acc[c][0]);
+              acc[c][1] = fmaf(wv[c], P[2 - dy][3 - dx], acc[c][1]);
+              acc[c][2] = fmaf(wv[c], P[3 - dy][2 - dx], acc[c][2]);
+              acc[c][3] = fmaf(wv[c], P[3 - dy][3 - dx], acc[c][3]);
+            }
+          }
         }
       }
 #pragma unroll
       for (int c = 0; c < C1; ++c)
-        s.da1m[c * (H1 * W1) + pos] = s.a1[c * A1_PLANE + (y + 1) * A1_LD + x + 1] > 0.f ? acc[c] : 0.f;
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+          const float* m = s.a1 + c * A1_PLANE + (2 * py + a + 1) * A1_LD + 2 * px + 1;
+          float2 v;
+          v.x = m[0] > 0.f ? acc[c][2 * a] : 0.f;
+          v.y = m[1] > 0.f ? acc[c][2 * a + 1] : 0.f;
+          *reinterpret_cast<float2*>(&s.da1m[c * (H1 * W1) + (2 * py + a) * W1 + 2 * px]) = v;
+        }
     }
     __syncthreads();
+    // the dense planes lay over a2 and the head of g3: give both their zero borders back (interiors are rewritten
+    // by the next frame's forward pass)
+    {
+      float4* z = reinterpret_cast<float4*>(s.a2);
+      for (int i = tid; i < 8 * A1_PLANE / 4; i += kThreads) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 
-    // ================= B5: dW1, db1
+    // ================= B5: dW1, db1 -- one thread = 32 pooled cells of one channel x all 9 taps
     {
       const float* dptr = s.da1m + b5_co * (H1 * W1);
       const uint8_t* iptr = s.idx1 + b5_co * (H1 * W1);
-      const int dy = b5_tap / 3, dx = b5_tap % 3;
-#pragma unroll 4
-      for (int cell = b5_q * 288; cell < b5_q * 288 + 288; ++cell) {
+#pragma unroll 2
+      for (int k = 0; k < (H1 * W1) / 36; ++k) {
+        const int cell = b5_grp + 36 * k;
         const float d = dptr[cell];
         const int id = iptr[cell];
         const int py = cell / W1, px = cell % W1;
-        acc1 = fmaf(d, s.in[(2 * py + (id >> 1) + dy) * IN_LD + 2 * px + (id & 1) + dx], acc1);
+        const float* p = s.in + (2 * py + (id >> 1)) * IN_LD + 2 * px + (id & 1);
+#pragma unroll
+        for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+          for (int dx = 0; dx < 3; ++dx) acc1[dy * 3 + dx] = fmaf(d, p[dy * IN_LD + dx], acc1[dy * 3 + dx]);
         accb1 += d;
       }
     }
@@ -274,8 +330,19 @@ roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     for (int t = 0; t < 9; ++t) atomicAdd(gW2 + (b3_co * C1 + b3_ci) * 9 + t, acc2[t]);
     if (b3_ci == 0) atomicAdd(gb2 + b3_co, accb2);
   }
-  atomicAdd(gW1 + b5_co * 9 + b5_tap, acc1);
-  if (b5_tap == 0) atomicAdd(gb1 + b5_co, accb1);
+  {                                                             // dW1/db1: 36 partial sums per channel meet in shared memory
+    float* red = s.da1m;                                        // [288][10]; the frame loop ended with a barrier
+#pragma unroll
+    for (int t = 0; t < 9; ++t) red[tid * 10 + t] = acc1[t];
+    red[tid * 10 + 9] = accb1;
+    __syncthreads();
+    if (tid < C1 * 10) {
+      const int co = tid / 10, t = tid % 10;
+      float a = 0.f;
+      for (int g = 0; g < 36; ++g) a += red[(co * 36 + g) * 10 + t];
+      if (t < 9) atomicAdd(gW1 + co * 9 + t, a); else atomicAdd(gb1 + co, a);
+    }
+  }
   if (tid < C3) atomicAdd(gb3 + tid, accb3);
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
