@@ -7,7 +7,7 @@
 //   B0  Linear(24->32) and the mean:      dWfc, dbfc, g3 = relu'(a3) * dmean/288, db3
 //   B1  conv3 weight gradient             dW3[co,ci,tap] += sum_pos g3[co,pos] a2[ci,pos+tap]
 //   B2  conv3 data gradient (gather)      da2, masked by relu'(a2)
-//   B3  conv2 weight gradient through the pool argmax     dW2, db2
+//   B3  conv2 weight gradient through the pool argmax     dW2, db2   (one 4x4 patch load serves all 16 channels)
 //   B4  conv2 data gradient (gather through the argmax)   da1, masked by relu'(a1)
 //   B5  conv1 weight gradient through the pool argmax     dW1, db1
 // The ROI pixels are inputs, not parameters, so nothing flows past conv1.  Every thread keeps
@@ -23,6 +23,7 @@ constexpr int A3_COL0 = 2;     // interior of the saved conv3 plane starts at co
 struct BwdSmem {
   SmemWeights w;
   float w2t[C2][9][C1];            // [co][tap][ci]: conv2 weights for the data gradient (B4)
+  float dW2s[C2 * C1 * 9 + C2];    // conv2 weight and bias gradient of this CTA, summed over its frames
   float in[IN_ROWS * IN_LD];
   float a1[C1 * A1_PLANE];
   float a2[C2 * A2_PLANE];
@@ -65,6 +66,7 @@ roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     const int co = i / (9 * C1), tap = (i / C1) % 9, ci = i % C1;
     s.w2t[co][tap][ci] = s.w.w2[ci][tap][co];
   }
+  for (int i = tid; i < C2 * C1 * 9 + C2; i += kThreads) s.dW2s[i] = 0.f;
   __syncthreads();
 
   // ---- per-thread slices of the weight gradients
@@ -74,10 +76,7 @@ roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   for (int k = 0; k < 4; ++k)
 #pragma unroll
     for (int t = 0; t < 9; ++t) acc3[k][t] = 0.f;
-  const int b3_half = tid >> 7, b3_co = (tid & 127) >> 3, b3_ci = tid & 7;            // dW2 (tid < 256)
-  float acc2[9], accb2 = 0.f;
-#pragma unroll
-  for (int t = 0; t < 9; ++t) acc2[t] = 0.f;
+  const int b3_ci = lane & 7, b3_cog = lane >> 3, b3_w = tid >> 5;   // dW2: 4 output channels x 1 input channel; warp = 32 cells
   const int b5_co = tid / 36, b5_grp = tid % 36;                                      // dW1: 32 pooled cells of one channel
   float acc1[9], accb1 = 0.f, accb3 = 0.f, accfc[3] = {0.f, 0.f, 0.f};
 
@@ -200,21 +199,62 @@ roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     __syncthreads();
 
     // ================= B3: dW2, db2 (gradient sits at the pooled cell's argmax position)
-    if (tid < 256) {
-      const float* dptr = s.da2m + b3_co * (H2 * W2);
-      const uint8_t* iptr = s.idx2 + b3_co * (H2 * W2);
+    // The 4x4 patch of a1 under a pooled cell holds the 3x3 window of every one of its four argmax positions, and it is
+    // the same for all 16 output channels: a lane loads it once for its input channel and picks the window of each of
+    // its four output channels with selects on the argmax bits.
+    {
+      float acc2[4][9], accb2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int t = 0; t < 9; ++t) acc2[k][t] = 0.f;
       const float* abase = s.a1 + b3_ci * A1_PLANE;
-#pragma unroll 2
-      for (int cell = b3_half * 144; cell < b3_half * 144 + 144; ++cell) {
-        const float d = dptr[cell];
-        const int id = iptr[cell];
+#pragma unroll 1
+      for (int i = 0; i < 32; ++i) {
+        const int cell = b3_w * 32 + i;
         const int py = cell / W2, px = cell % W2;
-        const float* p = abase + (2 * py + (id >> 1)) * A1_LD + 2 * px + (id & 1);
+        float P[4][4];
 #pragma unroll
-        for (int dy = 0; dy < 3; ++dy)
+        for (int r = 0; r < 4; ++r) {
+          const float2 a = *reinterpret_cast<const float2*>(abase + (2 * py + r) * A1_LD + 2 * px);
+          const float2 b = *reinterpret_cast<const float2*>(abase + (2 * py + r) * A1_LD + 2 * px + 2);
+          P[r][0] = a.x; P[r][1] = a.y; P[r][2] = b.x; P[r][3] = b.y;
+        }
 #pragma unroll
-          for (int dx = 0; dx < 3; ++dx) acc2[dy * 3 + dx] = fmaf(d, p[dy * A1_LD + dx], acc2[dy * 3 + dx]);
-        accb2 += d;
+        for (int k = 0; k < 4; ++k) {
+          const int co = b3_cog * 4 + k;
+          const float d = s.da2m[co * (H2 * W2) + cell];
+          const int id = s.idx2[co * (H2 * W2) + cell];
+          const bool dn = (id & 2) != 0, rt = (id & 1) != 0;
+#pragma unroll
+          for (int dy = 0; dy < 3; ++dy) {
+            float R[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) R[c] = dn ? P[dy + 1][c] : P[dy][c];
+#pragma unroll
+            for (int dx = 0; dx < 3; ++dx) acc2[k][dy * 3 + dx] = fmaf(d, rt ? R[dx + 1] : R[dx], acc2[k][dy * 3 + dx]);
+          }
+          accb2[k] += d;
+        }
+      }
+      // the 9 warps' partial sums meet in the (now dead) a2/g3 region: slot [warp][cog*296 + k*72 + ci*9 + tap]
+      // (296: the four channel groups of a warp land in different banks), biases behind the slots
+      constexpr int SLOT = 4 * 296, NW2 = C2 * C1 * 9;
+      float* red = s.a2;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+#pragma unroll
+        for (int t = 0; t < 9; ++t) red[b3_w * SLOT + b3_cog * 296 + k * 72 + b3_ci * 9 + t] = acc2[k][t];
+        if (b3_ci == 0) red[(kThreads / 32) * SLOT + b3_w * C2 + b3_cog * 4 + k] = accb2[k];
+      }
+      __syncthreads();
+      for (int i = tid; i < NW2 + C2; i += kThreads) {
+        const int at = i < NW2 ? (i / 288) * 296 + i % 288 : (kThreads / 32) * SLOT + (i - NW2);
+        const int stride = i < NW2 ? SLOT : C2;
+        float a = 0.f;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) a += red[at + w * stride];
+        s.dW2s[i] += a;
       }
     }
 
@@ -325,10 +365,8 @@ roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   for (int k = 0; k < 4; ++k)
 #pragma unroll
     for (int t = 0; t < 9; ++t) atomicAdd(gW3 + ((b1_cog * 4 + k) * C2 + b1_ci) * 9 + t, acc3[k][t]);
-  if (tid < 256) {
-#pragma unroll
-    for (int t = 0; t < 9; ++t) atomicAdd(gW2 + (b3_co * C1 + b3_ci) * 9 + t, acc2[t]);
-    if (b3_ci == 0) atomicAdd(gb2 + b3_co, accb2);
+  for (int i = tid; i < C2 * C1 * 9 + C2; i += kThreads) {
+    if (i < C2 * C1 * 9) atomicAdd(gW2 + i, s.dW2s[i]); else atomicAdd(gb2 + (i - C2 * C1 * 9), s.dW2s[i]);
   }
   {                                                             // dW1/db1: 36 partial sums per channel meet in shared memory
     float* red = s.da1m;                                        // [288][10]; the frame loop ended with a barrier
