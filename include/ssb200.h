@@ -130,6 +130,21 @@ int ssb_gemm_tc(const float* A1, int64_t lda1, int64_t K1, const float* A2, int6
                 int64_t M, int64_t N, int32_t passes, int32_t accumulate,
                 const int64_t* lengths, int64_t T, void* stream);
 
+/* Backward GEMMs of nn.GRU on the tensor cores (autograd of train_model_official.py:261-267 under
+ * loss.backward(), train:437): C[i,j] (+)= sum_k A[i*sai+k*sak] * B[k*sbk+j*sbj], the same strided contract as
+ * ssb_sgemm (no bias).  Operands contiguous along their OUTPUT index (the weight gradient dW = dgi^T Z contracts
+ * over frames) are transposed on the way into shared memory; split-fp16 x3, fp32 accumulation in TMEM.  a_amax
+ * (nullable, device) = max|A| from ssb_absmax: A is scaled by a power of two into fp16's range (gate gradients are
+ * far below it) and C un-scaled, without a host synchronisation.
+ * A k-contiguous operand needs its other stride and K multiples of 4 floats and a 16-byte aligned base.
+ * split_k > 1 requires accumulate = 1 (fp32 atomics).  lengths/T (optional): skip 128-row tiles of padded frames. */
+int ssb_gemm_tcx(const float* A, int64_t sai, int64_t sak, const float* B, int64_t sbk, int64_t sbj,
+                 float* C, int64_t ldc, int64_t M, int64_t N, int64_t K,
+                 int32_t accumulate, int32_t split_k, const int64_t* lengths, int64_t T,
+                 const float* a_amax, void* stream);
+/* out[0] = max |x[i]| over n floats (device scalar; feeds ssb_gemm_tcx's a_amax). */
+int ssb_absmax(const float* x, int64_t n, float* out, void* stream);
+
 /* K3b on the tensor cores (cluster of 4 CTAs, W_hh resident in shared memory as bf16, tcgen05.mma per
  * step, h slices exchanged by bulk DSMEM copies).  Same semantics/layouts as ssb_gru_layer_fwd, except that
  * gi must already include b_ih + (b_hr, b_hz, 0) -- build that bias with ssb_gru_fold_bias and pass it to the

@@ -14,15 +14,25 @@ from typing import Dict, Optional
 import torch
 
 from . import ops
-from .functional import G3, H, forward_impl
+from .functional import G3, H, _passes, forward_impl
 
 
 def _split_k(K: int) -> int:
     return max(1, min(64, K // 512))
 
 
-def _wgrad(dY2d, y_col0, y_cols, ldy, X2d, x_col0, x_cols, ldx, gW, gw_off, ldw, rows):
+def _split_k_tc(rows_out: int, cols_out: int, K: int) -> int:
+    """K splits of a tensor-core weight-gradient GEMM: about two 128x192-tile CTAs per SM in flight, >= 4 chunks each."""
+    tiles = -(-rows_out // 128) * -(-cols_out // 192)
+    return max(1, min(K // 128, (2 * 148 + tiles - 1) // tiles))
+
+
+def _wgrad(dY2d, y_col0, y_cols, ldy, X2d, x_col0, x_cols, ldx, gW, gw_off, ldw, rows, amax=None):
     """gW[row, :] += sum_m dY[m, y_col0+row] * X[m, x_col0 + :]   (rows = y_cols)."""
+    if amax is not None:          # tensor-core modes; amax = max|dY| (device scalar) scales dY into fp16's range
+        ops.gemm_tcx(dY2d, X2d, gW, y_cols, x_cols, rows, sa=(1, ldy), sb=(ldx, 1), ldc=ldw, accumulate=True,
+                     split_k=_split_k_tc(y_cols, x_cols, rows), a_off=y_col0, b_off=x_col0, c_off=gw_off, a_amax=amax)
+        return
     ops.sgemm(dY2d, X2d, gW, y_cols, x_cols, rows, sa=(1, ldy), sb=(ldx, 1), ldc=ldw, accumulate=True,
               split_k=_split_k(rows), a_off=y_col0, b_off=x_col0, c_off=gw_off)
 
@@ -30,21 +40,23 @@ def _wgrad(dY2d, y_col0, y_cols, ldy, X2d, x_col0, x_cols, ldx, gW, gw_off, ldw,
 def _gru_layer_backward(layer: int, dseq, seq_out, gates, lengths, B, T, inputs, model, grads, want_dinput):
     """inputs: list of (tensor2d [B*T, width], column offset inside weight_ih) feeding this layer."""
     p = model.gru.layer(layer)
+    tc = _passes(model)[1] != 0          # tensor-core modes: GEMM-shaped gradients on tcgen05 (split-bf16 x3)
     whhT = [ops.transpose(p["weight_hh"][d]) for d in (0, 1)]
     dgi, dghn, hprev = ops.gru_layer_bwd(dseq, seq_out, gates, whhT[0], whhT[1], lengths)
     M = B * T
     dgi2d, dghn2d, hprev2d = dgi.view(M, 2 * G3), dghn.view(M, 2 * H), hprev.view(M, 2 * H)
+    amax = ops.absmax(dgi) if tc else None          # |dghn| = |dgi_n * r| <= |dgi_n|: one scale serves both tensors
     dinput = None
     for d, sfx in ((0, ""), (1, "_reverse")):
         g_wih, g_whh = grads[f"gru.weight_ih_l{layer}{sfx}"], grads[f"gru.weight_hh_l{layer}{sfx}"]
         g_bih, g_bhh = grads[f"gru.bias_ih_l{layer}{sfx}"], grads[f"gru.bias_hh_l{layer}{sfx}"]
         width = g_wih.shape[1]
         for x2d, col0 in inputs:
-            _wgrad(dgi2d, d * G3, G3, 2 * G3, x2d, 0, x2d.shape[1], x2d.stride(0), g_wih, col0, width, M)
+            _wgrad(dgi2d, d * G3, G3, 2 * G3, x2d, 0, x2d.shape[1], x2d.stride(0), g_wih, col0, width, M, amax)
         ops.colsum(dgi2d[:, d * G3:(d + 1) * G3], g_bih)
         # hidden projection: r,z rows share dgi; the n rows use dghn = dgi_n * r
-        _wgrad(dgi2d, d * G3, 2 * H, 2 * G3, hprev2d, d * H, H, 2 * H, g_whh, 0, H, M)
-        _wgrad(dghn2d, d * H, H, 2 * H, hprev2d, d * H, H, 2 * H, g_whh, 2 * H * H, H, M)
+        _wgrad(dgi2d, d * G3, 2 * H, 2 * G3, hprev2d, d * H, H, 2 * H, g_whh, 0, H, M, amax)
+        _wgrad(dghn2d, d * H, H, 2 * H, hprev2d, d * H, H, 2 * H, g_whh, 2 * H * H, H, M, amax)
         ops.colsum(dgi2d[:, d * G3:d * G3 + 2 * H], g_bhh[:2 * H])
         ops.colsum(dghn2d[:, d * H:(d + 1) * H], g_bhh[2 * H:])
     if want_dinput is not None:
@@ -52,8 +64,12 @@ def _gru_layer_backward(layer: int, dseq, seq_out, gates, lengths, B, T, inputs,
         dinput = torch.empty(M, ncols, device=dgi.device, dtype=torch.float32)
         for d in (0, 1):
             W = p["weight_ih"][d]
-            ops.sgemm(dgi2d, W, dinput, M, ncols, G3, sa=(2 * G3, 1), sb=(W.shape[1], 1), ldc=ncols,
-                      accumulate=(d == 1), lengths=lengths, T=T, a_off=d * G3, b_off=col0)
+            kw = dict(sa=(2 * G3, 1), sb=(W.shape[1], 1), ldc=ncols, accumulate=(d == 1), lengths=lengths, T=T,
+                      a_off=d * G3, b_off=col0)
+            if tc:
+                ops.gemm_tcx(dgi2d, W, dinput, M, ncols, G3, a_amax=amax, **kw)
+            else:
+                ops.sgemm(dgi2d, W, dinput, M, ncols, G3, **kw)
     return dinput
 
 

@@ -105,6 +105,28 @@ def sgemm(A: torch.Tensor, Bm: torch.Tensor, C: torch.Tensor, M: int, N: int, K:
     return C
 
 
+def gemm_tcx(A: torch.Tensor, Bm: torch.Tensor, C: torch.Tensor, M: int, N: int, K: int,
+             sa=(None, None), sb=(None, None), ldc: Optional[int] = None,
+             accumulate: bool = False, split_k: int = 1, lengths: Optional[torch.Tensor] = None, T: int = 0,
+             a_off: int = 0, b_off: int = 0, c_off: int = 0, a_amax: Optional[torch.Tensor] = None):
+    """sgemm's contract on the tensor cores (split-fp16 x3): the backward GEMMs of the GRU.  a_amax = absmax(A)."""
+    import ctypes
+    check(_lib.lib().ssb_gemm_tcx(ctypes.c_void_p(A.data_ptr() + 4 * a_off), i64(sa[0]), i64(sa[1]),
+                                  ctypes.c_void_p(Bm.data_ptr() + 4 * b_off), i64(sb[0]), i64(sb[1]),
+                                  ctypes.c_void_p(C.data_ptr() + 4 * c_off), i64(ldc), i64(M), i64(N), i64(K),
+                                  i32(1 if accumulate else 0), i32(split_k), ptr(lengths), i64(T), ptr(a_amax),
+                                  stream_ptr()))
+    return C
+
+
+def absmax(x: torch.Tensor) -> torch.Tensor:
+    """Device scalar max|x| (no host sync); the scale source of gemm_tcx."""
+    _need(x, torch.float32, "x")
+    out = torch.empty(1, device=x.device, dtype=torch.float32)
+    check(_lib.lib().ssb_absmax(ptr(x), i64(x.numel()), ptr(out), stream_ptr()))
+    return out
+
+
 def linear_nt(A2d: torch.Tensor, W: torch.Tensor, bias, C2d: torch.Tensor, accumulate=False,
               lengths=None, T=0, w_col0: int = 0, k: Optional[int] = None, c_col0: int = 0):
     """C[:, c_col0:c_col0+N] (+)= A @ W[:, w_col0:w_col0+k]^T (+ bias).  A [M,k] rows contiguous."""

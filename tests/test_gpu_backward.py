@@ -227,3 +227,56 @@ def test_gru_layer_backward_all_tile_sizes(B, T):
         np.testing.assert_allclose(d1.cpu().numpy(), dgi[sl].cpu().numpy(), atol=1e-5 * max(1.0, float(dgi[sl].abs().max())))
         np.testing.assert_allclose(g1.cpu().numpy(), dghn[sl].cpu().numpy(), atol=1e-5 * max(1.0, float(dghn[sl].abs().max())))
         assert torch.equal(h1, hprev[sl])
+
+
+# --------------------------------------------------------------------------------------------- tensor-core backward GEMMs
+@pytest.mark.parametrize("M,N,K,split", [(576, 384, 11520, 30), (576, 180, 1000, 3), (576, 32, 777, 1), (192, 192, 4100, 7),
+                                         (384, 192, 90, 1), (130, 200, 33, 1)])
+def test_gemm_tcx_weight_gradient_shape(M, N, K, split):
+    """dW[i,j] += sum_m dY[m, c0+i] X[m, x0+j]: both operands contiguous along their output index, tiny dY values
+    (scaled into fp16's range by max|dY|), split-K atomics on top of an existing C."""
+    from silent_speech_b200 import ops
+    dev = _cuda()
+    g = torch.Generator().manual_seed(M * 7 + N)
+    dY = (torch.randn(K, M + 40, generator=g) * 1e-7).to(dev)
+    X = torch.randn(K, N + 8, generator=g).to(dev)
+    C0 = (torch.randn(M, N + 4, generator=g) * 1e-6).to(dev)
+    C = C0.clone()
+    ops.gemm_tcx(dY, X, C, M, N, K, sa=(1, M + 40), sb=(N + 8, 1), ldc=N + 4, accumulate=True, split_k=split,
+                 a_off=40, b_off=8, a_amax=ops.absmax(dY))
+    assert float(ops.absmax(dY)) == float(dY.abs().max())
+    ref = C0.double()
+    ref[:, :N] += dY[:, 40:].double().t() @ X[:, 8:].double()
+    assert rel_err(C[:, :N], ref[:, :N]) < 1e-5
+    assert torch.equal(C[:, N:], C0[:, N:])            # columns past N untouched
+
+
+@pytest.mark.parametrize("accumulate", [False, True])
+def test_gemm_tcx_data_gradient_shape(accumulate):
+    """dZ[m,j] (+)= sum_i dgi[m, c0+i] W[i, x0+j]: A contraction-contiguous, B output-contiguous, padded-frame tiles skipped."""
+    from silent_speech_b200 import ops
+    dev = _cuda()
+    B, T, G3, ncols, ldw = 5, 64, 576, 384, 400
+    g = torch.Generator().manual_seed(3)
+    dgi = (torch.randn(B * T, 2 * G3, generator=g) * 1e-5).to(dev)
+    W = (torch.randn(G3, ldw, generator=g) * 0.1).to(dev)
+    L = torch.tensor([64, 10, 64, 1, 33], dtype=torch.int64, device=dev)
+    C0 = torch.randn(B * T, ncols, generator=g).to(dev) * 1e-4
+    C = C0.clone()
+    ops.gemm_tcx(dgi, W, C, B * T, ncols, G3, sa=(2 * G3, 1), sb=(ldw, 1), ldc=ncols, accumulate=accumulate,
+                 lengths=L, T=T, a_off=G3, b_off=16, a_amax=ops.absmax(dgi))
+    ref = dgi[:, G3:].double() @ W[:, 16:16 + ncols].double() + (C0.double() if accumulate else 0)
+    valid = (torch.arange(T, device=dev)[None, :] < L[:, None]).reshape(-1)
+    scale = float(ref[valid].abs().max())
+    assert float((C[valid].double() - ref[valid]).abs().max()) < 1e-5 * scale
+
+
+def test_gemm_tcx_rejects_bad_arguments():
+    from silent_speech_b200 import ops
+    from silent_speech_b200._lib import SsbError
+    dev = _cuda()
+    A, Bm, C = (torch.zeros(64, 64, device=dev) for _ in range(3))
+    with pytest.raises(SsbError):
+        ops.gemm_tcx(A, Bm, C, 8, 8, 8, sa=(2, 3), sb=(64, 1), ldc=64)              # A contiguous along neither index
+    with pytest.raises(SsbError):
+        ops.gemm_tcx(A, Bm, C, 8, 8, 64, sa=(1, 64), sb=(64, 1), ldc=64, split_k=2)   # split-K needs accumulate
