@@ -77,6 +77,58 @@ __device__ __forceinline__ float tanh_fast(float x) {
   return copysignf(__fdividef(1.0f - e, 1.0f + e), x);
 }
 
+// Global accesses of the gate warps.  A TMEM lane is a clip, so the 32 lanes of a warp own 32 different rows of gi / out /
+// gates, and a float4 access per lane touches 32 different 128-byte lines per instruction -- the LSU spends one cycle per
+// line, and with 12 + 4 (+ 16 when the gates are saved) such instructions per thread and step the split-mode recurrence was
+// bound by exactly that (13.2 us per step with saved gates, 8.4 without).  Instead the four lanes of a quad read / write the
+// four consecutive float4 of ONE row per instruction (a quarter-warp covers 2 x 64 contiguous bytes: 8 lines per
+// instruction instead of 32) and a 4x4 transpose over the quad (two shuffle butterflies; an involution, so the same call
+// serves loads and stores) moves every item to / from the lane that owns the row.
+__device__ __forceinline__ void quad_transpose(float4 (&v)[4], int lane) {
+#pragma unroll
+  for (int mask = 1; mask <= 2; mask <<= 1) {
+    const bool up = (lane & mask) != 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (i & mask) continue;
+      const int i2 = i | mask;
+      const float4 send = up ? v[i] : v[i2];
+      float4 recv;
+      recv.x = __shfl_xor_sync(0xffffffffu, send.x, mask);
+      recv.y = __shfl_xor_sync(0xffffffffu, send.y, mask);
+      recv.z = __shfl_xor_sync(0xffffffffu, send.z, mask);
+      recv.w = __shfl_xor_sync(0xffffffffu, send.w, mask);
+      if (up) v[i] = recv; else v[i2] = recv;
+    }
+  }
+}
+// the row pointer of quad member i (nullptr = that row is inactive); all 32 lanes must call
+template <typename P>
+__device__ __forceinline__ P* quad_ptr(P* mine, int lane, int i) {
+  return reinterpret_cast<P*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(mine), (lane & ~3) | i));
+}
+// v[0..3] = the four float4 of this lane's row segment (64 bytes at `mine`); zeros when the row is inactive
+__device__ __forceinline__ void quad_load64(const float* mine, float4 (&v)[4], int lane) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float* p = quad_ptr(mine, lane, i);
+    v[i] = p ? __ldg(reinterpret_cast<const float4*>(p) + (lane & 3)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  quad_transpose(v, lane);
+}
+// this lane's 16 floats -> the 64-byte row segment at `mine` (skipped when nullptr)
+__device__ __forceinline__ void quad_store64(float* mine, const float* x16, int lane) {
+  float4 v[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v[i] = make_float4(x16[4 * i], x16[4 * i + 1], x16[4 * i + 2], x16[4 * i + 3]);
+  quad_transpose(v, lane);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float* p = quad_ptr(mine, lane, i);
+    if (p) reinterpret_cast<float4*>(p)[lane & 3] = v[i];
+  }
+}
+
 template <bool kSplit, bool kSave, int kGi>
 __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(THREADS, 1)
 gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
@@ -255,12 +307,15 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
       const int64_t bt = (int64_t)(act ? b : 0) * T + (act ? t : 0);
       float4 g4[12];                                             // gi: 3 gates x 16 units
       if (kSplit) {
-        if (act) {
-          const float* gp = gi + bt * gi_ld + dir * G3 + j0;
+        {
+          const float* gp = act ? gi + bt * gi_ld + dir * G3 + j0 : nullptr;
 #pragma unroll
-          for (int g = 0; g < 3; ++g)
+          for (int g = 0; g < 3; ++g) {
+            float4 q4[4];
+            quad_load64(gp ? gp + g * H : nullptr, q4, lane);
 #pragma unroll
-            for (int v = 0; v < 4; ++v) g4[g * 4 + v] = __ldg(reinterpret_cast<const float4*>(gp + g * H) + v);
+            for (int v = 0; v < 4; ++v) g4[g * 4 + v] = q4[v];
+          }
         }
         prefetch_gi(s + 1);
       } else if (kGi == 2) {
@@ -318,6 +373,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
         tc::mbar_wait_bounded(&ctl.mma_done, (s - 1) & 1);
         tc::fence_after_sync();
       }
+      float sv[kSave ? 4 : 1][kSave ? UT : 1];                   // kSave: r, z, n, W_hn h + b_hn, written out after the hand-off
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         float ar[8], az[8], an[8];
@@ -345,15 +401,10 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
             h[u] = (1.0f - z8[q]) * n8[q] + z8[q] * h[u];
           }
           if (kSave) {
-            float* gs = gates + (bt * 2 + dir) * (4 * H) + j0 + c * 8;
-            *reinterpret_cast<float4*>(gs) = make_float4(r8[0], r8[1], r8[2], r8[3]);
-            *reinterpret_cast<float4*>(gs + 4) = make_float4(r8[4], r8[5], r8[6], r8[7]);
-            *reinterpret_cast<float4*>(gs + H) = make_float4(z8[0], z8[1], z8[2], z8[3]);
-            *reinterpret_cast<float4*>(gs + H + 4) = make_float4(z8[4], z8[5], z8[6], z8[7]);
-            *reinterpret_cast<float4*>(gs + 2 * H) = make_float4(n8[0], n8[1], n8[2], n8[3]);
-            *reinterpret_cast<float4*>(gs + 2 * H + 4) = make_float4(n8[4], n8[5], n8[6], n8[7]);
-            *reinterpret_cast<float4*>(gs + 3 * H) = make_float4(hn8[0], hn8[1], hn8[2], hn8[3]);
-            *reinterpret_cast<float4*>(gs + 3 * H + 4) = make_float4(hn8[4], hn8[5], hn8[6], hn8[7]);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              sv[0][c * 8 + q] = r8[q]; sv[1][c * 8 + q] = z8[q]; sv[2][c * 8 + q] = n8[q]; sv[3][c * 8 + q] = hn8[q];
+            }
           }
           // Before this CTA's slice is overwritten with h(s): every peer has finished MMA #s, i.e. it has consumed
           // h(s-1) -- which also means the outgoing bulk copies of h(s-1), whose SOURCE is this slice, have landed
@@ -376,11 +427,11 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
       tc::mbar_arrive(&ctl.ready);                               // 384 arrivals: h(s) is complete in this CTA's slice
       // Global traffic goes AFTER the exchange has been kicked off: the proxy fence above waits for this thread's
       // outstanding memory operations, and a global store / cp.async in front of it put HBM latency on every step.
-      if (act) {
-        float* orow = out + bt * (2 * H) + dir * H + j0;
+      quad_store64(act ? out + bt * (2 * H) + dir * H + j0 : nullptr, h, lane);
+      if (kSave) {                                               // 16 stores that used to sit in front of the proxy fence
+        float* gs = act ? gates + (bt * 2 + dir) * (4 * H) + j0 : nullptr;
 #pragma unroll
-        for (int v = 0; v < UT / 4; ++v)
-          reinterpret_cast<float4*>(orow)[v] = make_float4(h[4 * v], h[4 * v + 1], h[4 * v + 2], h[4 * v + 3]);
+        for (int g = 0; g < 4; ++g) quad_store64(gs ? gs + g * H : nullptr, sv[g], lane);
       }
     }
     // zeros past each clip's length (pad_packed_sequence semantics)
