@@ -94,11 +94,13 @@ int ssb_head_bwd_pool(const float* dln, const float* xhat, const float* rstd, co
 int ssb_colsum(const float* A, int64_t lda, int64_t M, int64_t N, float* out, void* stream);
 
 /* K2-bwd: weight gradients of the fused ROI CNN (backward of train_model_official.py:209-229 as run by
- * loss.backward(), train:437).  The forward is recomputed per frame in shared memory.  grads_host =
- * 8 device pointers in the order of weights_host; they are accumulated into (+=). */
+ * loss.backward(), train:437).  saved = NULL: the forward is recomputed per frame in shared memory; saved = the records
+ * of ssb_roi_cnn_fwd_tc3 for the same R / lengths / weights: the recompute is skipped.  grads_host = 8 device pointers
+ * in the order of weights_host; they are accumulated into (+=). */
 int ssb_roi_cnn_bwd(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
                     int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
-                    const float* d_out, int64_t d_out_stride, float* const* grads_host, void* stream);
+                    const float* d_out, int64_t d_out_stride, float* const* grads_host, const void* saved,
+                    void* stream);
 
 /* K3-bwd: back-propagation through time of one bidirectional GRU layer (ATen's GRU backward under
  * train:437).  dout/out [B,T,384]; gates from ssb_gru_layer_fwd; whhT_* = W_hh^T [192,576].
@@ -166,7 +168,11 @@ int ssb_gru_layer_fwd_tc(const void* gi, int64_t gi_ld, const int64_t* lengths, 
  * frame is prefetched, conv2 tiles are committed one by one.  (Third generation of this kernel) */
 int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
                         int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
-                        float* out, int64_t out_stride, int32_t passes, void* stream);
+                        float* out, int64_t out_stride, int32_t passes, void* saved, void* stream);
+/* Training: bytes per frame of the record ssb_roi_cnn_fwd_tc3(passes = 3, saved != NULL) writes for every valid frame
+ * (saved = B*T records): pooled conv1 / conv2 activations (fp32), both max-pool argmax maps, the conv3 ReLU mask and the
+ * channel means -- what ssb_roi_cnn_bwd would otherwise recompute. */
+int64_t ssb_roi_cnn_saved_bytes(void);
 
 /* K3a v2 (fp16 single-pass mode): the input projections of BOTH directions as one persistent GEMM,
  * C[M, N] = [A1 | A2] . [W_a ; W_b]^T + bias (nn.GRU's x W_ih^T + b_ih, train_model_official.py:261-267, forward and

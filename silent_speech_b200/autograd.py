@@ -111,7 +111,7 @@ def backward_impl(model, ctx: Dict, grads: Dict[str, torch.Tensor], dlogits: Opt
         names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
                  "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
         ops.roi_cnn_bwd(ctx["R"], lengths, model.roi_cnn.tensors(), model.standardize_roi, d_emb.view(B, T, -1), 0,
-                        [grads[n] for n in names])
+                        [grads[n] for n in names], saved=ctx.get("cnn_saved"))
 
 
 class ClassifierFn(torch.autograd.Function):

@@ -19,6 +19,11 @@ namespace ssb {
 namespace cnn {
 
 constexpr int A3_COL0 = 2;     // interior of the saved conv3 plane starts at column 2 (float2-aligned pairs)
+// per-frame record written by the split-mode forward kernel (roi_cnn_tc3.cu: SV_*; ssb_roi_cnn_saved_bytes)
+constexpr int SV_A1 = 0, SV_A2 = 36864, SV_IDX1 = 55296, SV_IDX2 = 57600, SV_MASK3 = 58752, SV_MEAN3 = 59904, SV_BYTES = 60000;
+static_assert(SV_A2 == H1 * W1 * C1 * 4 && SV_IDX1 == SV_A2 + H2 * W2 * C2 * 4 && SV_IDX2 == SV_IDX1 + H1 * W1 * 2 &&
+              SV_MASK3 == SV_IDX2 + H2 * W2 * 4 && SV_MEAN3 == SV_MASK3 + H2 * W2 * 4 && SV_BYTES == SV_MEAN3 + C3 * 4 + 0 &&
+              kThreads == H2 * W2, "saved-activation record layout");
 
 struct BwdSmem {
   SmemWeights w;
@@ -52,7 +57,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ lengths, int B, int T,
                    Weights gw, int standardize, const float* __restrict__ d_out, int64_t d_out_stride,
                    float* __restrict__ gW1, float* __restrict__ gb1, float* __restrict__ gW2, float* __restrict__ gb2,
-                   float* __restrict__ gW3, float* __restrict__ gb3, float* __restrict__ gWfc, float* __restrict__ gbfc) {
+                   float* __restrict__ gW3, float* __restrict__ gb3, float* __restrict__ gWfc, float* __restrict__ gbfc,
+                   const uint8_t* __restrict__ saved) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BwdSmem& s = *reinterpret_cast<BwdSmem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31;
@@ -90,11 +96,51 @@ roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     // ================= forward recompute
     load_frame(R + f * NPIX, s.in, s.red, tid, standardize != 0);
     __syncthreads();
-    conv1_pool<true>(s.in, s.a1, s.w, s.idx1, tid);
-    __syncthreads();
-    conv2_pool<true>(s.a1, s.a2, s.w, s.idx2, tid);
-    __syncthreads();
-    conv3_save(s.a2, s.w, s.part, s.mean, s.g3, tid);          // ends with a barrier; s.mean valid
+    if (saved) {
+      // the forward call kept what the recompute would produce (a third of this kernel's arithmetic): pooled activations,
+      // pool argmax maps, the conv3 ReLU mask and the channel means -- 60 KB per frame, read once, coalesced
+      const uint8_t* rec = saved + f * SV_BYTES;
+#pragma unroll
+      for (int j = 0; j < H1 * W1 / kThreads; ++j) {             // a1 + idx1: 4 pooled pixels per thread
+        const int item = tid + j * kThreads, py = item / W1, px = item % W1;
+        const float4 v0 = __ldg(reinterpret_cast<const float4*>(rec + SV_A1) + 2 * item);
+        const float4 v1 = __ldg(reinterpret_cast<const float4*>(rec + SV_A1) + 2 * item + 1);
+        const uint32_t am = __ldg(reinterpret_cast<const uint16_t*>(rec + SV_IDX1) + item);
+        const float a[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+        for (int co = 0; co < C1; ++co) {
+          s.a1[co * A1_PLANE + (py + 1) * A1_LD + px + 1] = a[co];
+          s.idx1[co * (H1 * W1) + item] = (uint8_t)((am >> (2 * co)) & 3u);
+        }
+      }
+      {                                                          // a2 + idx2 + conv3 mask: one pooled pixel per thread
+        const int py = tid / W2, px = tid % W2;
+        const uint32_t am = __ldg(reinterpret_cast<const uint32_t*>(rec + SV_IDX2) + tid);
+        const uint32_t on = __ldg(reinterpret_cast<const uint32_t*>(rec + SV_MASK3) + tid);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float4 v = __ldg(reinterpret_cast<const float4*>(rec + SV_A2) + 4 * tid + q);
+          const float a[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int c = 4 * q + e;
+            s.a2[c * A2_PLANE + (py + 1) * A2_LD + px + 1] = a[e];
+            s.idx2[c * (H2 * W2) + tid] = (uint8_t)((am >> (2 * c)) & 3u);
+          }
+        }
+        float* g = s.g3 + (py + 1) * A3_LD + px + A3_COL0;
+#pragma unroll
+        for (int c = 0; c < C3; ++c) g[c * A3_PLANE] = ((on >> c) & 1u) ? 1.f : 0.f;    // B0 only tests g > 0
+      }
+      if (tid < C3) s.mean[tid] = __ldg(reinterpret_cast<const float*>(rec + SV_MEAN3) + tid);
+      __syncthreads();
+    } else {
+      conv1_pool<true>(s.in, s.a1, s.w, s.idx1, tid);
+      __syncthreads();
+      conv2_pool<true>(s.a1, s.a2, s.w, s.idx2, tid);
+      __syncthreads();
+      conv3_save(s.a2, s.w, s.part, s.mean, s.g3, tid);          // ends with a barrier; s.mean valid
+    }
 
     // ================= B0: fc, mean, relu mask of conv3
     if (tid < E) s.dE[tid] = d_out[f * d_out_stride + tid];
@@ -394,16 +440,20 @@ roi_cnn_bwd_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 }  // namespace ssb
 
 // Accumulates (+=) the 8 parameter gradients {net.0.w,b, net.3.w,b, net.6.w,b, fc.w,b} of the fused
-// ROI CNN given d_out[(b*T+t)*d_out_stride + 0..31] = dL/d(embedding).  R is re-read and the forward
-// recomputed in shared memory; nothing is saved by the forward call.
+// ROI CNN given d_out[(b*T+t)*d_out_stride + 0..31] = dL/d(embedding).  saved = NULL: R is re-read and the forward
+// recomputed in shared memory (nothing kept by the forward call).  saved = the records written by
+// ssb_roi_cnn_fwd_tc3(passes = 3, saved) for the SAME R / lengths / weights: the recompute is skipped (R is still read
+// for the conv1 weight gradient).
 extern "C" int ssb_roi_cnn_bwd(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
                                int32_t roi_h, int32_t roi_w, const float* const* weights, int32_t standardize,
-                               const float* d_out, int64_t d_out_stride, float* const* grads, void* stream) {
+                               const float* d_out, int64_t d_out_stride, float* const* grads, const void* saved,
+                               void* stream) {
   using namespace ssb;
   using namespace ssb::cnn;
   SSB_REQUIRE(R && weights && d_out && grads, "null pointer");
   SSB_REQUIRE(roi_h == H0 && roi_w == W0, "ROI must be 48x96");
   SSB_REQUIRE(d_out_stride >= E, "d_out_stride < 32");
+  SSB_REQUIRE(((uintptr_t)saved & 15) == 0, "saved must be 16-byte aligned");
   for (int i = 0; i < 8; ++i) SSB_REQUIRE(weights[i] && grads[i], "null weight/grad pointer");
   if (B * T == 0) return SSB_OK;
   Weights gw{weights[0], weights[1], weights[2], weights[3], weights[4], weights[5], weights[6], weights[7]};
@@ -412,7 +462,7 @@ extern "C" int ssb_roi_cnn_bwd(const uint8_t* R, const int64_t* lengths, int64_t
   const int grid = (int)(frames < kSMs ? frames : kSMs);
   roi_cnn_bwd_kernel<<<grid, kThreads, sizeof(BwdSmem), (cudaStream_t)stream>>>(
       R, lengths, (int)B, (int)T, gw, standardize, d_out, d_out_stride,
-      grads[0], grads[1], grads[2], grads[3], grads[4], grads[5], grads[6], grads[7]);
+      grads[0], grads[1], grads[2], grads[3], grads[4], grads[5], grads[6], grads[7], reinterpret_cast<const uint8_t*>(saved));
   SSB_LAUNCH_CHECK();
   return SSB_OK;
 }

@@ -35,6 +35,9 @@ constexpr int H0 = 48, W0 = 96, NPIX = H0 * W0;
 constexpr int H1 = 24, W1 = 48, C1 = 8;                // pooled conv1 output
 constexpr int H2 = 12, W2 = 24, C2 = 16;               // pooled conv2 output
 constexpr int C3 = 24, C3P = 32, E = 32;
+// Training: activations handed to the backward kernel instead of being recomputed there (one record per frame, the
+// layout ssb_roi_cnn_bwd reads -- see roi_cnn.cuh: SAVED_*).
+constexpr int SV_A1 = 0, SV_A2 = 36864, SV_IDX1 = 55296, SV_IDX2 = 57600, SV_MASK3 = 58752, SV_MEAN3 = 59904, SV_BYTES = 60000;
 constexpr int PIX_LD = 100, PIX_ROWS = 50;             // standardised frame, fp16, interior at [1..48][1..96]
 constexpr int PIX_BYTES = PIX_ROWS * PIX_LD * 2;       // 10,000
 constexpr int P1_ROWS = 13, P1_COLS = 25;              // a1 parity plane: [13][25] pixels x 16 B
@@ -135,7 +138,7 @@ template <bool kSplit, int kSlots, int ST>
 __global__ void __launch_bounds__(ST * kSlots, 1)
 roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ lengths, int B, int T,
                    Weights gw, int standardize, float* __restrict__ out, int64_t out_stride,
-                   unsigned int* __restrict__ counter) {
+                   unsigned int* __restrict__ counter, uint8_t* __restrict__ saved) {
   using L = Lay<kSplit>;
   constexpr int NWG = ST / 128;                        // warps per TMEM lane quarter
   constexpr int WPT = (NPIX / 4 + ST - 1) / ST;        // 4-pixel words per thread: 9 (ST=128) or 5 (ST=256)
@@ -413,6 +416,25 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           // biases as 16-byte broadcast loads (a scalar LDS per use made them a tenth of the kernel's shared-memory wavefronts)
           *reinterpret_cast<float4*>(bb) = *reinterpret_cast<const float4*>(sh.b1);
           *reinterpret_cast<float4*>(bb + 4) = *reinterpret_cast<const float4*>(sh.b1 + 4);
+          if (kSplit && saved) {                                          // fp32 activations + pool argmax for the backward pass
+            float a[8];
+            uint32_t am = 0;
+#pragma unroll
+            for (int co = 0; co < 8; ++co) {                              // first maximum in row-major order (ATen's choice)
+              float m = v[co];
+              uint32_t arg = 0;
+              if (v[8 + co] > m) { m = v[8 + co]; arg = 1; }
+              if (v[16 + co] > m) { m = v[16 + co]; arg = 2; }
+              if (v[24 + co] > m) { m = v[24 + co]; arg = 3; }
+              am |= arg << (2 * co);
+              a[co] = fmaxf(m + bb[co], 0.f);
+            }
+            const int Pp = (tile0 + tl) * 128 + row;
+            uint8_t* rec = saved + f * SV_BYTES;
+            reinterpret_cast<float4*>(rec + SV_A1)[2 * Pp] = make_float4(a[0], a[1], a[2], a[3]);
+            reinterpret_cast<float4*>(rec + SV_A1)[2 * Pp + 1] = make_float4(a[4], a[5], a[6], a[7]);
+            reinterpret_cast<uint16_t*>(rec + SV_IDX1)[Pp] = (uint16_t)am;
+          }
 #pragma unroll
           for (int co = 0; co < 8; ++co) {
             const float m4 = fmaxf(fmaxf(v[co], v[8 + co]), fmaxf(v[16 + co], v[24 + co]));
@@ -465,6 +487,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         // 256-thread slots: warpgroup wg owns output channels 8wg..8wg+7 (= channel plane wg of a2); per sub-position
         // it adds the A_hi.B_lo half (columns 64..) to the main half, then max / bias / ReLU / hi-lo split
         float m4[8];
+        uint32_t am = 0;                                                 // pool argmax, 2 bits per channel (saved for training)
 #pragma unroll
         for (int sub = 0; sub < 4; ++sub) {
           float a[8], bq[8];
@@ -472,7 +495,11 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           tc::tmem_ld8(tq + dcol + 64 + sub * 16 + wg * 8, bq);
           tc::tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 8; ++i) m4[i] = sub == 0 ? a[i] + bq[i] : fmaxf(m4[i], a[i] + bq[i]);
+          for (int i = 0; i < 8; ++i) {
+            const float x = a[i] + bq[i];
+            if (sub == 0) { m4[i] = x; }
+            else if (x > m4[i]) { m4[i] = x; am = (am & ~(3u << (2 * i))) | ((uint32_t)sub << (2 * i)); }
+          }
         }
         if (a2off[tl] >= 0) {
           float hi[8], lo[8];
@@ -483,6 +510,14 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 #pragma unroll
           for (int i = 0; i < 8; ++i) tc::split_bf16(fmaxf(m4[i] + bb[i], 0.f), hi[i], lo[i]);
           const uint32_t off = (uint32_t)a2off[tl] + wg * PLANE2;
+          if (saved) {
+            const int vp = tl * 128 + row, pix = (vp / P1_COLS) * W2 + vp % P1_COLS;
+            uint8_t* rec = saved + f * SV_BYTES;
+            float4* d = reinterpret_cast<float4*>(rec + SV_A2) + pix * 4 + wg * 2;
+            d[0] = make_float4(fmaxf(m4[0] + bb[0], 0.f), fmaxf(m4[1] + bb[1], 0.f), fmaxf(m4[2] + bb[2], 0.f), fmaxf(m4[3] + bb[3], 0.f));
+            d[1] = make_float4(fmaxf(m4[4] + bb[4], 0.f), fmaxf(m4[5] + bb[5], 0.f), fmaxf(m4[6] + bb[6], 0.f), fmaxf(m4[7] + bb[7], 0.f));
+            reinterpret_cast<uint16_t*>(rec + SV_IDX2)[pix * 2 + wg] = (uint16_t)am;
+          }
           *reinterpret_cast<uint4*>(r0 + off) = pack8(hi);
           *reinterpret_cast<uint4*>(r0 + A2_BYTES + off) = pack8(lo);
         }
@@ -577,14 +612,19 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         } else {
           tc::tmem_ld_wait();
         }
+        uint32_t on = 0;                                                 // relu'(conv3) per channel (saved for training)
 #pragma unroll
         for (int c4 = 0; c4 < C3 / 4; ++c4) {
           const float4 bq = *reinterpret_cast<const float4*>(sh.b3 + 4 * c4);
-          acc[4 * c4 + 0] += fmaxf(v[4 * c4 + 0] + bq.x, 0.f);
-          acc[4 * c4 + 1] += fmaxf(v[4 * c4 + 1] + bq.y, 0.f);
-          acc[4 * c4 + 2] += fmaxf(v[4 * c4 + 2] + bq.z, 0.f);
-          acc[4 * c4 + 3] += fmaxf(v[4 * c4 + 3] + bq.w, 0.f);
+          const float x0 = v[4 * c4 + 0] + bq.x, x1 = v[4 * c4 + 1] + bq.y, x2 = v[4 * c4 + 2] + bq.z, x3 = v[4 * c4 + 3] + bq.w;
+          acc[4 * c4 + 0] += fmaxf(x0, 0.f);
+          acc[4 * c4 + 1] += fmaxf(x1, 0.f);
+          acc[4 * c4 + 2] += fmaxf(x2, 0.f);
+          acc[4 * c4 + 3] += fmaxf(x3, 0.f);
+          if (kSplit) on |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * c4);
         }
+        if (kSplit && saved)                                             // tile tx: image rows row/8, columns 8 tx + row%8
+          reinterpret_cast<uint32_t*>(saved + f * SV_BYTES + SV_MASK3)[(row >> 3) * W2 + tx * 8 + (row & 7)] = on;
       }
     }
     if (q < 3) {
@@ -607,6 +647,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 #pragma unroll
       for (int i = 0; i < 3 * NWG; ++i) cs += mz.part[i][lane];
       cs *= 1.0f / (float)(H2 * W2);
+      if (kSplit && saved && tid < C3) reinterpret_cast<float*>(saved + f * SV_BYTES + SV_MEAN3)[tid] = cs;
       float a = sh.bfc[tid];
 #pragma unroll
       for (int c = 0; c < C3; ++c) a = fmaf(sh.wfc[tid][c], __shfl_sync(0xffffffffu, cs, c), a);
@@ -631,12 +672,16 @@ constexpr size_t smem_total() {
 
 // K2 v3 (see the header comment).  Same arguments as ssb_roi_cnn_fwd_tc; passes = 1: four 128-thread frame
 // slots per CTA; passes = 3 (split, fp32-parity grade): two 256-thread slots (shared memory bound).
+// saved (nullable, passes = 3): B*T records of ssb_roi_cnn_saved_bytes() bytes that receive the pooled activations, pool
+// argmax maps, conv3 ReLU mask and channel means of every valid frame, for ssb_roi_cnn_bwd.
+extern "C" int64_t ssb_roi_cnn_saved_bytes(void) { return ssb::cnn3::SV_BYTES; }
 extern "C" int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
                                    int32_t roi_h, int32_t roi_w, const float* const* weights, int32_t standardize,
-                                   float* out, int64_t out_stride, int32_t passes, void* stream) {
+                                   float* out, int64_t out_stride, int32_t passes, void* saved, void* stream) {
   using namespace ssb;
   using namespace ssb::cnn3;
   SSB_REQUIRE(R && weights && out, "null pointer");
+  SSB_REQUIRE(!saved || (passes == 3 && ((uintptr_t)saved & 15) == 0), "saved activations: split mode only, 16-byte aligned");
   SSB_REQUIRE(roi_h == H0 && roi_w == W0, "ROI must be 48x96 (train_model_official.py:38)");
   SSB_REQUIRE(out_stride >= E, "out_stride < 32");
   SSB_REQUIRE(passes == 1 || passes == 3, "passes must be 1 or 3");
@@ -655,7 +700,8 @@ extern "C" int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int
     const int64_t want = (frames + kSlots - 1) / kSlots;
     const int grid = (int)(want < kSMs ? want : kSMs);
     SSB_CUDA(cudaFuncSetAttribute(roi_cnn_tc3_kernel<true, kSlots, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    roi_cnn_tc3_kernel<true, kSlots, ST><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride, counter);
+    roi_cnn_tc3_kernel<true, kSlots, ST><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride, counter,
+                                                                          reinterpret_cast<uint8_t*>(saved));
   } else {
     constexpr int kSlots = 4, ST = 128;
     constexpr size_t smem = smem_total<false, kSlots>();
@@ -663,7 +709,7 @@ extern "C" int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int
     const int64_t want = (frames + kSlots - 1) / kSlots;
     const int grid = (int)(want < kSMs ? want : kSMs);
     SSB_CUDA(cudaFuncSetAttribute(roi_cnn_tc3_kernel<false, kSlots, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    roi_cnn_tc3_kernel<false, kSlots, ST><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride, counter);
+    roi_cnn_tc3_kernel<false, kSlots, ST><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride, counter, nullptr);
   }
   SSB_LAUNCH_CHECK();
   return SSB_OK;

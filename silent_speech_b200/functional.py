@@ -57,9 +57,13 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
         ctx["emb"] = emb
     elif R is not None:
         R = R.to(dev).contiguous()
+        cnn_saved = None
+        if save and _passes(model)[0] == 3:      # training in split mode: the forward keeps what the backward would recompute
+            cnn_saved = ops.roi_cnn_saved(B, T, dev)
         emb = ops.roi_cnn_fwd(R, lengths, model.roi_cnn.tensors(), standardize=model.standardize_roi,
-                              passes=_passes(model)[0])
+                              passes=_passes(model)[0], saved=cnn_saved)
         ctx["R"] = R
+        ctx["cnn_saved"] = cnn_saved
         ctx["emb"] = emb
     gi = torch.empty(B, T, 2 * G3, device=dev, dtype=torch.float32)
     gi2d = gi.view(B * T, 2 * G3)

@@ -66,8 +66,9 @@ def features_fwd(landmarks: torch.Tensor, ids: torch.Tensor, anchor_ids: Sequenc
 # ----------------------------------------------------------------------------- K2
 def roi_cnn_fwd(R: torch.Tensor, lengths: Optional[torch.Tensor], weights: Sequence[torch.Tensor],
                 standardize: bool = True, out: Optional[torch.Tensor] = None, out_col: int = 0,
-                passes: int = 0) -> torch.Tensor:
-    """R u8 [B,T,48,96] -> embedding f32 [B,T,32] (or written into out[..., out_col:out_col+32])."""
+                passes: int = 0, saved: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """R u8 [B,T,48,96] -> embedding f32 [B,T,32] (or written into out[..., out_col:out_col+32]).
+    saved (passes = 3): uint8 [B*T, roi_cnn_saved_bytes()] receiving the activations roi_cnn_bwd needs."""
     _need(R, torch.uint8, "R")
     B, T, Hh, Ww = R.shape
     for w in weights:
@@ -84,7 +85,7 @@ def roi_cnn_fwd(R: torch.Tensor, lengths: Optional[torch.Tensor], weights: Seque
     if passes:
         check(_lib.lib().ssb_roi_cnn_fwd_tc3(ptr(R), ptr(lengths), i64(B), i64(T), i32(Hh), i32(Ww), ptr_array(weights),
                                             i32(1 if standardize else 0), ctypes.c_void_p(base), i64(stride),
-                                            i32(passes), stream_ptr()))
+                                            i32(passes), ptr(saved), stream_ptr()))
         return out
     check(_lib.lib().ssb_roi_cnn_fwd(ptr(R), ptr(lengths), i64(B), i64(T), i32(Hh), i32(Ww), ptr_array(weights),
                                      i32(1 if standardize else 0), ctypes.c_void_p(base), i64(stride), stream_ptr()))
@@ -200,14 +201,22 @@ def colsum(A2d: torch.Tensor, out: torch.Tensor):
 
 
 # ----------------------------------------------------------------------------- backward / optimiser
-def roi_cnn_bwd(R, lengths, weights, standardize, d_out: torch.Tensor, d_col: int, grads):
-    """Accumulates the 8 ROI-CNN parameter gradients from d_out[..., d_col:d_col+32]."""
+def roi_cnn_saved(B: int, T: int, device) -> torch.Tensor:
+    """Buffer for the activations the split-mode forward hands to roi_cnn_bwd (60,000 B per frame)."""
+    L = _lib.lib()
+    L.ssb_roi_cnn_saved_bytes.restype = i64
+    return torch.empty(B * T, int(L.ssb_roi_cnn_saved_bytes()), device=device, dtype=torch.uint8)
+
+
+def roi_cnn_bwd(R, lengths, weights, standardize, d_out: torch.Tensor, d_col: int, grads, saved: Optional[torch.Tensor] = None):
+    """Accumulates the 8 ROI-CNN parameter gradients from d_out[..., d_col:d_col+32].  saved = the buffer the forward
+    filled (roi_cnn_fwd(..., passes=3, saved=...)): skips the recompute."""
     import ctypes
     B, T, Hh, Ww = R.shape
     base = d_out.data_ptr() + 4 * d_col
     check(_lib.lib().ssb_roi_cnn_bwd(ptr(R), ptr(lengths), i64(B), i64(T), i32(Hh), i32(Ww), ptr_array(weights),
                                      i32(1 if standardize else 0), ctypes.c_void_p(base), i64(d_out.shape[-1]),
-                                     ptr_array(grads), stream_ptr()))
+                                     ptr_array(grads), ptr(saved), stream_ptr()))
 
 
 def transpose(x2d: torch.Tensor) -> torch.Tensor:
