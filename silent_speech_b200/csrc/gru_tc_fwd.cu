@@ -135,7 +135,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
                   const float* __restrict__ whh_f, const float* __restrict__ whh_r,
                   const float* __restrict__ bhn_f, const float* __restrict__ bhn_r,
                   const int64_t* __restrict__ lengths, const int32_t* __restrict__ order, int B, int T,
-                  float* __restrict__ out, float* __restrict__ gates) {
+                  float* __restrict__ out, float* __restrict__ gates, int rows) {
   constexpr bool kBlk = kGi != 0;                           // 0: standard fp32 columns, 1: GRU-blocked fp32, 2: GRU-blocked fp16
   static_assert(kGi == 0 || !kSplit, "blocked gi staging exists in single-pass mode only");
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -149,7 +149,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t rank = tc::cluster_ctarank();
   const int dir = blockIdx.y;
-  const int b0 = (blockIdx.x / CL) * BM;
+  const int b0 = (blockIdx.x / CL) * rows;       // rows <= BM clips per cluster: the tile's first `rows` rows are real
   const float* __restrict__ whh = dir ? whh_r : whh_f;
   const float* __restrict__ bhn = dir ? bhn_r : bhn_f;
 
@@ -192,7 +192,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   const int m = (warp & 3) * 32 + lane;          // row of the tile == TMEM lane
   const int ug = (warp >> 2) % 3;                // which 16 of the CTA's 48 units
   int b = -1, len = 0;
-  if (tid < EPI_THREADS && b0 + m < B) {
+  if (tid < EPI_THREADS && m < rows && b0 + m < B) {
     b = order ? order[b0 + m] : b0 + m;
     len = max(0, min((int)lengths[b], T));
   }
@@ -494,14 +494,22 @@ extern "C" int ssb_gru_layer_fwd_tc(const void* gi_, int64_t gi_ld, const int64_
   SSB_REQUIRE(passes == 1 || passes == 3, "passes must be 1 or 3");
   SSB_REQUIRE(gi_layout == 0 || ((gi_layout == 1 || gi_layout == 2) && passes == 1 && !gates), "GRU-blocked gi: single-pass inference only");
   if (B == 0) return SSB_OK;
-  dim3 grid(CL * cdiv(B, BM), 2), block(THREADS);
+  // Small batches: a 128-row tile that is only partly filled costs the tensor core nothing extra, but the per-step work of
+  // the gate warps (gi reads, gate math, out / gates stores) is per REAL row.  So while all clusters still fit one wave
+  // (148 SMs / 4 CTAs / 2 directions = 18 per direction) the clips are dealt out 64 or 32 per cluster: at the train
+  // step's 128 clips per GPU that is 4 clusters per direction on 32 SMs instead of 1 + 1 on 8, each with one busy lane
+  // quarter -- the serial step then costs little more than its MMA + exchange chain.
+  int rows = BM;
+  if (cdiv(B, 32) <= 18) rows = 32;
+  else if (cdiv(B, 64) <= 18) rows = 64;
+  dim3 grid(CL * cdiv(B, rows), 2), block(THREADS);
   cudaStream_t st = (cudaStream_t)stream;
 #define SSB_LAUNCH_GRUTC(SPLIT, SAVE, BLK)                                                                          \
   do {                                                                                                               \
     SSB_CUDA(cudaFuncSetAttribute(gru_tc_fwd_kernel<SPLIT, SAVE, BLK>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
                                   (int)smem_bytes<SPLIT>()));                                                        \
     gru_tc_fwd_kernel<SPLIT, SAVE, BLK><<<grid, block, smem_bytes<SPLIT>(), st>>>(                                   \
-        gi, gi_ld, whh_f, whh_r, bhh_f + 2 * H, bhh_r + 2 * H, lengths, order, (int)B, (int)T, out, gates);          \
+        gi, gi_ld, whh_f, whh_r, bhh_f + 2 * H, bhh_r + 2 * H, lengths, order, (int)B, (int)T, out, gates, rows);    \
   } while (0)
   if (passes == 3)         { if (gates) SSB_LAUNCH_GRUTC(true, true, 0); else SSB_LAUNCH_GRUTC(true, false, 0); }
   else if (gi_layout == 2) { SSB_LAUNCH_GRUTC(false, false, 2); }
