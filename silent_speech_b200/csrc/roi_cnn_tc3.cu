@@ -134,7 +134,7 @@ __device__ __forceinline__ void build_weights(uint8_t* w1op, uint8_t* w2op, uint
   }
 }
 
-template <bool kSplit, int kSlots, int ST>
+template <bool kSplit, int kSlots, int ST, bool kSave>
 __global__ void __launch_bounds__(ST * kSlots, 1)
 roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ lengths, int B, int T,
                    Weights gw, int standardize, float* __restrict__ out, int64_t out_stride,
@@ -416,7 +416,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           // biases as 16-byte broadcast loads (a scalar LDS per use made them a tenth of the kernel's shared-memory wavefronts)
           *reinterpret_cast<float4*>(bb) = *reinterpret_cast<const float4*>(sh.b1);
           *reinterpret_cast<float4*>(bb + 4) = *reinterpret_cast<const float4*>(sh.b1 + 4);
-          if (kSplit && saved) {                                          // fp32 activations + pool argmax for the backward pass
+          if (kSave) {                                                    // fp32 activations + pool argmax for the backward pass
             float a[8];
             uint32_t am = 0;
 #pragma unroll
@@ -497,7 +497,8 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const float x = a[i] + bq[i];
-            if (sub == 0) { m4[i] = x; }
+            if (!kSave) { m4[i] = sub == 0 ? x : fmaxf(m4[i], x); }
+            else if (sub == 0) { m4[i] = x; }
             else if (x > m4[i]) { m4[i] = x; am = (am & ~(3u << (2 * i))) | ((uint32_t)sub << (2 * i)); }
           }
         }
@@ -510,7 +511,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 #pragma unroll
           for (int i = 0; i < 8; ++i) tc::split_bf16(fmaxf(m4[i] + bb[i], 0.f), hi[i], lo[i]);
           const uint32_t off = (uint32_t)a2off[tl] + wg * PLANE2;
-          if (saved) {
+          if (kSave) {
             const int vp = tl * 128 + row, pix = (vp / P1_COLS) * W2 + vp % P1_COLS;
             uint8_t* rec = saved + f * SV_BYTES;
             float4* d = reinterpret_cast<float4*>(rec + SV_A2) + pix * 4 + wg * 2;
@@ -621,9 +622,9 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           acc[4 * c4 + 1] += fmaxf(x1, 0.f);
           acc[4 * c4 + 2] += fmaxf(x2, 0.f);
           acc[4 * c4 + 3] += fmaxf(x3, 0.f);
-          if (kSplit) on |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * c4);
+          if (kSave) on |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * c4);
         }
-        if (kSplit && saved)                                             // tile tx: image rows row/8, columns 8 tx + row%8
+        if (kSave)                                                       // tile tx: image rows row/8, columns 8 tx + row%8
           reinterpret_cast<uint32_t*>(saved + f * SV_BYTES + SV_MASK3)[(row >> 3) * W2 + tx * 8 + (row & 7)] = on;
       }
     }
@@ -647,7 +648,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 #pragma unroll
       for (int i = 0; i < 3 * NWG; ++i) cs += mz.part[i][lane];
       cs *= 1.0f / (float)(H2 * W2);
-      if (kSplit && saved && tid < C3) reinterpret_cast<float*>(saved + f * SV_BYTES + SV_MEAN3)[tid] = cs;
+      if (kSave && tid < C3) reinterpret_cast<float*>(saved + f * SV_BYTES + SV_MEAN3)[tid] = cs;
       float a = sh.bfc[tid];
 #pragma unroll
       for (int c = 0; c < C3; ++c) a = fmaf(sh.wfc[tid][c], __shfl_sync(0xffffffffu, cs, c), a);
@@ -699,17 +700,23 @@ extern "C" int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int
     static_assert(smem <= 232448, "split-mode smem budget");
     const int64_t want = (frames + kSlots - 1) / kSlots;
     const int grid = (int)(want < kSMs ? want : kSMs);
-    SSB_CUDA(cudaFuncSetAttribute(roi_cnn_tc3_kernel<true, kSlots, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    roi_cnn_tc3_kernel<true, kSlots, ST><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride, counter,
-                                                                          reinterpret_cast<uint8_t*>(saved));
+    if (saved) {
+      SSB_CUDA(cudaFuncSetAttribute(roi_cnn_tc3_kernel<true, kSlots, ST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      roi_cnn_tc3_kernel<true, kSlots, ST, true><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride,
+                                                                                counter, reinterpret_cast<uint8_t*>(saved));
+    } else {
+      SSB_CUDA(cudaFuncSetAttribute(roi_cnn_tc3_kernel<true, kSlots, ST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      roi_cnn_tc3_kernel<true, kSlots, ST, false><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride,
+                                                                                 counter, nullptr);
+    }
   } else {
     constexpr int kSlots = 4, ST = 128;
     constexpr size_t smem = smem_total<false, kSlots>();
     static_assert(smem <= 232448, "fp16-mode smem budget");
     const int64_t want = (frames + kSlots - 1) / kSlots;
     const int grid = (int)(want < kSMs ? want : kSMs);
-    SSB_CUDA(cudaFuncSetAttribute(roi_cnn_tc3_kernel<false, kSlots, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    roi_cnn_tc3_kernel<false, kSlots, ST><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride, counter, nullptr);
+    SSB_CUDA(cudaFuncSetAttribute(roi_cnn_tc3_kernel<false, kSlots, ST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    roi_cnn_tc3_kernel<false, kSlots, ST, false><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride, counter, nullptr);
   }
   SSB_LAUNCH_CHECK();
   return SSB_OK;
