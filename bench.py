@@ -169,6 +169,7 @@ def run_extra(args, rank, world, local):
     import torch.distributed as dist
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    affinity = bind_near_gpu(dev) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -330,6 +331,31 @@ def workload_config(workload, B):
             "frames": T_FRAMES, "lengths": "all=T", "l2": "inputs (1.96 GB/step) larger than L2"}
 
 
+def bind_near_gpu(dev):
+    """Multi-GPU runs: pin this rank's host threads -- and with them the pinned staging buffers allocated afterwards --
+    to the CPUs NVML reports as local to its GPU, so that the e2e arm's host->device copies do not cross the socket
+    interconnect.  (Not done at N=1, where the in-process CPU baseline needs every core.)  Returns a short description."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(dev).uuid)
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(dev.index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if not cpus or len(cpus) == len(allowed):
+            return "all cpus local"
+        os.sched_setaffinity(0, cpus)
+        return f"{len(cpus)} gpu-local cpus of {len(allowed)}"
+    except Exception as e:                      # affinity is an optimisation, never a requirement
+        return f"unbound ({type(e).__name__})"
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -363,6 +389,7 @@ def main():
     import torch.distributed as dist
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    affinity = bind_near_gpu(dev) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -494,7 +521,7 @@ def main():
     clocks = clk.summary()
     if rank == 0:
         cpu = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:      # the contract's CPU baseline: rank 0 at N=1 only
             threads = os.cpu_count() or 1
             v, sample = cpu_reference_rate(args.workload, threads)
             cpu = {"value": v, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample}
@@ -509,6 +536,8 @@ def main():
                 "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
         if parity_mode:
             line["fp32_parity_mode"] = parity_mode
+        if affinity:
+            line["config"]["host_affinity"] = affinity
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
