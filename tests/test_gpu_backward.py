@@ -280,3 +280,33 @@ def test_gemm_tcx_rejects_bad_arguments():
         ops.gemm_tcx(A, Bm, C, 8, 8, 8, sa=(2, 3), sb=(64, 1), ldc=64)              # A contiguous along neither index
     with pytest.raises(SsbError):
         ops.gemm_tcx(A, Bm, C, 8, 8, 64, sa=(1, 64), sb=(64, 1), ldc=64, split_k=2)   # split-K needs accumulate
+
+
+# --------------------------------------------------------------------------------------------- ROI CNN: saved activations
+def test_roi_cnn_backward_from_saved_activations_matches_recompute():
+    """The split-mode forward's exported record (pooled activations, argmax maps, ReLU mask, means) drives the backward
+    kernel to the same parameter gradients as its own fp32 recompute; padded frames are skipped by both."""
+    from silent_speech_b200 import ops, synth
+    dev = _cuda()
+    p = ref_model.synth_params(11)
+    names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
+             "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
+    w = [p[n].to(dev).contiguous() for n in names]
+    d = synth.clip_batch(9, 17, mode="uniform", seed=5)
+    R, L = torch.from_numpy(d["R"]).to(dev), torch.from_numpy(d["lengths"]).to(dev)
+    B, T = R.shape[:2]
+    saved = ops.roi_cnn_saved(B, T, dev)
+    saved.fill_(0xAB)                                   # records of padded frames stay garbage and must not be read
+    emb = ops.roi_cnn_fwd(R, L, w, standardize=True, passes=3, saved=saved)
+    emb_plain = ops.roi_cnn_fwd(R, L, w, standardize=True, passes=3)
+    assert torch.equal(emb, emb_plain)                  # exporting does not change the forward result
+    g = torch.Generator().manual_seed(2)
+    d_emb = torch.randn(B, T, 32, generator=g).to(dev)
+    ga = [torch.zeros_like(x) for x in w]
+    gb = [torch.zeros_like(x) for x in w]
+    ops.roi_cnn_bwd(R, L, w, True, d_emb, 0, ga, saved=saved)
+    ops.roi_cnn_bwd(R, L, w, True, d_emb, 0, gb)
+    for n, a, b in zip(names, ga, gb):
+        assert rel_err(a, b) < 1e-4, n
+    with pytest.raises(Exception):                      # the export exists in split mode only
+        ops.roi_cnn_fwd(R, L, w, standardize=True, passes=1, saved=saved)
