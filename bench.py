@@ -449,13 +449,19 @@ def main():
     # ---- end to end through the public API with host buffers (H2D + D2H inside the timed region).
     # Inference: model.infer_host(X, lengths, R) -- pinned host batch in, host logits out; it overlaps the
     # host->device copy of one 512-clip chunk with the compute of the previous one.  Train: Trainer.step on
-    # freshly copied tensors, loss read back.
+    # batches staged by HostBatchPrefetcher (the copy of batch i+1 runs on a side stream during step i), loss read back.
     h_out = torch.empty(B, NUM_CLASSES, dtype=torch.float32).pin_memory()
+
+    if args.workload == "train":
+        from silent_speech_b200.train import HostBatchPrefetcher
+        prefetch = HostBatchPrefetcher(dev)
+        prefetch.submit(hX, hL, hR, hy)          # batch 0; every timed step copies exactly one (the next) batch
 
     def e2e_step():
         if args.workload == "train":
-            Xd, Ld, Rd = hX.to(dev, non_blocking=True), hL.to(dev, non_blocking=True), hR.to(dev, non_blocking=True)
-            return trainer.step(Xd, Ld, Rd, hy.to(dev, non_blocking=True)).cpu()
+            Xd, Ld, Rd, yd = prefetch.get()
+            prefetch.submit(hX, hL, hR, hy)      # the next step's batch travels while this step computes
+            return trainer.step(Xd, Ld, Rd, yd).cpu()
         return model.infer_host(hX, hL, hR, chunk=args.e2e_chunk, out=h_out)
     e2e_step()
     barrier()

@@ -118,3 +118,42 @@ class Trainer:
                            write_back_grad=True, norm_out=self.grad_norm)
         self.launches_per_step = _lib.launch_count() - c0
         return loss
+
+
+class HostBatchPrefetcher:
+    """Double-buffered host -> device staging for the training loop (train_model_official.py:428-439 iterates a
+    DataLoader of CPU batches and moves each one to the device right before its step).
+
+    ``submit(*host_tensors)`` starts the copy of the NEXT batch from pinned host memory on a side stream;
+    ``get()`` makes the compute stream wait for it and returns the device tensors.  Calling ``submit`` for batch
+    i+1 before ``Trainer.step`` on batch i hides the PCIe time (61 MB per 128 clips) behind the step's kernels.
+    """
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(self.device)
+        self._pending = None
+
+    def submit(self, *host_tensors):
+        if self._pending is not None:
+            raise RuntimeError("previous batch was not consumed: call get() first")
+        for t in host_tensors:
+            if t is not None and not t.is_pinned():
+                raise ValueError("host batches must live in pinned memory for an asynchronous copy")
+        with torch.cuda.stream(self.stream):
+            dev = tuple(None if t is None else t.to(self.device, non_blocking=True) for t in host_tensors)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        self._pending = (dev, ev)
+
+    def get(self):
+        if self._pending is None:
+            raise RuntimeError("no batch in flight: call submit() first")
+        dev, ev = self._pending
+        self._pending = None
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(ev)
+        for t in dev:
+            if t is not None:
+                t.record_stream(cur)         # allocated on the side stream, used on the compute stream
+        return dev

@@ -310,3 +310,32 @@ def test_roi_cnn_backward_from_saved_activations_matches_recompute():
         assert rel_err(a, b) < 1e-4, n
     with pytest.raises(Exception):                      # the export exists in split mode only
         ops.roi_cnn_fwd(R, L, w, standardize=True, passes=1, saved=saved)
+
+
+def test_host_batch_prefetcher_feeds_identical_steps():
+    """Steps fed through the double-buffered host->device prefetcher produce the same losses as direct device tensors."""
+    from silent_speech_b200 import synth
+    from silent_speech_b200.train import HostBatchPrefetcher, Trainer
+    dev = _cuda()
+    p = ref_model.synth_params(5)
+    batches = [synth.clip_batch(6, 12, mode="uniform", seed=s) for s in (1, 2, 3)]
+    host = [tuple(torch.from_numpy(d[k]).pin_memory() for k in ("X", "lengths", "R", "y")) for d in batches]
+    losses = []
+    for use_pf in (False, True):
+        tr = Trainer(_model(p, True, dev).eval(), dropout=False)
+        out = []
+        if use_pf:
+            pf = HostBatchPrefetcher(dev)
+            pf.submit(*host[0])
+            for i in range(3):
+                b = pf.get()
+                if i + 1 < 3:
+                    pf.submit(*host[i + 1])
+                out.append(tr.step(*b).mean().item())
+            with pytest.raises(RuntimeError):
+                pf.get()
+        else:
+            for h in host:
+                out.append(tr.step(*(t.to(dev) for t in h)).mean().item())
+        losses.append(out)
+    assert losses[0] == losses[1]
