@@ -37,28 +37,32 @@ def _wgrad(dY2d, y_col0, y_cols, ldy, X2d, x_col0, x_cols, ldx, gW, gw_off, ldw,
               split_k=_split_k(rows), a_off=y_col0, b_off=x_col0, c_off=gw_off)
 
 
-def _gru_layer_backward(layer: int, dseq, seq_out, gates, lengths, B, T, inputs, model, grads, want_dinput):
-    """inputs: list of (tensor2d [B*T, width], column offset inside weight_ih) feeding this layer."""
+_SIDE_STREAMS: Dict[int, "torch.cuda.Stream"] = {}
+
+
+def _side_stream(device) -> "torch.cuda.Stream":
+    """One auxiliary stream per device for work that is off the backward pass's critical path."""
+    idx = torch.device(device).index
+    idx = torch.cuda.current_device() if idx is None else idx
+    if idx not in _SIDE_STREAMS:
+        _SIDE_STREAMS[idx] = torch.cuda.Stream(idx)
+    return _SIDE_STREAMS[idx]
+
+
+def _gru_layer_backward(layer: int, dseq, seq_out, gates, lengths, B, T, inputs, model, grads, want_dinput, side=None):
+    """inputs: list of (tensor2d [B*T, width], column offset inside weight_ih) feeding this layer.
+
+    Order: BPTT, then the data gradient (the next stage waits for it), then the weight / bias gradients.  With ``side``
+    (a CUDA stream) the latter are enqueued there: nothing downstream reads them before the optimizer, and the next
+    stage (the other layer's BPTT: 128 latency-bound CTAs) leaves room on every SM for the GEMM CTAs to run beside it."""
     p = model.gru.layer(layer)
-    tc = _passes(model)[1] != 0          # tensor-core modes: GEMM-shaped gradients on tcgen05 (split-bf16 x3)
+    tc = _passes(model)[1] != 0          # tensor-core modes: GEMM-shaped gradients on tcgen05 (split-fp16 x3)
     whhT = [ops.transpose(p["weight_hh"][d]) for d in (0, 1)]
     dgi, dghn, hprev = ops.gru_layer_bwd(dseq, seq_out, gates, whhT[0], whhT[1], lengths)
     M = B * T
     dgi2d, dghn2d, hprev2d = dgi.view(M, 2 * G3), dghn.view(M, 2 * H), hprev.view(M, 2 * H)
     amax = ops.absmax(dgi) if tc else None          # |dghn| = |dgi_n * r| <= |dgi_n|: one scale serves both tensors
     dinput = None
-    for d, sfx in ((0, ""), (1, "_reverse")):
-        g_wih, g_whh = grads[f"gru.weight_ih_l{layer}{sfx}"], grads[f"gru.weight_hh_l{layer}{sfx}"]
-        g_bih, g_bhh = grads[f"gru.bias_ih_l{layer}{sfx}"], grads[f"gru.bias_hh_l{layer}{sfx}"]
-        width = g_wih.shape[1]
-        for x2d, col0 in inputs:
-            _wgrad(dgi2d, d * G3, G3, 2 * G3, x2d, 0, x2d.shape[1], x2d.stride(0), g_wih, col0, width, M, amax)
-        ops.colsum(dgi2d[:, d * G3:(d + 1) * G3], g_bih)
-        # hidden projection: r,z rows share dgi; the n rows use dghn = dgi_n * r
-        _wgrad(dgi2d, d * G3, 2 * H, 2 * G3, hprev2d, d * H, H, 2 * H, g_whh, 0, H, M, amax)
-        _wgrad(dghn2d, d * H, H, 2 * H, hprev2d, d * H, H, 2 * H, g_whh, 2 * H * H, H, M, amax)
-        ops.colsum(dgi2d[:, d * G3:d * G3 + 2 * H], g_bhh[:2 * H])
-        ops.colsum(dghn2d[:, d * H:(d + 1) * H], g_bhh[2 * H:])
     if want_dinput is not None:
         col0, ncols = want_dinput
         dinput = torch.empty(M, ncols, device=dgi.device, dtype=torch.float32)
@@ -70,6 +74,32 @@ def _gru_layer_backward(layer: int, dseq, seq_out, gates, lengths, B, T, inputs,
                 ops.gemm_tcx(dgi2d, W, dinput, M, ncols, G3, a_amax=amax, **kw)
             else:
                 ops.sgemm(dgi2d, W, dinput, M, ncols, G3, **kw)
+
+    def weight_grads():
+        for d, sfx in ((0, ""), (1, "_reverse")):
+            g_wih, g_whh = grads[f"gru.weight_ih_l{layer}{sfx}"], grads[f"gru.weight_hh_l{layer}{sfx}"]
+            g_bih, g_bhh = grads[f"gru.bias_ih_l{layer}{sfx}"], grads[f"gru.bias_hh_l{layer}{sfx}"]
+            width = g_wih.shape[1]
+            for x2d, col0 in inputs:
+                _wgrad(dgi2d, d * G3, G3, 2 * G3, x2d, 0, x2d.shape[1], x2d.stride(0), g_wih, col0, width, M, amax)
+            ops.colsum(dgi2d[:, d * G3:(d + 1) * G3], g_bih)
+            # hidden projection: r,z rows share dgi; the n rows use dghn = dgi_n * r
+            _wgrad(dgi2d, d * G3, 2 * H, 2 * G3, hprev2d, d * H, H, 2 * H, g_whh, 0, H, M, amax)
+            _wgrad(dghn2d, d * H, H, 2 * H, hprev2d, d * H, H, 2 * H, g_whh, 2 * H * H, H, M, amax)
+            ops.colsum(dgi2d[:, d * G3:d * G3 + 2 * H], g_bhh[:2 * H])
+            ops.colsum(dghn2d[:, d * H:(d + 1) * H], g_bhh[2 * H:])
+
+    if side is None:
+        weight_grads()
+    else:
+        ready = torch.cuda.Event()
+        ready.record()                               # BPTT outputs, amax and everything enqueued before them
+        with torch.cuda.stream(side):
+            side.wait_event(ready)
+            weight_grads()
+        for t in (dgi, dghn, hprev, amax):           # freed on return, still being read on the side stream
+            if t is not None:
+                t.record_stream(side)
     return dinput
 
 
@@ -94,8 +124,9 @@ def backward_impl(model, ctx: Dict, grads: Dict[str, torch.Tensor], dlogits: Opt
                               grads["pool.score.bias"])
     # layer 1
     M = B * T
+    side = _side_stream(dhid.device) if _passes(model)[1] != 0 else None
     dseq0 = _gru_layer_backward(1, dseq1, ctx["seq1"], ctx["gates1"], lengths, B, T,
-                                [(ctx["seq0_in"].view(M, 2 * H), 0)], model, grads, want_dinput=(0, 2 * H))
+                                [(ctx["seq0_in"].view(M, 2 * H), 0)], model, grads, want_dinput=(0, 2 * H), side=side)
     if ctx["gru_p"] > 0:
         ops.dropout(dseq0, ctx["gru_p"], ctx["drop_seed"], out=dseq0)      # same mask, same 1/(1-p)
     # layer 0
@@ -106,12 +137,14 @@ def backward_impl(model, ctx: Dict, grads: Dict[str, torch.Tensor], dlogits: Opt
     if emb is not None:
         inputs.append((emb.view(M, -1), x_dim))
     d_emb = _gru_layer_backward(0, dseq0.view(B, T, 2 * H), ctx["seq0"], ctx["gates0"], lengths, B, T, inputs, model,
-                                grads, want_dinput=(x_dim, emb.shape[-1]) if emb is not None else None)
+                                grads, want_dinput=(x_dim, emb.shape[-1]) if emb is not None else None, side=side)
     if emb is not None:
         names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
                  "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
         ops.roi_cnn_bwd(ctx["R"], lengths, model.roi_cnn.tensors(), model.standardize_roi, d_emb.view(B, T, -1), 0,
                         [grads[n] for n in names], saved=ctx.get("cnn_saved"))
+    if side is not None:
+        torch.cuda.current_stream().wait_stream(side)      # all gradients complete before anything that follows
 
 
 class ClassifierFn(torch.autograd.Function):

@@ -338,4 +338,6 @@ def test_host_batch_prefetcher_feeds_identical_steps():
             for h in host:
                 out.append(tr.step(*(t.to(dev) for t in h)).mean().item())
         losses.append(out)
-    assert losses[0] == losses[1]
+    # identical data, identical arithmetic; split-K atomics (and the side-stream weight-gradient GEMMs) only reorder fp32 sums
+    assert losses[0][0] == losses[1][0]
+    assert max(abs(a - b) for a, b in zip(*losses)) < 2e-5, losses
