@@ -151,7 +151,8 @@ class BiGRUClassifier(nn.Module):
     def infer_host(self, X: torch.Tensor, lengths: torch.Tensor, R: Optional[torch.Tensor] = None,
                    chunk: int = 512, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """``model(X, lengths, R)`` for HOST tensors (what collate_fn, train_model_official.py:174-204, yields):
-        the batch is cut into chunks of ``chunk`` clips (clips are independent), each chunk's host->device copy
+        the batch is cut into chunks of at most ``chunk`` clips (clips are independent; the first and last two chunks are
+        smaller, see the schedule below), each chunk's host->device copy
         runs on a copy stream while the previous chunk computes, and the logits come back into a host tensor.
         Pinned inputs give true overlap; pageable ones still work (the copies then serialise).  Returns f32 [B,C]
         on the host.  The PCIe copy of R (414,720 B/clip) is the floor of this call."""
@@ -179,9 +180,20 @@ class BiGRUClassifier(nn.Module):
         was_training = self.training
         self.eval()
         copy.wait_stream(main)
-        for i, lo in enumerate(range(0, B, chunk)):
-            hi = min(B, lo + chunk)
-            n = hi - lo
+        # chunk schedule: the copy engine is the bottleneck, so the first chunk (whose copy nothing overlaps) and the last one
+        # (whose compute nothing overlaps) are small -- chunk/4, chunk/2, chunk, ..., chunk, chunk/2, chunk/4
+        sizes, left = [], B
+        head = [max(1, chunk // 4), max(1, chunk // 2)] if B >= 4 * chunk else []
+        for h in head:
+            sizes.append(h); left -= h
+        tail = list(reversed(head))
+        left -= sum(tail)
+        while left > 0:
+            sizes.append(min(chunk, left)); left -= sizes[-1]
+        sizes += tail
+        lo = 0
+        for i, n in enumerate(sizes):
+            hi = lo + n
             b = bufs[i & 1]
             with torch.cuda.stream(copy):
                 if i >= 2:
@@ -195,6 +207,7 @@ class BiGRUClassifier(nn.Module):
             logits = F_ssb.classifier_forward(self, b["X"][:n], b["L"][:n], b["R"][:n] if use_roi else None)
             out[lo:hi].copy_(logits, non_blocking=True)
             b["free"].record(main)
+            lo = hi
         if was_training:
             self.train()
         main.synchronize()

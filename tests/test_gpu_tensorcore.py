@@ -235,3 +235,28 @@ def test_proj_gemm_vs_fp64(M, n_each, K1, K2, T):
         h = C3.cpu()
         assert torch.all(h[:, N:] == -7.0) and torch.all(h[~live][:, :N] == -7.0)
         assert torch.equal(h[live][:, :N], C2.cpu()[live].half())
+
+
+@pytest.mark.parametrize("use_roi,B,chunk,pinned", [(True, 70, 16, True), (True, 37, 512, False), (False, 90, 8, True)])
+def test_infer_host_matches_device_forward(use_roi, B, chunk, pinned):
+    """The host-buffer entry (bench.py's e2e arm): chunked, copy/compute-overlapped inference from host tensors returns
+    exactly what one device-resident forward call returns -- ramped chunk schedule, ragged last chunk, pageable inputs."""
+    dev = _cuda()
+    from oracle import ref_model
+    from silent_speech_b200 import BiGRUClassifier, synth
+    p = ref_model.synth_params(3, use_roi=use_roi)
+    d = synth.clip_batch(B, 20, mode="uniform", seed=4, use_roi=use_roi)
+    X, L = torch.from_numpy(d["X"]), torch.from_numpy(d["lengths"])
+    R = torch.from_numpy(d["R"]) if use_roi else None
+    if pinned:
+        X, L, R = X.pin_memory(), L.pin_memory(), None if R is None else R.pin_memory()
+    m = BiGRUClassifier(180, 10, use_roi=use_roi, precision="tc3")
+    m.load_state_dict(p)
+    m = m.to(dev).eval()
+    with torch.no_grad():
+        want = m(X.to(dev), L.to(dev), None if R is None else R.to(dev)).cpu()
+    got = m.infer_host(X, L, R, chunk=chunk)
+    assert got.shape == (B, 10) and not got.is_cuda
+    # a clip's logits do not depend on which other clips share its launch (tile-local arithmetic, fixed-order sums)
+    assert torch.equal(got, want)
+    assert torch.equal(m.infer_host(X, L, R, chunk=chunk), got)          # buffers are reused across calls
