@@ -1,3 +1,7 @@
+"""Write-only / copy / read-only HBM bandwidth at the projection GEMM's output size (torch fill, copy, sum), to tell
+whether a write-dominated kernel can be HBM-bound below the copy figure in MEASURED_PEAKS.json.  B200: fill 7.5 TB/s,
+copy 6.5 TB/s, read 5.9 TB/s ("What the profile says about K3a").
+    python tools/hbm_probe.py"""
 import torch
 dev=torch.device('cuda')
 def t(fn, n=10):
