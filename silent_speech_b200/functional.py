@@ -126,6 +126,9 @@ def classifier_forward(model, X, lengths, R=None, k_top: int = 0):
     if not X.is_cuda:
         raise ops._lib.SsbError("inputs must be CUDA tensors: this package has no CPU path")
     needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in model.parameters())
+    if X.shape[0] == 0 and not k_top:          # empty batch: nothing to launch (the reference returns a [0, C] tensor too)
+        z = torch.zeros(0, model.num_classes, device=X.device, dtype=torch.float32)
+        return z + sum(p.sum() * 0 for p in model.parameters()) if needs_grad else z
     if k_top or not needs_grad:
         with torch.no_grad():
             out, _ = forward_impl(model, X, lengths, R, training=model.training and needs_grad, save=False, k_top=k_top)

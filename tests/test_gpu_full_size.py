@@ -82,3 +82,39 @@ def test_train_gradients_are_additive_over_a_partition_of_128_clips():
     assert torch.allclose(torch.cat(losses), loss_full, rtol=0, atol=1e-6)
     scale = float(g_full.abs().max())
     assert float((g_sum - g_full).abs().max()) < 1e-5 * scale
+
+
+# --------------------------------------------------------------------------------------------- edges of the domain
+@pytest.mark.parametrize("precision,tol", [("tc3", 1e-4), ("fp16", 1e-3), ("fp32", 1e-4)])
+@pytest.mark.parametrize("B,T,lens", [(1, 1, [1]), (3, 90, [1, 90, 2]), (5, 7, [1, 1, 1, 1, 1]), (2, 256, [256, 6])])
+def test_shortest_and_longest_clips(precision, tol, B, T, lens):
+    """One-frame clips (pack_padded_sequence's minimum, train_model_official.py:301), a one-clip batch, T = 1, and the
+    T = 256 stress length of configs[3], against the oracle."""
+    from silent_speech_b200 import synth
+    dev = _cuda()
+    p = ref_model.synth_params(13)
+    d = synth.clip_batch(B, T, mode="full", seed=3)
+    X, R = torch.from_numpy(d["X"]), torch.from_numpy(d["R"])
+    L = torch.tensor(lens, dtype=torch.int64)
+    for b in range(B):
+        X[b, lens[b]:] = 0; R[b, lens[b]:] = 0
+    with torch.no_grad():
+        ref = ref_model.forward(p, X, L, R)
+    m = _model(p, dev, precision)
+    with torch.no_grad():
+        out = m(X.to(dev), L.to(dev), R.to(dev)).cpu()
+    assert torch.isfinite(out).all()
+    assert float((out - ref).abs().max() / ref.abs().max()) < tol
+    assert torch.equal(out.argmax(1), ref.argmax(1))
+
+
+def test_empty_batch_returns_empty_logits():
+    dev = _cuda()
+    m = _model(ref_model.synth_params(13), dev, "tc3")
+    X = torch.zeros(0, 90, 180, device=dev)
+    L = torch.zeros(0, dtype=torch.int64, device=dev)
+    R = torch.zeros(0, 90, 48, 96, dtype=torch.uint8, device=dev)
+    with torch.no_grad():
+        out = m(X, L, R)
+    assert out.shape == (0, 10)
+    assert m.infer_host(X.cpu(), L.cpu(), R.cpu()).shape == (0, 10)
