@@ -502,6 +502,36 @@ def main():
                 "note": "K2 (fused ROI CNN), algorithmic 5,309,952 FLOP/frame; step-level: %.1f TFLOP/s over %.0f MFLOP/clip" % (
                     FWD_FLOP_PER_FRAME * frames * world * args.steps / (ms / 1e3) / 1e12, FWD_FLOP_PER_FRAME * T_FRAMES / 1e6)}
 
+    if args.workload == "train" and cnn_passes == 3:
+        # The train step's dominant kernel is the ROI CNN BACKWARD (fp32 CUDA cores, fed by the forward's saved
+        # activations): time it alone on the saved records of one forward call and report it against the same tensor
+        # peak -- it does not use the tensor cores, which is exactly what the fraction says.  Algorithmic work = the two
+        # gradients of every convolution = 2 x the forward's FLOPs.
+        names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
+                 "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
+        sd = dict(model.named_parameters())
+        gbuf = [torch.zeros_like(sd[n]) for n in names]
+        saved = ops.roi_cnn_saved(B, T_FRAMES, dev)
+        ops.roi_cnn_fwd(R, L, w, passes=3, saved=saved)
+        d_emb = torch.randn(B, T_FRAMES, 32, device=dev) * 1e-3
+        for _ in range(2):
+            ops.roi_cnn_bwd(R, L, w, True, d_emb, 0, gbuf, saved=saved)
+        torch.cuda.synchronize()
+        k0.record()
+        for _ in range(5):
+            ops.roi_cnn_bwd(R, L, w, True, d_emb, 0, gbuf, saved=saved)
+        k1.record()
+        torch.cuda.synchronize()
+        bwd_ms = k0.elapsed_time(k1) / 5
+        ach = 2 * CNN_FLOP_PER_FRAME * frames / (bwd_ms / 1e3) / 1e12
+        fma_peak = 148 * 128 * 2 * 1.965e9 / 1e12            # fp32 FMA lanes x 2 FLOP x SM clock
+        roofline = {"kernel": "roi_cnn_bwd_kernel", "bound": "tensor", "achieved": ach, "peak": peaks["tensor_burst"],
+                    "unit": "TFLOP/s", "frac": ach / peaks["tensor_burst"], "traffic": None,
+                    "peak_src": f"{peaks['src']} bf16 burst", "ms_per_launch": bwd_ms,
+                    "note": "K2-bwd (fp32 CUDA cores, forward activations saved by the split-mode K2): algorithmic 2 x 5,309,952 "
+                            "FLOP/frame; %.0f %% of the fp32 FMA peak (%.1f TFLOP/s); the forward K2 in this step: %.3f ms = "
+                            "%.1f TFLOP/s" % (100 * ach / fma_peak, fma_peak, cnn_ms, achieved)}
+
     # ---- the same batch in the fp32-parity mode (tc3), reported beside the fp16 headline
     parity_mode = None
     if args.workload == "infer" and args.precision == "fp16":
