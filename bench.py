@@ -1,14 +1,28 @@
 #!/usr/bin/env python
-"""Benchmark of the Silent-Speech clip-classification hot path on B200 (contract in DESIGN.md).
+"""Benchmark of the Silent-Speech clip-classification hot path on B200 (contract in DESIGN.md section 5).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload infer|train]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload all|infer|train|...]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-A step = one pass of the hot path over one batch of synthetic clips of the reference's shape
-(T=90 frames, 180 point features, 48x96 u8 mouth ROI; train_model_official.py:34,38).  Workload at
-N=1: BASELINE.json configs[1] -- batched inference of the points+ROI model, 4096 clips per GPU,
-weak scaling (clips are independent: each rank gets its own 4096, no data-path collective).
-One JSON line is printed by rank 0.
+A step = one pass of the hot path over one batch of synthetic clips of the reference's shape (T = 90 frames, 180
+point features, 48x96 u8 mouth ROI; train_model_official.py:34,38).  BASELINE.json's metric has two halves and the
+default run measures both, at every N, in ONE JSON line printed by rank 0:
+
+  top level   configs[1]: batched inference of the points+ROI model, 4096 clips per GPU, in the fp32-parity
+              precision (tc3: fp16 hi/lo split operands x3, fp32 accumulation; logits within 1e-4 of the CPU reference)
+              -- `value` (inputs resident in HBM), `e2e` (pinned host buffers in, host logits out), `roofline` (K2)
+  fp16_mode   the same batch in the single-pass fp16 mode (stated tolerance 1e-3) with its own value / e2e / roofline and,
+              at N = 1, its measured logit error and argmax agreement against the CPU reference
+  train_step  configs[2]: full train step (forward, CE, backward, NCCL all-reduce of the flat gradient bucket, joint clip,
+              Adam) on 128 clips per GPU, with the all-reduce's own CUDA-event time, e2e and the CPU train baseline
+  dp_check    replicas identical after the timed steps; all-reduced gradients == one rank's full-batch gradients
+  points256   configs[3]: landmarks-only model, T = 256
+  stream      configs[4]: sliding-window streams, 1,250 per GPU
+  features    K1 (landmark feature kernel) against the HBM roofline
+  e2e.h2d_*   plain pinned host->device copy rate of the box, all ranks copying at once
+
+Weak scaling: clips / streams are independent, every rank gets its own batch; the only data-path collective is the
+train step's gradient all-reduce.
 """
 from __future__ import annotations
 
@@ -30,6 +44,13 @@ T_FRAMES, X_DIM, NUM_CLASSES = 90, 180, 10
 CNN_FLOP_PER_FRAME = 5_309_952
 GRU_FLOP_PER_FRAME = 2_257_920
 FWD_FLOP_PER_FRAME = CNN_FLOP_PER_FRAME + GRU_FLOP_PER_FRAME
+FEAT_BYTES_ALGO = 88 * 8 + 720          # 1,424 B/frame: 88 (x, y) pairs read + the 180-float row written
+FEAT_BYTES_ROWS = 478 * 12 + 720        # 6,456 B/frame when whole 5,736-byte landmark rows are streamed
+CPU_CHUNK = 64                          # clips per CPU-arm step (a bounded sample of the 4096-clip batch)
+DTYPE = {"fp32": "f32", "tc3": "f16 hi/lo split operands x3, f32 accumulate (f32-parity grade: logits within 1e-4 of the f32 CPU reference)",
+         "fp16": "f16 operands, f32 accumulate (stated tolerance 1e-3)"}
+K2_NAME = {0: "roi_cnn_fwd_kernel", 1: "roi_cnn_tc3_kernel<split=false>", 3: "roi_cnn_tc3_kernel<split=true>"}
+PASSES = {"fp32": 0, "tc3": 3, "fp16": 1}
 
 
 def env_int(name, default):
@@ -45,14 +66,14 @@ def load_peaks():
     return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor_sustained": 1400.0, "src": "fallback"}
 
 
-def ncu_traffic(precision, B, lengths):
-    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed `ncu --set full`
-    capture of this same launch shape (profiles/roofline_traffic.json); None when no capture matches."""
+def ncu_traffic(kernel_key, clips, lengths):
+    """dram__bytes_read.sum + dram__bytes_write.sum of a kernel from the committed `ncu --set full` capture of the same
+    launch shape (profiles/roofline_traffic.json); None when no capture matches."""
     path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if not os.path.exists(path):
         return None
     for e in json.load(open(path)):
-        if e["precision"] == precision and e["clips"] == B and e["lengths"] == lengths:
+        if e.get("precision") == kernel_key and e.get("clips") == clips and e.get("lengths") == lengths:
             return {"bytes_per_launch": e["dram_bytes"], "algorithmic_bytes": e["algorithmic_bytes"], "source": e["source"]}
     return None
 
@@ -76,6 +97,7 @@ class ClockSampler:
             self._stop.wait(0.15)
 
     def __enter__(self):
+        self._stop.clear()
         self._t = threading.Thread(target=self._run, daemon=True)
         self._t.start()
         return self
@@ -105,230 +127,445 @@ def make_batch(B, T, mode, use_roi=True, unique=64, seed=42):
     return out
 
 
-def cpu_reference_rate(workload, threads, budget_s=12.0, B=64):
-    """The reference's CPU path (oracle port = same ATen call sites) on a bounded sample."""
+def lengths_name(mode):
+    return "all=T" if mode == "full" else "uniform[6,T]"
+
+
+def infer_config(B, lengths_mode, precision):
+    return {"workload": "configs[1]: batched inference word_model_points_roi", "clips_per_gpu": B, "frames": T_FRAMES,
+            "lengths": lengths_name(lengths_mode), "l2": "inputs (1.96 GB/step) larger than L2", "precision": precision}
+
+
+def train_config(B, lengths_mode):
+    return {"workload": "configs[2]: full train step (fwd + bwd + all-reduce + clip + Adam), points+ROI model",
+            "clips_per_gpu": B, "frames": T_FRAMES, "lengths": lengths_name(lengths_mode), "precision": "tc3",
+            "l2": "inputs (61 MB/step) + saved activations (0.7 GB/step) larger than L2"}
+
+
+# ======================================================================================================== CPU arm
+def cpu_arm(workload, threads, steps, warmup, lengths_mode, budget_s=None, want_logits=False):
+    """The reference's CPU path (oracle port: the same ATen call sites as train_model_official.py, pinned bit-identical to
+    the imported reference by tests/test_oracle_golden.py) over a BOUNDED sample of the GPU arm's batch: step i processes
+    clips [64 i, 64 i + 64) of the same seeded 4096-clip (infer) / 128-clip (train) batch.  Returns (clips/s, ms/step,
+    sample description, logits of the first chunk or None)."""
     from oracle import ref_model
     torch.set_num_threads(threads)
     p = ref_model.synth_params(42)
-    d = make_batch(B, T_FRAMES, "full", unique=B)
-    X, L, R, y = (torch.from_numpy(d["X"]), torch.from_numpy(d["lengths"]), torch.from_numpy(d["R"]),
-                  torch.from_numpy(d["y"]))
-    times = []
-    if workload == "train":
-        st = ref_model.AdamState(p)
-        fn = lambda: st.step(X, L, R, y, training=True)
-    else:
-        def fn():
+    Bfull = 4096 if workload == "infer" else 128
+    d = make_batch(Bfull, T_FRAMES, lengths_mode, seed=42)
+    chunks = Bfull // CPU_CHUNK
+
+    def chunk(i):
+        lo = (i % chunks) * CPU_CHUNK
+        return tuple(torch.from_numpy(d[k][lo:lo + CPU_CHUNK]) for k in ("X", "lengths", "R", "y"))
+    st = ref_model.AdamState(p) if workload == "train" else None
+    first = None
+
+    def run(i):
+        nonlocal first
+        X, L, R, y = chunk(i)
+        if workload == "train":
+            st.step(X, L, R, y, training=True)
+        else:
             with torch.no_grad():
-                ref_model.forward(p, X, L, R)
-    fn()                                  # warm-up
-    t_end = time.perf_counter() + budget_s
-    while len(times) < 3 or (time.perf_counter() < t_end and len(times) < 10):
-        t0 = time.perf_counter(); fn(); times.append(time.perf_counter() - t0)
-    return B / min(times), f"B={B} clips x T={T_FRAMES}, full lengths, best of {len(times)}"
+                out = ref_model.forward(p, X, L, R)
+            if i == 0 and first is None:
+                first = out
+    for i in range(warmup):
+        run(i)
+    t_end = None if budget_s is None else time.perf_counter() + budget_s
+    times = []
+    for i in range(steps):
+        t0 = time.perf_counter(); run(warmup + i); times.append(time.perf_counter() - t0)
+        if t_end is not None and len(times) >= 3 and time.perf_counter() > t_end:
+            break
+    dt = sum(times)
+    sample = (f"each step = one {CPU_CHUNK}-clip chunk of the same seeded {Bfull}-clip batch (T={T_FRAMES}, {lengths_name(lengths_mode)}), "
+              f"{len(times)} steps, {threads} threads")
+    return CPU_CHUNK * len(times) / dt, 1e3 * dt / len(times), sample, (first if want_logits else None)
 
 
 def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU implementation of the path on the box's host cores (rank 0 only)."""
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    from oracle import ref_model
-    torch.set_num_threads(threads)
-    B = 64
-    p = ref_model.synth_params(42)
-    d = make_batch(B, T_FRAMES, "full", unique=B)
-    X, L, R, y = (torch.from_numpy(d["X"]), torch.from_numpy(d["lengths"]), torch.from_numpy(d["R"]),
-                  torch.from_numpy(d["y"]))
-    if args.workload == "train":
-        st = ref_model.AdamState(p)
-        step = lambda: st.step(X, L, R, y, training=True)
-    else:
-        def step():
-            with torch.no_grad():
-                ref_model.forward(p, X, L, R)
-    for _ in range(args.warmup):
-        step()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step()
-    dt = time.perf_counter() - t0
-    val = B * args.steps / dt
-    sample = f"each step = {B} clips x T={T_FRAMES} (bounded sample of the 4096-clip batch), {threads} threads"
-    line = {"impl": "reference", "metric": metric_name(args.workload), "value": val, "unit": "clips/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args.workload, B),
+    val, ms, sample, _ = cpu_arm("infer", threads, args.steps, args.warmup, args.lengths)
+    line = {"impl": "reference", "metric": "inference_clips_per_sec", "value": val, "unit": "clips/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": infer_config(4096, args.lengths, "tc3"),
             "cpu_baseline": {"value": val, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if args.workload in ("all", "train"):
+        n_tr = max(3, min(args.steps, 6))
+        tv, tms, tsample, _ = cpu_arm("train", threads, n_tr, 1, args.lengths)
+        line["train_step"] = {"metric": "train_step_samples_per_sec", "value": tv, "unit": "samples/s", "ms_per_step": tms,
+                              "config": train_config(128, args.lengths),
+                              "cpu_baseline": {"value": tv, "unit": "samples/s", "cores": threads, "kind": "port", "sample": tsample}}
     print(json.dumps(line), flush=True)
 
 
-def run_extra(args, rank, world, local):
-    """configs[3] (landmarks-only GRU stress, T=256) and configs[4] (sliding-window streams).  Same JSON contract;
-    the roofline entry is the projection GEMM (HBM-bound: A read + gi write) for points256 and the whole tick for stream."""
-    import torch.distributed as dist
-    dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
-    affinity = bind_near_gpu(dev) if world > 1 else None
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-    from silent_speech_b200 import BiGRUClassifier, _lib as ssb_lib, ops, synth
-    from oracle import ref_model
-    peaks = load_peaks()
+# ======================================================================================================== GPU arm
+class Ctx:
+    """Per-process state of the GPU arm: device, distributed helpers, peaks."""
 
-    def barrier():
+    def __init__(self, args, rank, world, local):
+        import torch.distributed as dist
+        self.args, self.rank, self.world, self.local, self.dist = args, rank, world, local, dist
+        self.dev = torch.device("cuda", local)
+        torch.cuda.set_device(self.dev)
+        self.affinity = bind_near_gpu(self.dev) if world > 1 else None
         if world > 1:
-            dist.barrier()
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.peaks = load_peaks()
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
         torch.cuda.synchronize()
 
-    def max_over_ranks(ms):
-        t = torch.tensor([ms], device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    def max_over_ranks(self, v):
+        t = torch.tensor([float(v)], device=self.dev, dtype=torch.float64)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return float(t.item())
 
-    if args.workload == "points256":
-        T, B = 256, args.batch or 4096
-        p = ref_model.synth_params(42, use_roi=False)
-        model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=False, precision=args.precision)
-        model.load_state_dict(p)
-        model = model.to(dev).eval()
-        d = make_batch(B, T, args.lengths, use_roi=False, seed=42 + rank)
-        hX, hL = torch.from_numpy(d["X"]).pin_memory(), torch.from_numpy(d["lengths"]).pin_memory()
-        X, L = hX.to(dev), hL.to(dev)
-        frames = int(d["lengths"].sum())
+    def min_over_ranks(self, v):
+        return -self.max_over_ranks(-float(v))
+
+    def sum_over_ranks(self, v):
+        t = torch.tensor([float(v)], device=self.dev, dtype=torch.float64)
+        if self.world > 1:
+            self.dist.all_reduce(t)
+        return float(t.item())
+
+    def timed(self, fn, steps, warmup, clk=None):
+        """warmup untimed calls, then `steps` calls between two CUDA events on the current stream, a barrier +
+        synchronize on both sides; -> (ms for all steps, max over ranks; C-ABI launches of this rank)."""
+        from silent_speech_b200 import _lib as ssb_lib
+        for _ in range(warmup):
+            fn()
+        self.barrier()
+        c0 = ssb_lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if clk is not None:
+            clk.__enter__()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        self.barrier()
+        if clk is not None:
+            clk.__exit__()
+        return self.max_over_ranks(e0.elapsed_time(e1)), ssb_lib.launch_count() - c0
+
+    def kernel_ms(self, fn, reps=5):
+        """One kernel timed alone (this rank): 2 warm-up launches, `reps` launches between CUDA events."""
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        k0.record()
+        for _ in range(reps):
+            fn()
+        k1.record()
+        torch.cuda.synchronize()
+        return k0.elapsed_time(k1) / reps
+
+
+def h2d_probe(cx, mb=256, reps=4):
+    """Plain pinned host -> device copy rate: `reps` cudaMemcpyAsync of `mb` MiB each (one call per copy), all ranks
+    copying at the same time.  -> GB/s per GPU (slowest rank)."""
+    n = mb << 20
+    h = torch.empty(n, dtype=torch.uint8).pin_memory()
+    h.fill_(1)
+    d = torch.empty(n, dtype=torch.uint8, device=cx.dev)
+    d.copy_(h, non_blocking=True)
+    cx.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        d.copy_(h, non_blocking=True)
+    e1.record()
+    cx.barrier()
+    ms = cx.max_over_ranks(e0.elapsed_time(e1))
+    del h, d
+    return reps * n / ms / 1e6
+
+
+def infer_block(cx, model, precision, dev_batch, host_batch, frames, steps, warmup, clk=None, h2d_gbs=None):
+    """configs[1] in one precision: device-resident value, e2e through model.infer_host, K2 roofline."""
+    from silent_speech_b200 import ops
+    args, world = cx.args, cx.world
+    X, L, R = dev_batch
+    hX, hL, hR = host_batch
+    B = X.shape[0]
+    model.precision = precision
+    model.eval()
+
+    def step():
+        with torch.no_grad():
+            return model(X, L, R)
+    ms, launches = cx.timed(step, steps, warmup, clk)
+    value = B * world * steps / (ms / 1e3)
+
+    h_out = torch.empty(B, NUM_CLASSES, dtype=torch.float32).pin_memory()
+    n_e2e = max(2, min(steps, 5))
+    e2e_ms, _ = cx.timed(lambda: model.infer_host(hX, hL, hR, chunk=args.e2e_chunk, out=h_out), n_e2e, 1, clk)
+    e2e_val = B * world * n_e2e / (e2e_ms / 1e3)
+    h2d = hX.numel() * 4 + hL.numel() * 8 + hR.numel()
+    e2e = {"value": e2e_val, "unit": "clips/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(h_out.numel() * 4),
+           "ms_per_step": e2e_ms / n_e2e}
+    if h2d_gbs:
+        e2e["h2d_peak_gbs"] = h2d_gbs
+        e2e["frac_of_h2d"] = (h2d * n_e2e / (e2e_ms / 1e3) / 1e9) / h2d_gbs
+        e2e["note"] = ("PCIe-bound: h2d_peak_gbs = plain pinned cudaMemcpyAsync rate per GPU with all ranks copying at once; "
+                       "frac_of_h2d = this arm's input bytes/s per GPU over that rate")
+
+    passes = PASSES[precision]
+    w = model.roi_cnn.tensors()
+    cnn_ms = cx.kernel_ms(lambda: ops.roi_cnn_fwd(R, L, w, passes=passes))
+    achieved = CNN_FLOP_PER_FRAME * frames / (cnn_ms / 1e3) / 1e12
+    peaks = cx.peaks
+    roofline = {"kernel": K2_NAME[passes], "bound": "tensor", "achieved": achieved, "peak": peaks["tensor_burst"],
+                "unit": "TFLOP/s", "frac": achieved / peaks["tensor_burst"],
+                "traffic": ncu_traffic(precision, B, args.lengths),
+                "peak_src": f"{peaks['src']} bf16 burst (kernel timed alone)", "ms_per_launch": cnn_ms,
+                "note": "K2 (fused ROI CNN), algorithmic 5,309,952 FLOP/frame x %d frames; step-level: %.1f TFLOP/s over %.0f MFLOP/clip" % (
+                    frames, FWD_FLOP_PER_FRAME * frames * world * steps / (ms / 1e3) / 1e12, FWD_FLOP_PER_FRAME * T_FRAMES / 1e6)}
+    return {"value": value, "unit": "clips/s", "ms_per_step": ms / steps, "e2e": e2e, "gpu_launches": launches,
+            "roofline": roofline, "dtype": DTYPE[precision]}
+
+
+def train_block(cx, steps, warmup, want_cpu):
+    """configs[2]: Trainer.step (forward, fused CE, backward, NCCL all-reduce of the flat bucket, clip + Adam) on 128
+    clips per GPU in the fp32-parity precision, dropout on (throughput mode); + dp_check."""
+    from silent_speech_b200 import BiGRUClassifier, ops, synth
+    from silent_speech_b200.train import HostBatchPrefetcher, Trainer
+    args, world, rank, dev = cx.args, cx.world, cx.rank, cx.dev
+    B = args.train_batch
+    model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=True, precision="tc3")
+    model.load_state_dict(synth.synth_params(42))
+    model = model.to(dev).train()
+    d = make_batch(B, T_FRAMES, args.lengths, seed=1042 + rank)
+    hX = torch.from_numpy(d["X"]).pin_memory(); hL = torch.from_numpy(d["lengths"]).pin_memory()
+    hR = torch.from_numpy(d["R"]).pin_memory(); hy = torch.from_numpy(d["y"]).pin_memory()
+    X, L, R, y = hX.to(dev), hL.to(dev), hR.to(dev), hy.to(dev)
+    frames = int(d["lengths"].sum())
+    trainer = Trainer(model, lr=3e-4, world_size=world)
+    clk = ClockSampler(cx.local)
+    trainer.allreduce_events = None
+    for _ in range(warmup):
+        trainer.step(X, L, R, y)
+    trainer.allreduce_events = [] if world > 1 else None
+    ms, launches = cx.timed(lambda: trainer.step(X, L, R, y), steps, 0, clk)
+    value = B * world * steps / (ms / 1e3)
+    ar_ms = None
+    if world > 1 and trainer.allreduce_events:
+        torch.cuda.synchronize()
+        ar = [a.elapsed_time(b) for a, b in trainer.allreduce_events]
+        ar_ms = {"mean": cx.max_over_ranks(float(np.mean(ar))), "min": cx.min_over_ranks(float(np.min(ar))),
+                 "bytes": int(trainer.buckets.grad.numel() * 4),
+                 "note": "CUDA events around dist.all_reduce on the compute stream (includes waiting for the slowest rank's backward)"}
+    trainer.allreduce_events = None
+
+    # e2e: batches staged from pinned host memory by HostBatchPrefetcher (copy of batch i+1 during step i), loss read back
+    prefetch = HostBatchPrefetcher(dev)
+    prefetch.submit(hX, hL, hR, hy)
+
+    def e2e_step():
+        Xd, Ld, Rd, yd = prefetch.get()
+        prefetch.submit(hX, hL, hR, hy)
+        return trainer.step(Xd, Ld, Rd, yd).cpu()
+    n_e2e = max(2, min(steps, 5))
+    e2e_ms, _ = cx.timed(e2e_step, n_e2e, 1, clk)
+    prefetch.get()
+    h2d = hX.numel() * 4 + hL.numel() * 8 + hR.numel() + hy.numel() * 8
+    e2e = {"value": B * world * n_e2e / (e2e_ms / 1e3), "unit": "samples/s", "h2d_bytes_per_step": int(h2d),
+           "d2h_bytes_per_step": int(B * 4), "ms_per_step": e2e_ms / n_e2e}
+
+    # dominant kernel of the step timed alone on the saved records of one forward call: the ROI-CNN backward
+    w = model.roi_cnn.tensors()
+    names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
+             "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
+    sd = dict(model.named_parameters())
+    gbuf = [torch.zeros_like(sd[n]) for n in names]
+    saved = ops.roi_cnn_saved(B, T_FRAMES, dev)
+    ops.roi_cnn_fwd(R, L, w, passes=3, saved=saved)
+    d_emb = torch.randn(B, T_FRAMES, 32, device=dev) * 1e-3
+    bwd_ms = cx.kernel_ms(lambda: ops.roi_cnn_bwd(R, L, w, True, d_emb, 0, gbuf, saved=saved))
+    fwd_ms = cx.kernel_ms(lambda: ops.roi_cnn_fwd(R, L, w, passes=3, saved=saved))
+    ach = 2 * CNN_FLOP_PER_FRAME * frames / (bwd_ms / 1e3) / 1e12
+    peaks = cx.peaks
+    roofline = {"kernel": "roi_cnn_bwd_kernel", "bound": "tensor", "achieved": ach, "peak": peaks["tensor_burst"],
+                "unit": "TFLOP/s", "frac": ach / peaks["tensor_burst"], "traffic": None,
+                "peak_src": f"{peaks['src']} bf16 burst (kernel timed alone)", "ms_per_launch": bwd_ms,
+                "note": "K2-bwd: algorithmic 2 x 5,309,952 FLOP/frame x %d frames; the forward K2 of this step (with saved activations): "
+                        "%.3f ms; step-level %.1f TFLOP/s over 3 x 681 MFLOP/clip" % (
+                            frames, fwd_ms, 3 * FWD_FLOP_PER_FRAME * frames * world * steps / (ms / 1e3) / 1e12)}
+    block = {"metric": "train_step_samples_per_sec", "value": value, "unit": "samples/s", "ms_per_step": ms / steps,
+             "steps": steps, "warmup": warmup, "config": train_config(B, args.lengths) | {"global_batch": B * world, "dropout": "on"},
+             "allreduce_ms": ar_ms, "e2e": e2e, "gpu_launches": launches, "launches_per_step": trainer.launches_per_step,
+             "roofline": roofline, "clocks": clk.summary(), "dtype": DTYPE["tc3"], "cpu_baseline": None}
+
+    # ---- dp_check (a) replicas: every rank's parameter bucket equals rank 0's after the timed steps
+    dp = {"world": world}
+    if world > 1:
+        ref = trainer.buckets.param.clone()
+        cx.dist.broadcast(ref, 0)
+        dp["param_max_abs_diff_vs_rank0"] = cx.max_over_ranks(float((trainer.buckets.param - ref).abs().max()))
+        # (b) all-reduced shard gradients == one rank's full-batch gradients (dropout off, same weights everywhere)
+        m2 = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=True, precision="tc3")
+        m2.load_state_dict(synth.synth_params(43))
+        m2 = m2.to(dev).train()
+        t2 = Trainer(m2, world_size=world, dropout=False)
+        gb = B * world
+        t2.forward_backward(X, L, R, y, global_batch=gb)
+        g_dp = t2.buckets.grad.clone()
+        cx.dist.all_reduce(g_dp)
+        full = []
+        for t in (X, L, R, y):
+            parts = [torch.empty_like(t) for _ in range(world)]
+            cx.dist.all_gather(parts, t)
+            full.append(torch.cat(parts, 0))
+        t2.forward_backward(*full, global_batch=gb)
+        g_full = t2.buckets.grad
+        dp["allreduced_vs_fullbatch_grad_rel_err"] = cx.max_over_ranks(float((g_dp - g_full).abs().max() / g_full.abs().max()))
+        dp["note"] = ("param diff must be 0 (same reduced gradients, same fused update on every rank); gradient check: SUM all-reduce of "
+                      "per-shard gradients scaled by 1/B_global vs a single-rank forward_backward over the gathered %d-clip batch, "
+                      "relative to max|g| (fp32 summation order differs: <= 1e-5)" % gb)
+    else:
+        dp["note"] = "single rank: no collective on the path"
+    if want_cpu:
+        threads = os.cpu_count() or 1
+        v, cms, sample, _ = cpu_arm("train", threads, 5, 1, args.lengths, budget_s=10.0)
+        block["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample}
+    return block, dp
+
+
+def points256_block(cx, steps, warmup):
+    """configs[3]: landmarks-only BiGRU at T = 256, 4096 clips per GPU, in both precisions (value = fp32-parity mode)."""
+    from silent_speech_b200 import BiGRUClassifier, ops, synth
+    args, world, rank, dev = cx.args, cx.world, cx.rank, cx.dev
+    T, B = 256, args.points_batch
+    model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=False, precision="tc3")
+    model.load_state_dict(synth.synth_params(42, use_roi=False))
+    model = model.to(dev).eval()
+    d = make_batch(B, T, args.lengths, use_roi=False, seed=2042 + rank)
+    hX, hL = torch.from_numpy(d["X"]).pin_memory(), torch.from_numpy(d["lengths"]).pin_memory()
+    X, L = hX.to(dev), hL.to(dev)
+    frames = int(d["lengths"].sum())
+    out = {}
+    for prec in ("tc3", "fp16"):
+        model.precision = prec
 
         def step():
             with torch.no_grad():
                 return model(X, L)
-        for _ in range(args.warmup):
-            step()
-        barrier()
-        c0 = ssb_lib.launch_count()
+        ms, launches = cx.timed(step, steps, warmup)
+        out[prec] = (B * world * steps / (ms / 1e3), ms / steps, launches)
+    h_out = torch.empty(B, NUM_CLASSES, dtype=torch.float32).pin_memory()
+    model.precision = "tc3"
+    n_e2e = 2
+    e2e_ms, _ = cx.timed(lambda: model.infer_host(hX, hL, None, chunk=args.e2e_chunk, out=h_out), n_e2e, 1)
+    # dominant HBM mover of the fp16 mode: the layer-1 projection GEMM (A [M,384] read + gi [M,1152] written), timed alone
+    A1 = torch.randn(B * T, 384, device=dev)
+    packed = ops.proj_prepack(model.gru.weight_ih_l1, model.gru.weight_ih_l1_reverse, 384, 0)
+    gi = torch.empty(B * T, 1152, device=dev)
+    bias = torch.zeros(1152, device=dev)
+    kms = cx.kernel_ms(lambda: ops.proj_gemm(A1, packed, bias, gi, 1152, lengths=L, T=T), reps=3)
+    by = frames * (384 + 1152) * 4
+    peaks = cx.peaks
+    roofline = {"kernel": "proj_gemm_kernel (layer 1, fp16 mode)", "bound": "hbm", "achieved": by / kms / 1e6, "peak": peaks["hbm"],
+                "unit": "GB/s", "frac": by / kms / 1e6 / peaks["hbm"], "traffic": None, "ms_per_launch": kms,
+                "peak_src": f"{peaks['src']} copy bandwidth", "note": "algorithmic bytes = frames x (384 + 1152) x 4"}
+    return {"metric": "inference_clips_per_sec", "value": out["tc3"][0], "unit": "clips/s", "ms_per_step": out["tc3"][1],
+            "steps": steps, "warmup": warmup, "dtype": DTYPE["tc3"], "gpu_launches": out["tc3"][2],
+            "fp16_mode": {"value": out["fp16"][0], "ms_per_step": out["fp16"][1], "dtype": DTYPE["fp16"]},
+            "config": {"workload": "configs[3]: landmarks-only BiGRU (no ROI CNN), T=256", "clips_per_gpu": B, "frames": T,
+                       "lengths": lengths_name(args.lengths), "l2": "inputs (0.75 GB/step) larger than L2"},
+            "e2e": {"value": B * world * n_e2e / (e2e_ms / 1e3), "unit": "clips/s",
+                    "h2d_bytes_per_step": int(hX.numel() * 4 + hL.numel() * 8), "d2h_bytes_per_step": int(h_out.numel() * 4)},
+            "roofline": roofline}
+
+
+def stream_block(cx, steps, warmup):
+    """configs[4]: sliding-window streams (inactive/live_feed.py:155-213 policy: window 90, predict every 2nd frame after
+    10 warm-up frames), 1,250 streams per GPU; a step = two camera frames per stream = one prediction per stream.  Every
+    tick copies its frames from pinned host memory and returns the logits to the host, so `value` is end to end."""
+    from silent_speech_b200 import BiGRUClassifier, _lib as ssb_lib, synth
+    from silent_speech_b200.streaming import StreamScheduler
+    args, world, rank, dev = cx.args, cx.world, cx.rank, cx.dev
+    S, W = args.streams, T_FRAMES
+    model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=True, precision="tc3")
+    model.load_state_dict(synth.synth_params(42))
+    model = model.to(dev).eval()
+    sch = StreamScheduler(model, S, max_t=W)
+    rng = np.random.default_rng(42 + rank)
+    pool = 8                                            # distinct synthetic frames per stream, cycled
+    hX = torch.from_numpy(rng.normal(0, 0.5, (pool, S, X_DIM)).astype(np.float32)).pin_memory()
+    hR = torch.from_numpy(rng.integers(0, 256, (pool, S, 48, 96)).astype(np.uint8)).pin_memory()
+    ids = np.arange(S)
+
+    def tick(k):
+        Xd, Rd = hX[k % pool].to(dev, non_blocking=True), hR[k % pool].to(dev, non_blocking=True)
+        due, logits = sch.tick(ids, Xd, Rd)
+        return due, (None if logits is None else logits.cpu())
+    for k in range(W + 2 * warmup):                     # fill every window, then warm up
+        tick(k)
+    cx.barrier()
+    c0 = ssb_lib.launch_count()
+    lat, preds = [], 0
+    t_all0 = time.perf_counter()
+    for k in range(2 * steps):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        with ClockSampler(local) as clk:
-            e0.record()
-            for _ in range(args.steps):
-                step()
-            e1.record()
-            barrier()
-            launches = ssb_lib.launch_count() - c0
-            ms = max_over_ranks(e0.elapsed_time(e1))
-            h_out = torch.empty(B, NUM_CLASSES, dtype=torch.float32).pin_memory()
-            model.infer_host(hX, hL, None, chunk=args.e2e_chunk, out=h_out)
-            barrier()
-            e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            n_e2e = max(2, min(args.steps, 5))
-            e2.record()
-            for _ in range(n_e2e):
-                model.infer_host(hX, hL, None, chunk=args.e2e_chunk, out=h_out)
-            e3.record()
-            barrier()
-            e2e_ms = max_over_ranks(e2.elapsed_time(e3))
-        # dominant HBM mover: the layer-1 projection GEMM (A [M,384] read + gi [M,1152] written), timed alone
-        passes = {"fp32": 0, "tc3": 3, "fp16": 1}[args.precision]
-        roofline = None
-        if passes == 1:
-            A1 = torch.randn(B * T, 384, device=dev)
-            packed = ops.proj_prepack(model.gru.weight_ih_l1, model.gru.weight_ih_l1_reverse, 384, 0)
-            gi = torch.empty(B * T, 1152, device=dev)
-            bias = torch.zeros(1152, device=dev)
-            for _ in range(2):
-                ops.proj_gemm(A1, packed, bias, gi, 1152, lengths=L, T=T)
-            torch.cuda.synchronize()
-            k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            k0.record()
-            for _ in range(3):
-                ops.proj_gemm(A1, packed, bias, gi, 1152, lengths=L, T=T)
-            k1.record()
-            torch.cuda.synchronize()
-            kms = k0.elapsed_time(k1) / 3
-            by = frames * (384 + 1152) * 4
-            roofline = {"kernel": "proj_gemm_kernel (layer 1)", "bound": "hbm", "achieved": by / kms / 1e6, "peak": peaks["hbm"],
-                        "unit": "GB/s", "frac": by / kms / 1e6 / peaks["hbm"], "traffic": None, "ms_per_launch": kms,
-                        "peak_src": f"{peaks['src']} copy bandwidth", "note": "algorithmic bytes = frames x (384 + 1152) x 4"}
-        if rank == 0:
-            line = {"metric": "inference_clips_per_sec", "value": B * world * args.steps / (ms / 1e3), "unit": "clips/s",
-                    "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-                    "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
-                    "config": {"workload": "configs[3]: landmarks-only BiGRU (no ROI CNN), T=256", "clips_per_gpu": B, "frames": T,
-                               "lengths": "all=T" if args.lengths == "full" else "uniform[6,T]", "precision": args.precision,
-                               "l2": "inputs (0.75 GB/step) larger than L2"},
-                    "clocks": clk.summary(),
-                    "e2e": {"value": B * world * n_e2e / (e2e_ms / 1e3), "unit": "clips/s",
-                            "h2d_bytes_per_step": int(hX.numel() * 4 + hL.numel() * 8), "d2h_bytes_per_step": int(h_out.numel() * 4)},
-                    "gpu_launches": launches, "roofline": roofline, "cpu_baseline": None}
-            print(json.dumps(line), flush=True)
-    else:
-        from silent_speech_b200.streaming import StreamScheduler
-        S, W = args.batch or 1250, T_FRAMES
-        p = ref_model.synth_params(42)
-        model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=True, precision=args.precision)
-        model.load_state_dict(p)
-        model = model.to(dev).eval()
-        sch = StreamScheduler(model, S, max_t=W)
-        rng = np.random.default_rng(42 + rank)
-        pool = 8                                            # distinct synthetic frames per stream, cycled
-        hX = torch.from_numpy(rng.normal(0, 0.5, (pool, S, X_DIM)).astype(np.float32)).pin_memory()
-        hR = torch.from_numpy(rng.integers(0, 256, (pool, S, 48, 96)).astype(np.uint8)).pin_memory()
-        ids = np.arange(S)
-
-        def tick(k):
-            Xd, Rd = hX[k % pool].to(dev, non_blocking=True), hR[k % pool].to(dev, non_blocking=True)
-            due, logits = sch.tick(ids, Xd, Rd)
-            return due, (None if logits is None else logits.cpu())      # host copy of the predictions: e2e by construction
-        for k in range(W + 2 * args.warmup):                # fill every window, then warm up
-            tick(k)
-        barrier()
-        c0 = ssb_lib.launch_count()
-        lat, preds = [], 0
-        with ClockSampler(local) as clk:
-            t_all0 = time.perf_counter()
-            for k in range(2 * args.steps):                 # a step = two camera frames = one prediction per stream
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                due, _ = tick(W + 2 * args.warmup + k)
-                e1.record()
-                e1.synchronize()
-                lat.append(e0.elapsed_time(e1))
-                preds += int(due.size)
-            barrier()
-            wall_ms = (time.perf_counter() - t_all0) * 1e3
-        launches = ssb_lib.launch_count() - c0
-        ms = max_over_ranks(float(np.sum(lat)))
-        tot = torch.tensor([preds], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(tot)
-        if rank == 0:
-            val = float(tot.item()) / (ms / 1e3)
-            line = {"metric": "stream_predictions_per_sec", "value": val, "unit": "window classifications/s", "n_gpus": world,
-                    "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-                    "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
-                    "config": {"workload": "configs[4]: sliding-window streams (live_feed.py policy: window 90, predict every 2nd frame)",
-                               "streams_per_gpu": S, "window": W, "step": "2 camera frames per stream",
-                               "precision": args.precision, "l2": "ring state 95 MB + 6.7 MB new frames per tick"},
-                    "clocks": clk.summary(),
-                    "tick_latency_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
-                                        "frames_per_sec_sustained_per_stream": 1e3 * len(lat) / wall_ms},
-                    "e2e": {"value": val, "unit": "window classifications/s",
-                            "h2d_bytes_per_step": int(2 * S * (X_DIM * 4 + 48 * 96)), "d2h_bytes_per_step": int(S * NUM_CLASSES * 4)},
-                    "gpu_launches": launches, "roofline": None, "cpu_baseline": None}
-            print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+        e0.record()
+        due, _ = tick(W + 2 * warmup + k)
+        e1.record()
+        e1.synchronize()
+        lat.append(e0.elapsed_time(e1))
+        preds += int(due.size)
+    cx.barrier()
+    wall_ms = (time.perf_counter() - t_all0) * 1e3
+    launches = ssb_lib.launch_count() - c0
+    ms = cx.max_over_ranks(float(np.sum(lat)))
+    tot = cx.sum_over_ranks(preds)
+    val = tot / (ms / 1e3)
+    return {"metric": "stream_predictions_per_sec", "value": val, "unit": "window classifications/s", "ms_per_step": ms / steps,
+            "steps": steps, "warmup": warmup, "dtype": DTYPE["tc3"], "gpu_launches": launches,
+            "config": {"workload": "configs[4]: sliding-window streams (live_feed.py policy: window 90, predict every 2nd frame)",
+                       "streams_per_gpu": S, "window": W, "step": "2 camera frames per stream",
+                       "l2": "ring state 95 MB + 6.7 MB new frames per tick"},
+            "tick_latency_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
+                                "frames_per_sec_sustained_per_stream": 1e3 * len(lat) / wall_ms},
+            "e2e": {"value": val, "unit": "window classifications/s",
+                    "h2d_bytes_per_step": int(2 * S * (X_DIM * 4 + 48 * 96)), "d2h_bytes_per_step": int(S * NUM_CLASSES * 4)}}
 
 
-def metric_name(workload):
-    return "train_step_samples_per_sec" if workload == "train" else "inference_clips_per_sec"
-
-
-def workload_config(workload, B):
-    if workload == "train":
-        return {"workload": "configs[2]: full train step (fwd+bwd+clip+Adam) points+ROI model", "clips_per_gpu": B,
-                "frames": T_FRAMES, "lengths": "all=T", "l2": "inputs larger than L2"}
-    return {"workload": "configs[1]: batched inference word_model_points_roi", "clips_per_gpu": B,
-            "frames": T_FRAMES, "lengths": "all=T", "l2": "inputs (1.96 GB/step) larger than L2"}
+def features_block(cx):
+    """K1 (landmark feature kernel, live_infer_official.py:141-169): frames/s and GB/s against both byte counts of SURVEY
+    section 8(d) -- 1,424 B/frame compulsory, 6,456 B/frame when whole landmark rows are streamed."""
+    from silent_speech_b200 import extract_features, synth
+    dev = cx.dev
+    B, T = cx.args.features_batch, T_FRAMES
+    lm_h, present_h = synth.landmarks(64, T, seed=1)
+    reps = (B + 63) // 64
+    lm = torch.from_numpy(lm_h).to(dev).repeat(reps, 1, 1, 1)[:B].contiguous()
+    present = torch.from_numpy(present_h).to(dev).repeat(reps, 1)[:B].contiguous()
+    ms = cx.kernel_ms(lambda: extract_features(lm, synth.FRAME_W, synth.FRAME_H, present=present), reps=5)
+    fr = B * T
+    peaks = cx.peaks
+    gbs_algo, gbs_rows = fr * FEAT_BYTES_ALGO / ms / 1e6, fr * FEAT_BYTES_ROWS / ms / 1e6
+    return {"metric": "feature_frames_per_sec", "value": fr / (ms / 1e3), "unit": "frames/s", "ms_per_launch": ms,
+            "config": {"workload": "K1: landmarks f32[B,T,478,3] -> X f32[B,T,180]", "clips": B, "frames": T,
+                       "l2": "landmark tensor (%.2f GB) larger than L2" % (lm.numel() * 4 / 1e9)},
+            "roofline": {"kernel": "features_kernel", "bound": "hbm", "achieved": gbs_algo, "peak": peaks["hbm"], "unit": "GB/s",
+                         "frac": gbs_algo / peaks["hbm"], "achieved_row_granular": gbs_rows, "frac_row_granular": gbs_rows / peaks["hbm"],
+                         "traffic": ncu_traffic("features", B, "full"), "peak_src": f"{peaks['src']} copy bandwidth",
+                         "note": "achieved = 1,424 B/frame (compulsory) x frames / time; *_row_granular = 6,456 B/frame (whole 5,736-byte "
+                                 "landmark rows streamed + 720 B written)"}}
 
 
 def bind_near_gpu(dev):
@@ -356,227 +593,145 @@ def bind_near_gpu(dev):
         return f"unbound ({type(e).__name__})"
 
 
+def run_ours(args, rank, world, local):
+    cx = Ctx(args, rank, world, local)
+    dev = cx.dev
+    from silent_speech_b200 import BiGRUClassifier, synth
+    wl = args.workload
+    line = {}
+    t_start = time.perf_counter()
+    want_cpu = (not args.no_cpu_baseline) and world == 1 and rank == 0      # the contract's CPU baseline: rank 0 at N=1 only
+
+    if wl in ("all", "infer"):
+        B = args.batch
+        model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=True, precision=args.precision)
+        model.load_state_dict(synth.synth_params(42))     # seed-42 weights of the reference's init magnitudes (no ckpt is shipped)
+        model = model.to(dev).eval()
+        d = make_batch(B, T_FRAMES, args.lengths, seed=42 + rank)
+        hX = torch.from_numpy(d["X"]).pin_memory(); hL = torch.from_numpy(d["lengths"]).pin_memory()
+        hR = torch.from_numpy(d["R"]).pin_memory()
+        X, L, R = hX.to(dev), hL.to(dev), hR.to(dev)
+        frames = int(d["lengths"].sum())
+        h2d_gbs = h2d_probe(cx)
+        clk = ClockSampler(local)
+        head = infer_block(cx, model, args.precision, (X, L, R), (hX, hL, hR), frames, args.steps, args.warmup, clk, h2d_gbs)
+        line = {"metric": "inference_clips_per_sec", "value": head["value"], "unit": "clips/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": head["dtype"], "data": "synthetic",
+                "config": infer_config(B, args.lengths, args.precision), "clocks": clk.summary(), "e2e": head["e2e"],
+                "gpu_launches": head["gpu_launches"], "roofline": head["roofline"], "cpu_baseline": None}
+        if cx.affinity:
+            line["config"]["host_affinity"] = cx.affinity
+        other = "fp16" if args.precision != "fp16" else "tc3"
+        if wl == "all" or args.both_precisions:
+            n2 = max(3, min(args.steps, 6))
+            blk = infer_block(cx, model, other, (X, L, R), (hX, hL, hR), frames, n2, 3, None, h2d_gbs)
+            blk["config"] = infer_config(B, args.lengths, other)
+            blk["steps"], blk["warmup"] = n2, 3
+            # the two modes against each other on the device (every rank), and against the CPU reference below (N = 1)
+            with torch.no_grad():
+                model.precision = args.precision; a = model(X[:CPU_CHUNK], L[:CPU_CHUNK], R[:CPU_CHUNK]).float().cpu()
+                model.precision = other; b = model(X[:CPU_CHUNK], L[:CPU_CHUNK], R[:CPU_CHUNK]).float().cpu()
+            blk["logit_diff_between_modes"] = float((a - b).abs().max() / a.abs().max())
+            blk["argmax_agreement_between_modes"] = float((a.argmax(1) == b.argmax(1)).float().mean())
+            line[f"{other}_mode"] = blk
+            gpu_logits = {args.precision: a, other: b}
+        else:
+            with torch.no_grad():
+                model.precision = args.precision
+                gpu_logits = {args.precision: model(X[:CPU_CHUNK], L[:CPU_CHUNK], R[:CPU_CHUNK]).float().cpu()}
+        model.precision = args.precision
+        if want_cpu:
+            threads = os.cpu_count() or 1
+            v, cms, sample, ref = cpu_arm("infer", threads, 10, 1, args.lengths, budget_s=12.0, want_logits=True)
+            line["cpu_baseline"] = {"value": v, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample}
+            # the CPU arm's first chunk IS clips [0, 64) of this rank's batch: measured logit error of each precision mode
+            for prec, g in gpu_logits.items():
+                err = {"logit_rel_err_vs_cpu_reference": float((g - ref).abs().max() / ref.abs().max()),
+                       "argmax_agreement_vs_cpu_reference": float((g.argmax(1) == ref.argmax(1)).float().mean()), "clips_checked": CPU_CHUNK}
+                if prec == args.precision:
+                    line["parity"] = err
+                else:
+                    line[f"{prec}_mode"]["parity"] = err
+        del X, L, R, hX, hL, hR, model
+        torch.cuda.empty_cache()
+
+    if wl in ("all", "train"):
+        n_tr = args.steps if wl == "train" else max(5, min(args.steps, 20))
+        block, dp = train_block(cx, n_tr, max(3, args.warmup), want_cpu)
+        if wl == "train":
+            line = {"metric": block["metric"], "value": block["value"], "unit": block["unit"], "n_gpus": world, "steps": n_tr,
+                    "warmup": max(3, args.warmup), "ms_per_step": block["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+                    "vs_baseline": None, "dtype": block["dtype"], "data": "synthetic", "config": block["config"],
+                    "clocks": block["clocks"], "e2e": block["e2e"], "gpu_launches": block["gpu_launches"], "roofline": block["roofline"],
+                    "cpu_baseline": block["cpu_baseline"], "allreduce_ms": block["allreduce_ms"], "dp_check": dp}
+        else:
+            line["train_step"] = block
+            line["dp_check"] = dp
+        torch.cuda.empty_cache()
+
+    if wl in ("all", "features"):
+        blk = features_block(cx)
+        if wl == "features":
+            line = blk | {"n_gpus": world, "higher_is_better": True, "scaling": "weak", "data": "synthetic", "dtype": "f32", "vs_baseline": None}
+        else:
+            line["features"] = blk
+        torch.cuda.empty_cache()
+
+    if wl in ("all", "points256"):
+        n = args.steps if wl == "points256" else max(3, min(args.steps, 4))
+        blk = points256_block(cx, n, 3)
+        if wl == "points256":
+            line = blk | {"n_gpus": world, "higher_is_better": True, "scaling": "weak", "data": "synthetic", "vs_baseline": None}
+        else:
+            line["points256"] = blk
+        torch.cuda.empty_cache()
+
+    if wl in ("all", "stream"):
+        n = args.steps if wl == "stream" else max(5, min(args.steps, 20))
+        blk = stream_block(cx, n, 3)
+        if wl == "stream":
+            line = blk | {"n_gpus": world, "higher_is_better": True, "scaling": "weak", "data": "synthetic", "vs_baseline": None}
+        else:
+            line["stream"] = blk
+
+    cx.barrier()
+    if rank == 0:
+        line["bench_wall_s"] = time.perf_counter() - t_start
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        cx.dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="infer", choices=["infer", "train", "points256", "stream"],
-                    help="infer = configs[1] (default, the headline); train = configs[2]; points256 = configs[3] "
-                         "(landmarks-only, T=256); stream = configs[4] (sliding-window streams, 1,250 per GPU)")
-    ap.add_argument("--batch", type=int, default=0, help="clips per GPU (default 4096 infer / 128 train)")
+    ap.add_argument("--workload", default="all", choices=["all", "infer", "train", "points256", "stream", "features"],
+                    help="all (default) = configs[1] headline + fp16_mode + train_step + dp_check + features + points256 + stream "
+                         "blocks in one line; the others run one workload alone with its own top-level line")
+    ap.add_argument("--batch", type=int, default=4096, help="clips per GPU, inference (configs[1])")
+    ap.add_argument("--train-batch", type=int, default=128, help="clips per GPU, train step (configs[2]: 1024 over 8 GPUs)")
+    ap.add_argument("--points-batch", type=int, default=4096, help="clips per GPU, configs[3]")
+    ap.add_argument("--streams", type=int, default=1250, help="streams per GPU, configs[4] (10,000 over 8 GPUs)")
+    ap.add_argument("--features-batch", type=int, default=4096, help="clips per launch of the K1 block")
     ap.add_argument("--lengths", default="full", choices=["full", "uniform"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--both-precisions", action="store_true", help="--workload infer: also report the other precision mode")
     ap.add_argument("--e2e-chunk", type=int, default=512, help="clips per pipelined host->device chunk in the e2e arm")
-    ap.add_argument("--precision", default="", choices=["", "fp32", "tc3", "fp16"],
-                    help="fp16 = tcgen05 single pass, f16 operands / f32 accumulate (inference default; stated tolerance: logits "
-                         "within 1e-3 of max|logit| of the fp32 CPU reference, identical argmax -- tests/test_gpu_tensorcore.py); "
-                         "tc3 = tcgen05 split-fp16 x3, fp32-parity grade 1e-4 (training default; also measured and reported "
-                         "beside the inference headline); fp32 = CUDA-core FMA")
+    ap.add_argument("--precision", default="tc3", choices=["fp32", "tc3", "fp16"],
+                    help="headline precision of the inference workload: tc3 = tcgen05 split-fp16 x3, the fp32-parity mode (default: "
+                         "configs[1] asks for fp32 parity vs the CPU logits); fp16 = tcgen05 single pass (stated tolerance 1e-3); "
+                         "fp32 = CUDA-core FMA")
     args = ap.parse_args()
-    if not args.precision:
-        args.precision = "tc3" if args.workload == "train" else "fp16"
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
-    if args.workload in ("points256", "stream"):
-        run_extra(args, rank, world, local)
-        return
-
-    import torch.distributed as dist
-    dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
-    affinity = bind_near_gpu(dev) if world > 1 else None
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-    from silent_speech_b200 import BiGRUClassifier
-    from oracle import ref_model
-
-    B = args.batch or (4096 if args.workload == "infer" else 128)
-    peaks = load_peaks()
-    p = ref_model.synth_params(42)         # seed-42 weights of the reference's init magnitudes (no ckpt is shipped)
-    model = BiGRUClassifier(X_DIM, NUM_CLASSES, use_roi=True, precision=args.precision)
-    model.load_state_dict(p)
-    model = model.to(dev)
-    d = make_batch(B, T_FRAMES, args.lengths, seed=42 + rank)
-    hX = torch.from_numpy(d["X"]).pin_memory(); hL = torch.from_numpy(d["lengths"]).pin_memory()
-    hR = torch.from_numpy(d["R"]).pin_memory(); hy = torch.from_numpy(d["y"]).pin_memory()
-    X, L, R, y = hX.to(dev), hL.to(dev), hR.to(dev), hy.to(dev)
-    frames = int(d["lengths"].sum())
-
-    if args.workload == "train":
-        from silent_speech_b200.train import Trainer
-        trainer = Trainer(model, lr=3e-4, world_size=world)
-        step = lambda: trainer.step(X, L, R, y)
-        launches_per_step = trainer.launches_per_step
-    else:
-        model.eval()
-
-        def step():
-            with torch.no_grad():
-                return model(X, L, R)
-        launches_per_step = None
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    from silent_speech_b200 import _lib as ssb_lib
-    for _ in range(args.warmup):
-        step()
-    barrier()
-    c0 = ssb_lib.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk:
-        e0.record()
-        for _ in range(args.steps):
-            step()
-        e1.record()
-        barrier()
-    launches = ssb_lib.launch_count() - c0
-    ms = e0.elapsed_time(e1)
-    t = torch.tensor([ms], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    value = B * world * args.steps / (ms / 1e3)
-
-    # ---- end to end through the public API with host buffers (H2D + D2H inside the timed region).
-    # Inference: model.infer_host(X, lengths, R) -- pinned host batch in, host logits out; it overlaps the
-    # host->device copy of one 512-clip chunk with the compute of the previous one.  Train: Trainer.step on
-    # batches staged by HostBatchPrefetcher (the copy of batch i+1 runs on a side stream during step i), loss read back.
-    h_out = torch.empty(B, NUM_CLASSES, dtype=torch.float32).pin_memory()
-
-    if args.workload == "train":
-        from silent_speech_b200.train import HostBatchPrefetcher
-        prefetch = HostBatchPrefetcher(dev)
-        prefetch.submit(hX, hL, hR, hy)          # batch 0; every timed step copies exactly one (the next) batch
-
-    def e2e_step():
-        if args.workload == "train":
-            Xd, Ld, Rd, yd = prefetch.get()
-            prefetch.submit(hX, hL, hR, hy)      # the next step's batch travels while this step computes
-            return trainer.step(Xd, Ld, Rd, yd).cpu()
-        return model.infer_host(hX, hL, hR, chunk=args.e2e_chunk, out=h_out)
-    e2e_step()
-    barrier()
-    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n_e2e = max(2, min(args.steps, 5))
-    with ClockSampler(local) as clk2:
-        e2.record()
-        for _ in range(n_e2e):
-            res = e2e_step()
-        e3.record()
-        barrier()
-    t = torch.tensor([e2.elapsed_time(e3)], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_val = B * world * n_e2e / (float(t.item()) / 1e3)
-    h2d = hX.numel() * 4 + hL.numel() * 8 + hR.numel() + (hy.numel() * 8 if args.workload == "train" else 0)
-    d2h = res.numel() * res.element_size()
-
-    # ---- dominant kernel (fused ROI CNN) timed alone for the roofline line
-    from silent_speech_b200 import ops
-    w = model.roi_cnn.tensors()
-    cnn_passes = {"fp32": 0, "tc3": 3, "fp16": 1}[args.precision]
-    for _ in range(2):
-        ops.roi_cnn_fwd(R, L, w, passes=cnn_passes)
-    torch.cuda.synchronize()
-    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    k0.record()
-    for _ in range(5):
-        ops.roi_cnn_fwd(R, L, w, passes=cnn_passes)
-    k1.record()
-    torch.cuda.synchronize()
-    cnn_ms = k0.elapsed_time(k1) / 5
-    achieved = CNN_FLOP_PER_FRAME * frames / (cnn_ms / 1e3) / 1e12
-    roofline = {"kernel": {0: "roi_cnn_fwd_kernel", 1: "roi_cnn_tc3_kernel<false,4,128>", 3: "roi_cnn_tc3_kernel<true,2,256>"}[cnn_passes], "bound": "tensor", "achieved": achieved, "peak": peaks["tensor_burst"],
-                "unit": "TFLOP/s", "frac": achieved / peaks["tensor_burst"],
-                "traffic": ncu_traffic(args.precision, B, args.lengths),
-                "peak_src": f"{peaks['src']} bf16 burst", "ms_per_launch": cnn_ms,
-                "note": "K2 (fused ROI CNN), algorithmic 5,309,952 FLOP/frame; step-level: %.1f TFLOP/s over %.0f MFLOP/clip" % (
-                    FWD_FLOP_PER_FRAME * frames * world * args.steps / (ms / 1e3) / 1e12, FWD_FLOP_PER_FRAME * T_FRAMES / 1e6)}
-
-    if args.workload == "train" and cnn_passes == 3:
-        # The train step's dominant kernel is the ROI CNN BACKWARD (fp32 CUDA cores, fed by the forward's saved
-        # activations): time it alone on the saved records of one forward call and report it against the same tensor
-        # peak -- it does not use the tensor cores, which is exactly what the fraction says.  Algorithmic work = the two
-        # gradients of every convolution = 2 x the forward's FLOPs.
-        names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
-                 "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
-        sd = dict(model.named_parameters())
-        gbuf = [torch.zeros_like(sd[n]) for n in names]
-        saved = ops.roi_cnn_saved(B, T_FRAMES, dev)
-        ops.roi_cnn_fwd(R, L, w, passes=3, saved=saved)
-        d_emb = torch.randn(B, T_FRAMES, 32, device=dev) * 1e-3
-        for _ in range(2):
-            ops.roi_cnn_bwd(R, L, w, True, d_emb, 0, gbuf, saved=saved)
-        torch.cuda.synchronize()
-        k0.record()
-        for _ in range(5):
-            ops.roi_cnn_bwd(R, L, w, True, d_emb, 0, gbuf, saved=saved)
-        k1.record()
-        torch.cuda.synchronize()
-        bwd_ms = k0.elapsed_time(k1) / 5
-        ach = 2 * CNN_FLOP_PER_FRAME * frames / (bwd_ms / 1e3) / 1e12
-        fma_peak = 148 * 128 * 2 * 1.965e9 / 1e12            # fp32 FMA lanes x 2 FLOP x SM clock
-        roofline = {"kernel": "roi_cnn_bwd_kernel", "bound": "tensor", "achieved": ach, "peak": peaks["tensor_burst"],
-                    "unit": "TFLOP/s", "frac": ach / peaks["tensor_burst"], "traffic": None,
-                    "peak_src": f"{peaks['src']} bf16 burst", "ms_per_launch": bwd_ms,
-                    "note": "K2-bwd (fp32 CUDA cores, forward activations saved by the split-mode K2): algorithmic 2 x 5,309,952 "
-                            "FLOP/frame; %.0f %% of the fp32 FMA peak (%.1f TFLOP/s); the forward K2 in this step: %.3f ms = "
-                            "%.1f TFLOP/s" % (100 * ach / fma_peak, fma_peak, cnn_ms, achieved)}
-
-    # ---- the same batch in the fp32-parity mode (tc3), reported beside the fp16 headline
-    parity_mode = None
-    if args.workload == "infer" and args.precision == "fp16":
-        model.precision = "tc3"
-        for _ in range(2):
-            step()
-        barrier()
-        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        n_par = max(2, min(args.steps, 4))
-        p0.record()
-        for _ in range(n_par):
-            step()
-        p1.record()
-        barrier()
-        t = torch.tensor([p0.elapsed_time(p1)], device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        model.precision = "fp16"
-        parity_mode = {"precision": "tc3 (f16 hi/lo split x3, logits within 1e-4 of the fp32 CPU reference)",
-                       "value": B * world * n_par / (float(t.item()) / 1e3), "unit": "clips/s", "ms_per_step": float(t.item()) / n_par}
-
-    clk.rows += clk2.rows                   # clocks sampled over both timed regions (device-resident and e2e)
-    clocks = clk.summary()
-    if rank == 0:
-        cpu = None
-        if not args.no_cpu_baseline and world == 1:      # the contract's CPU baseline: rank 0 at N=1 only
-            threads = os.cpu_count() or 1
-            v, sample = cpu_reference_rate(args.workload, threads)
-            cpu = {"value": v, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample}
-        line = {"metric": metric_name(args.workload), "value": value, "unit": "clips/s", "n_gpus": world,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None,
-                "dtype": {"fp32": "f32", "tc3": "f16 hi/lo split operands, f32 accumulate (f32-parity grade)", "fp16": "f16 operands, f32 accumulate"}[args.precision],
-                "data": "synthetic",
-                "config": workload_config(args.workload, B) | {"precision": args.precision} | {"lengths": "all=T" if args.lengths == "full" else "uniform[6,T]"},
-                "clocks": clocks,
-                "e2e": {"value": e2e_val, "unit": "clips/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
-                "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
-        if parity_mode:
-            line["fp32_parity_mode"] = parity_mode
-        if affinity:
-            line["config"]["host_affinity"] = affinity
-        print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    run_ours(args, rank, world, local)
 
 
 if __name__ == "__main__":

@@ -32,15 +32,20 @@ int ssb_device_info(int32_t* sm_count, int32_t* cc_major, int32_t* cc_minor);
  * (live_infer_official.py:141-169, 275-296).
  * landmarks [B,T,n_lm,lm_stride] (x,y first), ids [K<=128], anchor_ids = {left corner 61,
  * right corner 291, upper inner 13, lower inner 14} as landmark ids, present [B,T] or NULL.
- * X [B,T,2K+4]; center [B,T,2], mouth_w [B,T], valid [B,T], lengths [B] may be NULL.
+ * X [B,T,2K+4]; center [B,T,2], mouth_w [B,T], valid [B,T] (required when compact), lengths [B] may be NULL.
  * compact != 0 packs the used frames to the front of each clip (what the reference's bufX holds)
- * and writes their count to lengths; otherwise skipped frames give zero rows in place. */
+ * and writes their count to lengths; otherwise skipped frames give zero rows in place.
+ * xy_px [B,T,K,2] or NULL: the gathered pixel positions (x*w, y*h) of the K landmarks, i.e. `xy` of
+ * live_infer_official.py:147 -- the pure data-movement part of the feature, exported so that the gather can be checked
+ * bit for bit (rows follow X: compacted or in place, zeros for skipped frames).
+ * Velocity history: an undetected frame (present = 0) leaves it untouched, a detected frame outside the band resets it
+ * (live_infer_official.py:272-296). */
 int ssb_features_fwd(const float* landmarks, int64_t B, int64_t T, int64_t n_lm, int64_t lm_stride,
                      const int32_t* ids, int32_t K, const int32_t anchor_ids_host[4],
                      const uint8_t* present, float frame_w, float frame_h,
                      float gate_min_px, float gate_max_px, int32_t compact,
                      float* X, float* center, float* mouth_w, uint8_t* valid, int64_t* lengths,
-                     void* stream);
+                     float* xy_px, void* stream);
 
 /* K2: fused mouth-ROI CNN forward (normalise, per-frame standardise, TinyROICNN).
  * Replaces train_model_official.py:286-294 (standardize=1) / live_infer_official.py:126-127 (0).

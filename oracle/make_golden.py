@@ -81,23 +81,37 @@ def golden_features(live, record):
     out = {"lm": lm, "present": present, "w": np.int64(synth.FRAME_W), "h": np.int64(synth.FRAME_H),
            "ids": np.array(live.FIXED_IDXS, np.int32)}
     assert live.FIXED_IDXS == record.FIXED_IDXS and len(live.FIXED_IDXS) == 88
+    # make sure the fixture holds the case the capture loop treats specially: a dropped detection BETWEEN two used
+    # frames (velocity must bridge it) and a dropped detection right after an out-of-band frame (history stays reset)
+    present[0, 3] = 0; present[0, 2] = 1; present[0, 4] = 1
+    present[1, 6] = 0; present[1, 4] = 1; present[1, 7] = 1
+    w, h = synth.FRAME_W, synth.FRAME_H
     for tag, mod in (("live", live), ("record", record)):
         X = np.zeros((B, T, 180), np.float32); C = np.zeros((B, T, 2), np.float32)
-        MW = np.zeros((B, T), np.float64); V = np.zeros((B, T), np.uint8)
+        MW = np.zeros((B, T), np.float64); V = np.zeros((B, T), np.uint8); XY = np.zeros((B, T, 88, 2), np.float32)
         for b in range(B):
-            prev = None
+            prev_xy = None
+            recording = True
             for t in range(T):
-                face = as_face(lm[b, t])
-                ok = bool(present[b, t])
-                if ok:
-                    mw = mod.mouth_width_px(face, synth.FRAME_W, synth.FRAME_H)
-                    ok = mod.MOUTH_W_MIN_PX <= mw <= mod.MOUTH_W_MAX_PX
-                if not ok:
-                    prev = None
-                    continue
-                feat, prev, center, mw = mod.extract_feature(face, synth.FRAME_W, synth.FRAME_H, mod.FIXED_IDXS, prev)
-                X[b, t] = feat; C[b, t] = center; MW[b, t] = mw; V[b, t] = 1
+                # the body of the capture loop, live_infer_official.py:272-296 / record_landmarks_official.py:178-201,
+                # statement for statement: `res.face_landmarks` is empty when no face was detected
+                face_landmarks = [as_face(lm[b, t])] if present[b, t] else []
+                if face_landmarks:
+                    face = face_landmarks[0]
+                    mw = mod.mouth_width_px(face, w, h)
+                    in_range = mod.MOUTH_W_MIN_PX <= mw <= mod.MOUTH_W_MAX_PX
+                    if recording and in_range:
+                        feat, prev_xy, center, mw_ret = mod.extract_feature(face, w, h, mod.FIXED_IDXS, prev_xy)
+                        X[b, t] = feat; C[b, t] = center; MW[b, t] = mw_ret; V[b, t] = 1
+                        # `xy` of live:147 / record:64, the gather itself (not returned by extract_feature)
+                        XY[b, t] = np.array([[face[i].x * w, face[i].y * h] for i in mod.FIXED_IDXS], dtype=np.float32)
+                    else:
+                        if recording:
+                            prev_xy = None
         out[f"X_{tag}"] = X; out[f"center_{tag}"] = C; out[f"mouth_w_{tag}"] = MW; out[f"valid_{tag}"] = V
+        out[f"xy_px_{tag}"] = XY
+    # a bridged frame really carries a velocity (otherwise the fixture would not distinguish the two readings)
+    assert out["valid_live"][0, 2] and out["valid_live"][0, 4] and out["X_live"][0, 4, 176] > 0
     np.savez_compressed(os.path.join(OUT, "features.npz"), **out)
     print("features.npz", {k: getattr(v, "shape", v) for k, v in out.items()})
 
@@ -343,11 +357,66 @@ def golden_legacy():
           "toggles", int(np.abs(np.diff(open_tr.astype(int), axis=1)).sum()))
 
 
+def golden_checkpoint(train, live):
+    """The checkpoint contract (train_model_official.py:489-500 written, live_infer_official.py:198-221 read) and the
+    constructor's seed-42 initialisation (train:45-47, 402), both directions, executed against the reference here:
+      * the reference constructor under torch.manual_seed(42): per-tensor (norm, sum) + strided samples -> `init/...`
+      * a file written by silent_speech_b200.checkpoint.save is loaded by the reference's own load_classifier and run
+        on a fixed input -> `ref_loaded_ours_logits` (+ the returned id_to_label / max_t / use_roi)
+      * a file written the way train:489-500 writes it (the reference's model, the same dict literal) is loaded by
+        silent_speech_b200.load_classifier(device="cpu") and must hold identical tensors
+    The .pt files themselves are 4.8 MB each and are not committed; the CPU tests rebuild both files from seeds."""
+    import silent_speech_b200 as ssb
+    from silent_speech_b200 import checkpoint as ckpt_io
+    out = {}
+    torch.manual_seed(42)
+    ref = train.BiGRUClassifier(180, 10, use_roi=True, roi_emb=32, hidden=192)
+    sd = ref.state_dict()
+    out["names"] = np.array(list(sd.keys()))
+    for k, v in sd.items():
+        out[f"init_stat/{k}"], out[f"init_samp/{k}"] = summarise(v)
+        out[f"shape/{k}"] = np.array(v.shape, np.int64)
+    torch.manual_seed(42)
+    ours = ssb.BiGRUClassifier(180, 10, use_roi=True)
+    osd = ours.state_dict()
+    assert list(osd.keys()) == list(sd.keys())
+    assert all(torch.equal(osd[k], sd[k]) for k in sd), "seed-42 init differs from the reference constructor"
+    labels = ["hello", "yes", "no", "please", "thanks", "stop", "go", "left", "right", "help"]
+    tmp = tempfile.mkdtemp()
+    # ours -> reference loader
+    path_ours = os.path.join(tmp, "ours.pt")
+    ckpt_io.save(path_ours, ours, labels, max_t=90, seed=42)
+    model_r, id_to_label, max_t, use_roi = live.load_classifier(path_ours)
+    rng = np.random.default_rng(5)
+    X = rng.normal(0, 0.25, (2, 9, 180)).astype(np.float32)
+    R = rng.integers(0, 256, (2, 9, 48, 96)).astype(np.uint8)
+    L = np.array([9, 6], np.int64)
+    with torch.no_grad():
+        lg = model_r(torch.from_numpy(X), torch.from_numpy(L), torch.from_numpy(R))
+    out.update(X=X, R=R, lengths=L, ref_loaded_ours_logits=lg.numpy(), ref_loaded_max_t=np.int64(max_t),
+               ref_loaded_use_roi=np.bool_(use_roi), ref_loaded_labels=np.array([id_to_label[i] for i in range(10)]),
+               labels=np.array(labels))
+    # reference -> our loader (dict literal of train:489-500)
+    path_ref = os.path.join(tmp, "ref.pt")
+    label_to_id = {lab: i for i, lab in enumerate(labels)}
+    id_to_label_w = {i: lab for lab, i in label_to_id.items()}
+    torch.save({"model": ref.state_dict(), "x_dim": 180, "max_t": train.MAX_T, "use_roi": True, "roi_w": train.ROI_W,
+                "roi_h": train.ROI_H, "labels": labels, "label_to_id": label_to_id, "id_to_label": id_to_label_w,
+                "seed": train.SEED}, path_ref)
+    out["ref_ckpt_keys"] = np.array(sorted(torch.load(path_ref, map_location="cpu").keys()))
+    m2, id2, mt2, ur2 = ssb.load_classifier(path_ref, device="cpu")
+    assert all(torch.equal(m2.state_dict()[k], sd[k]) for k in sd) and mt2 == train.MAX_T and ur2 and id2 == id_to_label_w
+    out["ours_ckpt_keys"] = np.array(sorted(torch.load(path_ours, map_location="cpu").keys()))
+    np.savez_compressed(os.path.join(OUT, "checkpoint.npz"), **out)
+    print("checkpoint.npz: init identical, ours->reference loader ok, reference->our loader ok; keys", out["ref_ckpt_keys"].tolist())
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     train, live, record = import_reference()
     torch.set_num_threads(1)                 # deterministic reduction order for the fixtures
     golden_features(live, record)
+    golden_checkpoint(train, live)
     golden_model(train, live, "roi", True, B=4, T=12, lens=[12, 5, 1, 9], seed=101)
     golden_model(train, live, "points", False, B=5, T=20, lens=[20, 6, 13, 1, 17], seed=102)
     golden_model(train, live, "roi_hot", True, B=3, T=10, lens=[7, 10, 3], seed=103, scale=2.0)

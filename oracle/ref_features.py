@@ -83,8 +83,11 @@ def clip_features(lm: np.ndarray, w: int, h: int, ids: np.ndarray = LANDMARK_IDS
     gate     (min_px, max_px) distance band on mouth width, or None to disable
              (live_infer_official.py:275-276: a frame is used only inside the band)
 
-    A frame that is absent or outside the band is skipped and resets the
-    velocity history (live_infer_official.py:294-296).
+    A frame without a detected face is skipped and leaves the velocity history
+    untouched (the reference's reset, live_infer_official.py:294-296 /
+    record_landmarks_official.py:199-201, sits inside ``if res.face_landmarks:``,
+    live:272 / record:178); a detected face outside the band is skipped and
+    resets it.
 
     Returns dict with
       X       float32 [T, 2K+4]  feature rows (zeros where the frame was skipped;
@@ -92,6 +95,7 @@ def clip_features(lm: np.ndarray, w: int, h: int, ids: np.ndarray = LANDMARK_IDS
                                  which is what the reference's ``bufX`` holds)
       valid   uint8   [T]        frame was used
       center  float32 [T, 2], mouth_w float32 [T]   (inputs of the ROI cropper)
+      xy_px   float32 [T, K, 2]  the gathered pixel positions (``xy`` of live:147; rows as X)
       length  int                number of used frames
     """
     T = lm.shape[0]
@@ -100,21 +104,23 @@ def clip_features(lm: np.ndarray, w: int, h: int, ids: np.ndarray = LANDMARK_IDS
     valid = np.zeros(T, np.uint8)
     center = np.zeros((T, 2), np.float32)
     mouth_w = np.zeros(T, np.float32)
+    xy_px = np.zeros((T, K, 2), np.float32)
     prev = None
     n = 0
     for t in range(T):
-        ok = True if present is None else bool(present[t])
-        if ok and gate is not None:
+        if present is not None and not bool(present[t]):
+            continue                      # `if res.face_landmarks:` is false: nothing happens, prev_xy survives
+        if gate is not None:
             mw = mouth_width(lm[t], w, h, flavour)
-            ok = gate[0] <= mw <= gate[1]
-        if not ok:
-            prev = None
-            continue
+            if not (gate[0] <= mw <= gate[1]):
+                prev = None               # live:294-296
+                continue
         feat, prev, c, mw = frame_feature(lm[t], w, h, ids, prev, flavour)
         row = n if compact else t
         X[row] = feat
         center[row] = c
         mouth_w[row] = mw
+        xy_px[row] = np.array([[float(lm[t, i, 0]) * w, float(lm[t, i, 1]) * h] for i in ids], np.float32)   # live:147
         valid[t] = 1
         n += 1
-    return {"X": X, "valid": valid, "center": center, "mouth_w": mouth_w, "length": n}
+    return {"X": X, "valid": valid, "center": center, "mouth_w": mouth_w, "xy_px": xy_px, "length": n}

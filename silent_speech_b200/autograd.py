@@ -93,7 +93,7 @@ def _gru_layer_backward(layer: int, dseq, seq_out, gates, lengths, B, T, inputs,
         weight_grads()
     else:
         ready = torch.cuda.Event()
-        ready.record()                               # BPTT outputs, amax and everything enqueued before them
+        ready.record(torch.cuda.current_stream(dgi.device))   # BPTT outputs, amax and everything enqueued before them
         with torch.cuda.stream(side):
             side.wait_event(ready)
             weight_grads()
@@ -144,7 +144,7 @@ def backward_impl(model, ctx: Dict, grads: Dict[str, torch.Tensor], dlogits: Opt
         ops.roi_cnn_bwd(ctx["R"], lengths, model.roi_cnn.tensors(), model.standardize_roi, d_emb.view(B, T, -1), 0,
                         [grads[n] for n in names], saved=ctx.get("cnn_saved"))
     if side is not None:
-        torch.cuda.current_stream().wait_stream(side)      # all gradients complete before anything that follows
+        torch.cuda.current_stream(dhid.device).wait_stream(side)      # all gradients complete before anything that follows
 
 
 class ClassifierFn(torch.autograd.Function):
@@ -160,7 +160,8 @@ class ClassifierFn(torch.autograd.Function):
     @staticmethod
     def backward(fctx, dlogits):
         model, names = fctx.model, fctx.names
-        grads = {n: torch.zeros_like(p) for n, p in model.named_parameters()}
-        backward_impl(model, fctx.ctx, grads, dlogits=dlogits.contiguous().float())
+        with torch.cuda.device(dlogits.device):
+            grads = {n: torch.zeros_like(p) for n, p in model.named_parameters()}
+            backward_impl(model, fctx.ctx, grads, dlogits=dlogits.contiguous().float())
         fctx.ctx = None
         return (None, None, None, None, None) + tuple(grads[n] for n in names)

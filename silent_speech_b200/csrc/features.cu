@@ -9,10 +9,17 @@
 // Layout: landmarks f32 [B,T,n_lm,lm_stride] (x,y first), ids i32 [K] sorted.
 // One warp owns a run of `frames_per_warp` consecutive frames of one clip and
 // carries the previous frame's normalised points in registers, so the only
-// cross-frame dependency (velocity, t-1 -> t) never leaves the warp; the frame
-// just before the run is recomputed (an L2 hit: the neighbouring warp streams it).
+// cross-frame dependency (velocity, previous used frame -> t) never leaves the warp; the
+// last detected frame before the run is recomputed (an L2 hit: the neighbouring warp streams it).
 // Per valid frame the compulsory traffic is K*8 B gathered + (2K+4)*4 B written
-// = 1,424 B at K = 88.
+// = 1,424 B at K = 88; at the (x,y,z) stride of 12 B the 88 points touch 4.2 KB of 32-byte
+// sectors of the 5,736-byte landmark row, and that sector traffic is what the kernel is bound by
+// (ncu: 6.3 TB/s of DRAM traffic, profiles/r2a_features_ncu.txt).
+//
+// Velocity history (live_infer_official.py:272-296, record_landmarks_official.py:178-201): a frame with NO
+// detected face leaves prev_xy untouched (the reset sits inside `if res.face_landmarks:`); a detected face outside
+// the 60..150 px band resets it.  So the predecessor of frame t is the last DETECTED frame before t, and it counts
+// only if it was inside the band.
 #include "common.cuh"
 
 namespace ssb {
@@ -26,9 +33,13 @@ struct FrameGeom {
   bool usable;        // present && inside the distance band
 };
 
-// (x, y) of one landmark; two 4-byte loads so any landmark stride (3 for x,y,z) is legal.
+// (x, y) of one landmark: one 8-byte load when the landmark stride keeps (x, y) 8-byte aligned (kVec2: even stride and
+// an 8-byte aligned tensor), two 4-byte loads otherwise (stride 3 = MediaPipe's x,y,z).  A compile-time switch: a
+// run-time branch around every load kept the compiler from batching a frame's loads (0.31 -> 0.52 ms per 4096 clips).
+template <bool kVec2>
 __device__ __forceinline__ float2 ld_xy(const float* __restrict__ f, int64_t idx, int lm_stride) {
   const float* p = f + idx * lm_stride;
+  if (kVec2) return __ldg(reinterpret_cast<const float2*>(p));
   return make_float2(__ldg(p), __ldg(p + 1));
 }
 
@@ -38,6 +49,7 @@ __device__ __forceinline__ float dist2f(float ax, float ay, float bx, float by) 
 }
 
 // Loads one frame: gathers this lane's points (pixel units) and the anchors.
+template <bool kVec2>
 __device__ __forceinline__ FrameGeom load_frame(const float* __restrict__ f, int lm_stride,
                                                 const int* __restrict__ ids, int K, int lane,
                                                 int4 anchors, float w, float h, bool present,
@@ -49,16 +61,16 @@ __device__ __forceinline__ FrameGeom load_frame(const float* __restrict__ f, int
     int k = lane + 32 * j;
     px[j] = 0.f; py[j] = 0.f;
     if (k < K) {
-      const float2 v = ld_xy(f, __ldg(ids + k), lm_stride);
+      const float2 v = ld_xy<kVec2>(f, __ldg(ids + k), lm_stride);
       px[j] = v.x * w; py[j] = v.y * h;
       sx += px[j]; sy += py[j];
     }
   }
   // anchors: every lane reads the same 4 landmarks (one broadcast transaction each)
-  const float2 a = ld_xy(f, anchors.x, lm_stride);
-  const float2 b = ld_xy(f, anchors.y, lm_stride);
-  const float2 u = ld_xy(f, anchors.z, lm_stride);
-  const float2 l = ld_xy(f, anchors.w, lm_stride);
+  const float2 a = ld_xy<kVec2>(f, anchors.x, lm_stride);
+  const float2 b = ld_xy<kVec2>(f, anchors.y, lm_stride);
+  const float2 u = ld_xy<kVec2>(f, anchors.z, lm_stride);
+  const float2 l = ld_xy<kVec2>(f, anchors.w, lm_stride);
   FrameGeom g;
   g.mouth_w = dist2f(a.x * w, a.y * h, b.x * w, b.y * h);
   g.open_px = dist2f(u.x * w, u.y * h, l.x * w, l.y * h);
@@ -68,13 +80,32 @@ __device__ __forceinline__ FrameGeom load_frame(const float* __restrict__ f, int
   return g;
 }
 
+// Pass 0 of compact mode: usable[b,t] = detected && mouth width inside the band (two landmarks per frame), so that the
+// main kernel finds a run's first output row by summing T bytes instead of re-deriving every earlier frame.
+__global__ void __launch_bounds__(256)
+features_valid_kernel(const float* __restrict__ lm, int64_t frames, int n_lm, int lm_stride, int4 anchors,
+                      const uint8_t* __restrict__ present, float w, float h, float gate_lo, float gate_hi,
+                      uint8_t* __restrict__ valid) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= frames) return;
+  bool ok = !present || present[i];
+  if (ok) {
+    const float* f = lm + i * n_lm * lm_stride;
+    const float2 a = ld_xy<false>(f, anchors.x, lm_stride), c = ld_xy<false>(f, anchors.y, lm_stride);
+    const float mw = dist2f(a.x * w, a.y * h, c.x * w, c.y * h);
+    ok = mw >= gate_lo && mw <= gate_hi;
+  }
+  valid[i] = ok ? 1 : 0;
+}
+
+template <bool kVec2>
 __global__ void __launch_bounds__(128)
 features_kernel(const float* __restrict__ lm, int B, int T, int n_lm, int lm_stride,
                 const int* __restrict__ ids, int K, int4 anchors,
                 const uint8_t* __restrict__ present, float w, float h,
                 float gate_lo, float gate_hi, int compact, int frames_per_warp,
                 float* __restrict__ X, float* __restrict__ center, float* __restrict__ mouth_w,
-                uint8_t* __restrict__ valid, int64_t* __restrict__ lengths) {
+                uint8_t* __restrict__ valid, int64_t* __restrict__ lengths, float* __restrict__ xy_px) {
   const int lane = threadIdx.x & 31;
   const int runs_per_clip = (T + frames_per_warp - 1) / frames_per_warp;
   const int64_t warp_id = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -86,29 +117,22 @@ features_kernel(const float* __restrict__ lm, int B, int T, int n_lm, int lm_str
   const float* clip = lm + (int64_t)b * T * n_lm * lm_stride;
   const uint8_t* pres = present ? present + (int64_t)b * T : nullptr;
 
-  // Output row of frame t0 when compacting = number of usable frames before it.
+  // Output row of frame t0 when compacting = number of usable frames before it (pass 0 wrote the flags).
   int row = t0;
   if (compact) {
     int cnt = 0;
-    for (int t = lane; t < t0; t += 32) {
-      const float* f = clip + (int64_t)t * n_lm * lm_stride;
-      const float2 a = ld_xy(f, anchors.x, lm_stride);
-      const float2 c = ld_xy(f, anchors.y, lm_stride);
-      float mw = dist2f(a.x * w, a.y * h, c.x * w, c.y * h);
-      bool ok = (!pres || pres[t]) && mw >= gate_lo && mw <= gate_hi;
-      cnt += ok ? 1 : 0;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-    row = cnt;
+    for (int t = lane; t < t0; t += 32) cnt += valid[(int64_t)b * T + t];
+    row = __reduce_add_sync(0xffffffffu, cnt);
   }
 
-  float qx[kMaxPtsPerLane], qy[kMaxPtsPerLane];     // previous frame, normalised
+  float qx[kMaxPtsPerLane], qy[kMaxPtsPerLane];     // previous used frame, normalised
   bool have_prev = false;
-  if (t0 > 0) {
+  int tp = t0 - 1;                                  // last DETECTED frame before the run (absent frames are transparent)
+  while (tp >= 0 && pres && !pres[tp]) --tp;
+  if (tp >= 0) {
     float px[kMaxPtsPerLane], py[kMaxPtsPerLane];
-    const int t = t0 - 1;
-    FrameGeom g = load_frame(clip + (int64_t)t * n_lm * lm_stride, lm_stride, ids, K, lane, anchors,
+    const int t = tp;
+    FrameGeom g = load_frame<kVec2>(clip + (int64_t)t * n_lm * lm_stride, lm_stride, ids, K, lane, anchors,
                              w, h, !pres || pres[t], gate_lo, gate_hi, px, py);
     if (g.usable) {
       const float scale = (float)((double)g.mouth_w + 1e-6);
@@ -120,14 +144,16 @@ features_kernel(const float* __restrict__ lm, int B, int T, int n_lm, int lm_str
 
   for (int t = t0; t < t1; ++t) {
     float px[kMaxPtsPerLane], py[kMaxPtsPerLane];
-    FrameGeom g = load_frame(clip + (int64_t)t * n_lm * lm_stride, lm_stride, ids, K, lane, anchors,
+    FrameGeom g = load_frame<kVec2>(clip + (int64_t)t * n_lm * lm_stride, lm_stride, ids, K, lane, anchors,
                              w, h, !pres || pres[t], gate_lo, gate_hi, px, py);
-    if (valid && lane == 0) valid[(int64_t)b * T + t] = g.usable ? 1 : 0;
+    const bool detected = !pres || pres[t];
+    if (valid && !compact && lane == 0) valid[(int64_t)b * T + t] = g.usable ? 1 : 0;
     if (!g.usable) {
-      have_prev = false;                              // live_infer_official.py:294-296
+      if (detected) have_prev = false;                // live_infer_official.py:294-296: only a detected, out-of-band face resets
       if (!compact) {
         float* xr = X + ((int64_t)b * T + t) * D;
         for (int i = lane; i < D; i += 32) xr[i] = 0.f;
+        if (xy_px) for (int i = lane; i < 2 * K; i += 32) xy_px[((int64_t)b * T + t) * 2 * K + i] = 0.f;
         if (lane == 0) {
           if (center) { center[((int64_t)b * T + t) * 2] = 0.f; center[((int64_t)b * T + t) * 2 + 1] = 0.f; }
           if (mouth_w) mouth_w[(int64_t)b * T + t] = 0.f;
@@ -145,6 +171,7 @@ features_kernel(const float* __restrict__ lm, int B, int T, int n_lm, int lm_str
       const float nx = (px[j] - g.cx) / scale, ny = (py[j] - g.cy) / scale;   // live:153
       if (k < K) {
         *reinterpret_cast<float2*>(xr + 2 * k) = make_float2(nx, ny);
+        if (xy_px) *reinterpret_cast<float2*>(xy_px + (orow * K + k) * 2) = make_float2(px[j], py[j]);   // the gather itself (live:147)
         if (have_prev) vel_part += dist2f(nx, ny, qx[j], qy[j]);
       }
       qx[j] = nx; qy[j] = ny;
@@ -166,6 +193,7 @@ features_kernel(const float* __restrict__ lm, int B, int T, int n_lm, int lm_str
     for (int r = row; r < T; ++r) {
       float* xr = X + ((int64_t)b * T + r) * D;
       for (int i = lane; i < D; i += 32) xr[i] = 0.f;
+      if (xy_px) for (int i = lane; i < 2 * K; i += 32) xy_px[((int64_t)b * T + r) * 2 * K + i] = 0.f;
       if (lane == 0) {
         if (center) { center[((int64_t)b * T + r) * 2] = 0.f; center[((int64_t)b * T + r) * 2 + 1] = 0.f; }
         if (mouth_w) mouth_w[(int64_t)b * T + r] = 0.f;
@@ -181,22 +209,31 @@ extern "C" int ssb_features_fwd(const float* landmarks, int64_t B, int64_t T, in
                                 const uint8_t* present, float frame_w, float frame_h,
                                 float gate_min_px, float gate_max_px, int32_t compact,
                                 float* X, float* center, float* mouth_w, uint8_t* valid,
-                                int64_t* lengths, void* stream) {
+                                int64_t* lengths, float* xy_px, void* stream) {
   using namespace ssb;
   SSB_REQUIRE(landmarks && ids && X && anchor_ids, "null pointer");
   SSB_REQUIRE(B >= 0 && T >= 1 && n_lm >= 1, "bad shape");
   SSB_REQUIRE(lm_stride >= 2, "landmark stride must hold at least x,y");
   SSB_REQUIRE(K >= 1 && K <= 32 * kMaxPtsPerLane, "K must be in 1..128");
   for (int i = 0; i < 4; ++i) SSB_REQUIRE(anchor_ids[i] >= 0 && anchor_ids[i] < n_lm, "anchor id out of range");
+  SSB_REQUIRE(!compact || valid, "compact mode needs the valid buffer (pass 0 writes the flags it counts)");
   if (B == 0) return SSB_OK;
+  int4 anchors = make_int4(anchor_ids[0], anchor_ids[1], anchor_ids[2], anchor_ids[3]);
+  if (compact) {
+    const int64_t frames = B * T;
+    features_valid_kernel<<<(unsigned)cdiv(frames, 256), 256, 0, (cudaStream_t)stream>>>(
+        landmarks, frames, (int)n_lm, (int)lm_stride, anchors, present, frame_w, frame_h, gate_min_px, gate_max_px, valid);
+    SSB_LAUNCH_CHECK();
+  }
   const int frames_per_warp = 6;
   const int64_t warps = B * ((T + frames_per_warp - 1) / frames_per_warp);
   const int warps_per_block = 4;
   dim3 grid((unsigned)cdiv(warps, warps_per_block)), block(32 * warps_per_block);
-  int4 anchors = make_int4(anchor_ids[0], anchor_ids[1], anchor_ids[2], anchor_ids[3]);
-  features_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(
+  const bool vec2 = (lm_stride & 1) == 0 && (reinterpret_cast<uintptr_t>(landmarks) & 7) == 0;
+  auto kern = vec2 ? features_kernel<true> : features_kernel<false>;
+  kern<<<grid, block, 0, (cudaStream_t)stream>>>(
       landmarks, (int)B, (int)T, (int)n_lm, (int)lm_stride, ids, K, anchors, present, frame_w, frame_h,
-      gate_min_px, gate_max_px, compact, frames_per_warp, X, center, mouth_w, valid, lengths);
+      gate_min_px, gate_max_px, compact, frames_per_warp, X, center, mouth_w, valid, lengths, xy_px);
   SSB_LAUNCH_CHECK();
   return SSB_OK;
 }

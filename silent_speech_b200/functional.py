@@ -125,6 +125,11 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
 def classifier_forward(model, X, lengths, R=None, k_top: int = 0):
     if not X.is_cuda:
         raise ops._lib.SsbError("inputs must be CUDA tensors: this package has no CPU path")
+    with torch.cuda.device(X.device):          # kernels and streams follow the tensors, not the caller's current device
+        return _classifier_forward(model, X, lengths, R, k_top)
+
+
+def _classifier_forward(model, X, lengths, R, k_top):
     needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in model.parameters())
     if X.shape[0] == 0 and not k_top:          # empty batch: nothing to launch (the reference returns a [0, C] tensor too)
         z = torch.zeros(0, model.num_classes, device=X.device, dtype=torch.float32)

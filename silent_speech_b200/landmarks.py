@@ -35,7 +35,7 @@ def ids_tensor(device, idxs=None) -> torch.Tensor:
 
 
 def extract_features(landmarks: torch.Tensor, w: int, h: int, idxs=None, present: Optional[torch.Tensor] = None,
-                     gate=(MOUTH_W_MIN_PX, MOUTH_W_MAX_PX), compact: bool = False):
+                     gate=(MOUTH_W_MIN_PX, MOUTH_W_MAX_PX), compact: bool = False, want_xy_px: bool = False):
     """Batched form of ``extract_feature(face, w, h, idxs, prev_xy)`` (live_infer_official.py:146-169)
     plus the capture loop's gate / velocity reset (live:275-296).
 
@@ -43,9 +43,14 @@ def extract_features(landmarks: torch.Tensor, w: int, h: int, idxs=None, present
     present    u8 [B,T] face detected (None = all)
     gate       (min_px, max_px) band on the mouth width, None to disable
     compact    pack used frames to the front of each clip, as the reference's bufX does
-    returns    dict X [B,T,2K+4], center [B,T,2], mouth_w [B,T], valid [B,T], lengths [B]"""
-    return ops.features_fwd(landmarks, ids_tensor(landmarks.device, idxs), ANCHORS, float(w), float(h),
-                            present=present, gate=gate, compact=compact)
+    want_xy_px also return the gathered pixel positions xy_px [B,T,K,2] (`xy` of live:147, before any arithmetic)
+    returns    dict X [B,T,2K+4], center [B,T,2], mouth_w [B,T], valid [B,T], lengths [B]
+
+    An undetected frame (present = 0) is skipped without touching the velocity history; a detected face outside the
+    band is skipped and resets it (live:272-296: the reset sits inside ``if res.face_landmarks``)."""
+    with torch.cuda.device(landmarks.device):
+        return ops.features_fwd(landmarks, ids_tensor(landmarks.device, idxs), ANCHORS, float(w), float(h),
+                                present=present, gate=gate, compact=compact, want_xy_px=want_xy_px)
 
 
 class _Pt:
@@ -76,6 +81,5 @@ def crop_rois(frames, centers, mouth_w, flavor: str = "live", frame_index=None):
     record_landmarks_official.py:102-118) on the GPU: frames u8 [F,H,W,3] BGR, centers f32 [N,2] and mouth_w [N]
     as returned by extract_features -> (R u8 [N,48,96], ok u8 [N]); rows where the reference returns None are zero
     frames (what live_infer_official.py:290-293 substitutes)."""
-    import torch
-    from . import ops
-    return ops.roi_crop(frames, centers.contiguous().float(), mouth_w.to(torch.float64).contiguous(), flavor, frame_index)
+    with torch.cuda.device(frames.device):
+        return ops.roi_crop(frames, centers.contiguous().float(), mouth_w.to(torch.float64).contiguous(), flavor, frame_index)

@@ -130,7 +130,9 @@ class BiGRUClassifier(nn.Module):
         self.head.add_module("1", fc1)
         fc2 = _Bag(weight=(num_classes, 128), bias=(num_classes,)); _init_affine(fc2, 128)
         self.head.add_module("4", fc2)
-        self._seed = 0x5EED
+        # dropout-mask counter: follows torch.manual_seed like the reference's nn.Dropout / nn.GRU masks do; Trainer mixes
+        # in the data-parallel rank (every rank must draw its own masks) and checkpoints it (Trainer.state_dict)
+        self._seed = (0x5EED ^ (torch.initial_seed() * 0x9E3779B97F4A7C15)) & 0xFFFFFFFFFFFFFFFF
 
     # -- parameter groups in the order the C ABI takes them
     def head_tensors(self):
@@ -159,6 +161,10 @@ class BiGRUClassifier(nn.Module):
         dev = next(self.parameters()).device
         if dev.type != "cuda":
             raise F_ssb.ops._lib.SsbError("infer_host needs the model on a CUDA device (no CPU path)")
+        with torch.cuda.device(dev):
+            return self._infer_host(dev, X, lengths, R, chunk, out)
+
+    def _infer_host(self, dev, X, lengths, R, chunk, out):
         B = X.shape[0]
         use_roi = self.use_roi and R is not None
         if out is None:

@@ -38,8 +38,8 @@ def device_info():
 # ----------------------------------------------------------------------------- K1
 def features_fwd(landmarks: torch.Tensor, ids: torch.Tensor, anchor_ids: Sequence[int],
                  frame_w: float, frame_h: float, present: Optional[torch.Tensor] = None,
-                 gate=(60.0, 150.0), compact: bool = False):
-    """landmarks f32 [B,T,N,S>=2] -> dict(X [B,T,2K+4], center, mouth_w, valid, lengths)."""
+                 gate=(60.0, 150.0), compact: bool = False, want_xy_px: bool = False):
+    """landmarks f32 [B,T,N,S>=2] -> dict(X [B,T,2K+4], center, mouth_w, valid, lengths[, xy_px [B,T,K,2]])."""
     _need(landmarks, torch.float32, "landmarks")
     _need(ids, torch.int32, "ids")
     B, T, N, S = landmarks.shape
@@ -52,15 +52,21 @@ def features_fwd(landmarks: torch.Tensor, ids: torch.Tensor, anchor_ids: Sequenc
     mouth_w = torch.empty(B, T, device=dev, dtype=torch.float32)
     valid = torch.empty(B, T, device=dev, dtype=torch.uint8)
     lengths = torch.full((B,), T, device=dev, dtype=torch.int64)
+    xy_px = torch.empty(B, T, K, 2, device=dev, dtype=torch.float32) if want_xy_px else None
     lo, hi = (-float("inf"), float("inf")) if gate is None else gate
     anchors = (i32 * 4)(*[int(a) for a in anchor_ids])
     check(_lib.lib().ssb_features_fwd(ptr(landmarks), i64(B), i64(T), i64(N), i64(S), ptr(ids), i32(K), anchors,
                                       ptr(present), f32(frame_w), f32(frame_h), f32(lo), f32(hi),
                                       i32(1 if compact else 0), ptr(X), ptr(center), ptr(mouth_w), ptr(valid),
-                                      ptr(lengths), stream_ptr()))
-    if not compact:
+                                      ptr(lengths), ptr(xy_px), stream_ptr()))
+    if compact:
+        _lib._launches += 1          # compact mode enqueues two kernels (the usable-flag pass, then the features)
+    else:
         lengths = valid.sum(dim=1, dtype=torch.int64)
-    return {"X": X, "center": center, "mouth_w": mouth_w, "valid": valid, "lengths": lengths}
+    out = {"X": X, "center": center, "mouth_w": mouth_w, "valid": valid, "lengths": lengths}
+    if want_xy_px:
+        out["xy_px"] = xy_px
+    return out
 
 
 # ----------------------------------------------------------------------------- K2

@@ -5,7 +5,8 @@ points(+ROI) model:
 
     buf = deque(maxlen=max_t)                 # per stream
     every camera frame:  frame_idx += 1
-        face found -> buf.append(feature row)          (no face: nothing appended, live_feed.py:178-184)
+        no face found -> continue                      (nothing appended, NO prediction; live_feed.py:178-184)
+        buf.append(feature row)
         if len(buf) >= WARMUP_MIN and frame_idx % PRED_EVERY == 0:
             window = buf zero-padded to max_t ; logits = model(window, lengths=len(buf))
 
@@ -52,7 +53,9 @@ class WindowState:
         pos = self.head[a].copy()
         self.head[a] = (pos + 1) % self.W
         self.count[a] = np.minimum(self.count[a] + 1, self.W)
-        due = (self.count[ids] >= self.warmup_min) & (self.frame_idx[ids] % self.pred_every == 0)
+        # a frame without a face hits `continue` before the predict block (live_feed.py:178-184): it advances the frame
+        # counter but never produces a prediction, however full the window is
+        due = found & (self.count[ids] >= self.warmup_min) & (self.frame_idx[ids] % self.pred_every == 0)
         d = ids[due]
         cnt = self.count[d]
         return a, pos, d, (self.head[d] - cnt) % self.W, cnt
@@ -82,6 +85,10 @@ class StreamScheduler:
         X f32 [n, x_dim] feature rows, R u8 [n,48,96] mouth ROIs (ROI model), face_found bool [n] (default all).
         Returns (due_ids int64 ndarray [m], logits f32 [m,C] on the device) for the streams whose window was
         classified this tick (and top-k ids/probs instead of logits when k_top > 0)."""
+        with torch.cuda.device(self.dev):
+            return self._tick(stream_ids, X, R, face_found, k_top)
+
+    def _tick(self, stream_ids, X, R, face_found, k_top):
         ids = np.asarray(stream_ids, np.int64)
         n = ids.shape[0]
         found = np.ones(n, bool) if face_found is None else np.asarray(face_found, bool)

@@ -11,6 +11,8 @@ record_landmarks_official.py:30-46 (K=88 landmarks of 478).
 """
 from __future__ import annotations
 
+import math
+
 import numpy as np
 
 N_LANDMARKS = 478
@@ -95,3 +97,58 @@ def clip_batch(B: int, T: int = MAX_T, mode: str = "full", seed: int = 42, use_r
     L = lengths(B, T, mode, seed)
     return {"X": point_features(B, T, L, x_dim, seed), "lengths": L,
             "R": rois(B, T, L, seed) if use_roi else None, "y": labels(B, num_classes, seed)}
+
+
+# --------------------------------------------------------------------------
+# synthetic weights (no trained checkpoint is shipped: .MISSING_LARGE_BLOBS lists word_model_points_roi.pt)
+# --------------------------------------------------------------------------
+def param_shapes(x_dim: int = 180, num_classes: int = 10, use_roi: bool = True, roi_emb: int = 32, hidden: int = 192):
+    """State-dict names and shapes in the order the reference's ``state_dict()`` lists them
+    (TinyROICNN train_model_official.py:212-221, nn.GRU 261-267, AttnPool 236, head 271-277)."""
+    s = {}
+    if use_roi:
+        for idx, (co, ci) in (("0", (8, 1)), ("3", (16, 8)), ("6", (24, 16))):
+            s[f"roi_cnn.net.{idx}.weight"] = (co, ci, 3, 3)
+            s[f"roi_cnn.net.{idx}.bias"] = (co,)
+        s["roi_cnn.fc.weight"] = (roi_emb, 24)
+        s["roi_cnn.fc.bias"] = (roi_emb,)
+    for layer, width in ((0, x_dim + (roi_emb if use_roi else 0)), (1, 2 * hidden)):
+        for sfx in ("", "_reverse"):
+            s[f"gru.weight_ih_l{layer}{sfx}"] = (3 * hidden, width)
+            s[f"gru.weight_hh_l{layer}{sfx}"] = (3 * hidden, hidden)
+            s[f"gru.bias_ih_l{layer}{sfx}"] = (3 * hidden,)
+            s[f"gru.bias_hh_l{layer}{sfx}"] = (3 * hidden,)
+    s["pool.score.weight"] = (1, 2 * hidden)
+    s["pool.score.bias"] = (1,)
+    s["head.0.weight"] = (2 * hidden,)
+    s["head.0.bias"] = (2 * hidden,)
+    s["head.1.weight"] = (128, 2 * hidden)
+    s["head.1.bias"] = (128,)
+    s["head.4.weight"] = (num_classes, 128)
+    s["head.4.bias"] = (num_classes,)
+    return s
+
+
+def synth_params(seed: int, x_dim: int = 180, num_classes: int = 10, use_roi: bool = True, scale: float = 1.0):
+    """Machine-independent weights (numpy PCG64) with the reference constructor's default-init magnitudes:
+    U(+-1/sqrt(fan_in)) for convolutions / linears, U(+-1/sqrt(H)) for the GRU, LayerNorm near (1, 0) but perturbed.
+    -> {state-dict name: torch.float32 tensor}.  The same generator as the test oracle's (tests assert equality), kept
+    here so that bench.py and the examples never import test infrastructure."""
+    import torch
+    shapes = param_shapes(x_dim, num_classes, use_roi)
+    rng = np.random.default_rng(seed)
+    out = {}
+    for name, shp in shapes.items():
+        if name == "head.0.weight":
+            out[name] = torch.from_numpy(1.0 + 0.1 * rng.standard_normal(shp)).float()
+            continue
+        if name == "head.0.bias":
+            out[name] = torch.from_numpy(0.1 * rng.standard_normal(shp)).float()
+            continue
+        if name.startswith("gru."):
+            b = 1.0 / math.sqrt(192)
+        else:
+            wshape = shapes[name.rsplit(".", 1)[0] + ".weight"]
+            b = 1.0 / math.sqrt(int(np.prod(wshape[1:])))
+        out[name] = torch.from_numpy(rng.uniform(-b * scale, b * scale, size=shp)).float()
+    return out

@@ -73,22 +73,35 @@ class Trainer:
         self.model, self.lr, self.betas, self.eps = model, lr, betas, eps
         self.world, self.clip_norm, self.ls = world_size, clip_norm, label_smoothing
         self.dropout = dropout
+        self.rank = dist.get_rank() if (world_size > 1 and dist.is_available() and dist.is_initialized()) else 0
+        if self.rank:              # per-rank dropout masks: identical replicas would otherwise mask (clip i, t, j) alike
+            model._seed = (model._seed + 0xD1B54A32D192ED03 * self.rank) & 0xFFFFFFFFFFFFFFFF
         self.buckets = FlatBuckets(model)
         dev = self.buckets.param.device
         self.sqnorm = torch.zeros(1, device=dev, dtype=torch.float64)
         self.grad_norm = torch.zeros(1, device=dev, dtype=torch.float32)
         self.t = 0
         self.launches_per_step = 0
+        self.allreduce_events = None        # set to [] to collect one (start, end) CUDA-event pair per all-reduce
 
     def state_dict(self):
-        return {"step": self.t, "exp_avg": self.buckets.m.clone(), "exp_avg_sq": self.buckets.v.clone()}
+        """Optimiser state for resume: Adam step count and moments plus the model's dropout-mask counter, so that
+        two steps == one step + save/load + one step, bit for bit (tests/test_gpu_checkpoint.py)."""
+        return {"step": self.t, "exp_avg": self.buckets.m.clone(), "exp_avg_sq": self.buckets.v.clone(),
+                "dropout_seed": int(self.model._seed)}
 
     def load_state_dict(self, sd):
         self.t = int(sd["step"]); self.buckets.m.copy_(sd["exp_avg"]); self.buckets.v.copy_(sd["exp_avg_sq"])
+        if "dropout_seed" in sd:
+            self.model._seed = int(sd["dropout_seed"])
 
     def forward_backward(self, X, lengths, R, y, global_batch: Optional[int] = None):
         """Fills the flat gradient bucket with d(mean CE over the GLOBAL batch)/d(params) of the
         local shard; returns (per-clip loss [B_local], logits)."""
+        with torch.cuda.device(X.device):
+            return self._forward_backward(X, lengths, R, y, global_batch)
+
+    def _forward_backward(self, X, lengths, R, y, global_batch):
         model = self.model
         training = self.dropout and model.training
         y = y.to(device=X.device, dtype=torch.int64).contiguous()
@@ -103,13 +116,24 @@ class Trainer:
         """One full train step on this rank's shard; returns the local per-clip losses.
         augment_seed: apply NPZWordDataset's augmentation (train_model_official.py:143-152: noise p=0.7, 1-2 dropped
         frames p=0.35) to the batch on the device first; R is then cut in place to the new lengths."""
+        with torch.cuda.device(X.device):
+            return self._step(X, lengths, R, y, global_batch, augment_seed)
+
+    def _step(self, X, lengths, R, y, global_batch, augment_seed):
         c0 = _lib.launch_count()
         if augment_seed is not None:
             lengths = lengths.to(device=X.device, dtype=torch.int64).contiguous()
             X, lengths, _ = ops.augment_clips(X.contiguous().float(), lengths, R if self.model.use_roi else None, augment_seed)
-        loss, _ = self.forward_backward(X, lengths, R, y, global_batch)
+        loss, _ = self._forward_backward(X, lengths, R, y, global_batch)
         if self.world > 1:
+            ev = None
+            if self.allreduce_events is not None:
+                ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                ev[0].record()
             dist.all_reduce(self.buckets.grad, op=dist.ReduceOp.SUM)       # 4.76 MB over NVLink / NVSwitch
+            if ev is not None:
+                ev[1].record()
+                self.allreduce_events.append(ev)
         self.t += 1
         self.sqnorm.zero_()
         ops.grad_sqnorm(self.buckets.grad, self.sqnorm)

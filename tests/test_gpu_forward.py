@@ -57,12 +57,11 @@ def test_features_vs_golden_and_oracle(golden_dir):
     err = np.abs(X - ref).max() / np.abs(ref).max()
     assert err < 1e-5, err
     np.testing.assert_allclose(out["center"].cpu().numpy(), g["center_live"], rtol=1e-6, atol=1e-4)
-    # the gather itself is data movement: pixel positions recovered from the outputs must be
-    # the bit-exact products x*w, y*h of the selected landmarks
-    ids = g["ids"]
-    b, t = 0, int(np.argmax(g["valid_live"][0]))
-    px = g["lm"][b, t, ids, 0] * np.float32(g["w"])
-    assert np.array_equal(px.astype(np.float32), (g["lm"][b, t, ids, 0].astype(np.float64) * int(g["w"])).astype(np.float32))
+    # the gather itself is data movement (live:147): the kernel's gathered pixel positions must equal the reference's
+    # `xy` bit for bit -- on the golden clip (ids up to 436) ...
+    outp = extract_features(lm, int(g["w"]), int(g["h"]), present=present, want_xy_px=True)
+    assert np.array_equal(outp["xy_px"].cpu().numpy(), g["xy_px_live"])
+    assert np.array_equal(outp["X"].cpu().numpy(), X)                 # the extra output does not change the features
     # compact mode == the reference's bufX
     outc = extract_features(lm, int(g["w"]), int(g["h"]), present=present, compact=True)
     for b in range(lm.shape[0]):
@@ -72,6 +71,30 @@ def test_features_vs_golden_and_oracle(golden_dir):
         e = np.abs(outc["X"][b].cpu().numpy() - o["X"]).max() / np.abs(o["X"]).max()
         assert e < 1e-5, e
         assert np.all(outc["X"][b, n:].cpu().numpy() == 0)
+
+
+@pytest.mark.parametrize("lm_stride", [2, 3, 4])
+@pytest.mark.parametrize("compact", [False, True])
+def test_landmark_gather_bit_exact(lm_stride, compact):
+    """north_star: "landmark gather is bit-exact".  Seeded clips, landmark strides 2 (x,y), 3 (x,y,z) and 4, in place
+    and compacted: xy_px == float32(x * w), float32(y * h) of the selected ids, exactly (the oracle evaluates the
+    reference's expression `face[i].x * w` in Python floats and stores into a float32 array, live:147)."""
+    dev = _cuda()
+    from silent_speech_b200 import extract_features, synth
+    lm3, present = synth.landmarks(5, 23, seed=17, drop=0.1)
+    lm3[2, 7, 291, 0] += 0.3                                          # one detected frame outside the band
+    lm = np.zeros(lm3.shape[:3] + (lm_stride,), np.float32)
+    lm[..., :min(3, lm_stride)] = lm3[..., :min(3, lm_stride)]
+    out = extract_features(torch.from_numpy(lm).to(dev), synth.FRAME_W, synth.FRAME_H, present=torch.from_numpy(present).to(dev),
+                           compact=compact, want_xy_px=True)
+    for b in range(lm.shape[0]):
+        o = ref_features.clip_features(lm[b], synth.FRAME_W, synth.FRAME_H, present=present[b], compact=compact)
+        assert np.array_equal(out["xy_px"][b].cpu().numpy(), o["xy_px"]), (b, lm_stride, compact)
+        assert np.array_equal(out["valid"][b].cpu().numpy(), o["valid"])
+        e = np.abs(out["X"][b].cpu().numpy() - o["X"]).max() / np.abs(o["X"]).max()
+        assert e < 1e-5, e
+        if compact:
+            assert int(out["lengths"][b]) == o["length"]
 
 
 def test_features_larger_seeded():

@@ -31,7 +31,23 @@ def test_features_match_reference(golden_dir, flavour):
         assert np.array_equal(o["valid"], g[f"valid_{flavour}"][b])
         assert np.array_equal(o["X"], g[f"X_{flavour}"][b])          # same numpy ops -> bit-exact
         assert np.array_equal(o["center"], g[f"center_{flavour}"][b])
+        assert np.array_equal(o["xy_px"], g[f"xy_px_{flavour}"][b])   # the gather (live:147): pure data movement
     assert g["valid_live"].sum() < g["valid_live"].size              # gate / absent frames exercised
+    # the capture loop's history rule (live:272-296): a missed detection between two used frames does not reset the
+    # velocity (clip 0: frames 2 and 4 used, 3 undetected); an out-of-band face does, and a missed detection after it
+    # keeps the history empty (clip 1: frame 5 out of band, 6 undetected, 7 used)
+    K2 = 2 * 88
+    assert present[0, 3] == 0 and g["valid_live"][0, 2] and g["valid_live"][0, 4] and g["X_live"][0, 4, K2] > 0
+    assert present[1, 6] == 0 and not g["valid_live"][1, 5] and g["valid_live"][1, 7] and g["X_live"][1, 7, K2] == 0
+
+
+def test_product_synth_params_equal_the_oracles():
+    """bench.py and the examples take their weights from silent_speech_b200.synth (never from test infrastructure);
+    the fixtures were generated with the oracle's generator: they must be the same function."""
+    from silent_speech_b200 import synth
+    for kw in (dict(), dict(use_roi=False), dict(scale=2.0), dict(num_classes=7)):
+        a, b = ref_model.synth_params(11, **kw), synth.synth_params(11, **kw)
+        assert list(a) == list(b) and all(torch.equal(a[k], b[k]) for k in a)
 
 
 def _inputs(g):

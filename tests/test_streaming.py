@@ -18,8 +18,9 @@ def _simulate(S, W, pred_every, warmup, ticks, rng):
         events = []
         for i, f in zip(ids, found):
             frame_idx[i] += 1
-            if f:
-                bufs[i].append((t, int(i)))
+            if not f:
+                continue                                    # live_feed.py:178-184: "No face found" -> next camera frame
+            bufs[i].append((t, int(i)))
             if len(bufs[i]) >= warmup and frame_idx[i] % pred_every == 0:
                 events.append((int(i), list(bufs[i])))
         yield t, ids, found, events
@@ -75,8 +76,9 @@ def test_stream_scheduler_vs_oracle(use_roi):
         want_ids = []
         for i, f in zip(ids, found):
             frame_idx[i] += 1
-            if f:
-                bufs[i].append(t)
+            if not f:
+                continue                                    # no face: no append, no prediction (live_feed.py:178-184)
+            bufs[i].append(t)
             if len(bufs[i]) >= 5 and frame_idx[i] % 2 == 0:
                 want_ids.append(int(i))
         assert [int(x) for x in due] == want_ids
