@@ -129,8 +129,8 @@ int ssb_clip_adam_step(float* p, float* g, float* m, float* v, int64_t n, const 
 /* Counter-based dropout: y = x * keep(seed, i) / (1-p)  (nn.GRU inter-layer dropout, train:266). */
 int ssb_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, void* stream);
 
-/* K3a on the tensor cores: C[M,N] = [A1 | A2] . W[N, K1+K2]^T + bias with tcgen05.mma (bf16 operands
- * converted on the fly from fp32, fp32 accumulation in TMEM).  passes = 1: bf16; 3: split-bf16 (fp32 grade).
+/* K3a on the tensor cores: C[M,N] = [A1 | A2] . W[N, K1+K2]^T + bias with tcgen05.mma (fp16 operands
+ * converted on the fly from fp32, fp32 accumulation in TMEM).  passes = 1: fp16; 3: split-fp16 hi/lo x3 (fp32 grade).
  * The matmuls inside nn.GRU (train_model_official.py:261-267); A2 may be NULL. */
 int ssb_gemm_tc(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
                 const float* W, int64_t ldw, const float* bias, float* C, int64_t ldc,
@@ -152,7 +152,7 @@ int ssb_gemm_tcx(const float* A, int64_t sai, int64_t sak, const float* B, int64
 /* out[0] = max |x[i]| over n floats (device scalar; feeds ssb_gemm_tcx's a_amax). */
 int ssb_absmax(const float* x, int64_t n, float* out, void* stream);
 
-/* K3b on the tensor cores (cluster of 4 CTAs, W_hh resident in shared memory as bf16, tcgen05.mma per
+/* K3b on the tensor cores (cluster of 4 CTAs, W_hh resident in shared memory as fp16, tcgen05.mma per
  * step, h slices exchanged by bulk DSMEM copies).  Same semantics/layouts as ssb_gru_layer_fwd, except that
  * gi must already include b_ih + (b_hr, b_hz, 0) -- build that bias with ssb_gru_fold_bias and pass it to the
  * projection GEMM.  order (nullable) = clip index per batch slot (e.g. sorted by length). passes = 1 or 3.

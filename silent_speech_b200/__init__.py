@@ -9,7 +9,8 @@ from .model import BiGRUClassifier, load_classifier  # noqa: F401
 from .dataset import ClipStore, scan_clips, split_by_label  # noqa: F401
 from .legacy import GRUClassifier, MouthOpenDetector, load_word_model  # noqa: F401
 from .streaming import StreamScheduler  # noqa: F401
+from .live import ClipRecorder, classify_camera_clips, clips_from_camera, evaluate, top_confusions  # noqa: F401
 
 __all__ = ["BiGRUClassifier", "load_classifier", "extract_features", "extract_feature", "crop_rois", "FIXED_IDXS",
            "ClipStore", "scan_clips", "split_by_label", "StreamScheduler", "GRUClassifier", "MouthOpenDetector",
-           "load_word_model"]
+           "load_word_model", "ClipRecorder", "classify_camera_clips", "clips_from_camera", "evaluate", "top_confusions"]

@@ -127,8 +127,15 @@ features_kernel(const float* __restrict__ lm, int B, int T, int n_lm, int lm_str
 
   float qx[kMaxPtsPerLane], qy[kMaxPtsPerLane];     // previous used frame, normalised
   bool have_prev = false;
-  int tp = t0 - 1;                                  // last DETECTED frame before the run (absent frames are transparent)
-  while (tp >= 0 && pres && !pres[tp]) --tp;
+  // last DETECTED frame before the run (absent frames are transparent): one coalesced byte load + a ballot per 32 frames
+  int tp = pres ? -1 : t0 - 1;
+  if (pres) {
+    for (int base = t0 - 1; base >= 0 && tp < 0; base -= 32) {
+      const int t = base - lane;
+      const unsigned m = __ballot_sync(0xffffffffu, t >= 0 && pres[t] != 0);
+      if (m) tp = base - (__ffs(m) - 1);
+    }
+  }
   if (tp >= 0) {
     float px[kMaxPtsPerLane], py[kMaxPtsPerLane];
     const int t = tp;

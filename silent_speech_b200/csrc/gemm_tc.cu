@@ -4,9 +4,9 @@
 //   train_model_official.py:261-267; A1 = point features, A2 = ROI embedding: the concat of train:297
 //   is two K-segments of one product and is never materialised)
 //
-// Operands stay fp32 in HBM (the state-dict contract); each CTA converts its tiles to bf16 on the way
-// into shared memory, so there is no separate cast pass.  passes = 1: plain bf16 (rel. error ~2^-9 per
-// product); passes = 3: split-bf16, x = hi + lo, D += Ahi.Bhi + Ahi.Blo + Alo.Bhi (error ~2^-17, i.e. fp32
+// Operands stay fp32 in HBM (the state-dict contract); each CTA converts its tiles to fp16 on the way
+// into shared memory, so there is no separate cast pass.  passes = 1: plain fp16 (rel. error ~2^-12 per
+// product); passes = 3: split-fp16, x = hi + lo, D += Ahi.Bhi + Ahi.Blo + Alo.Bhi (error ~2^-22, i.e. fp32
 // parity grade).  One CTA = one 128 x 192 output tile (UMMA M=128, N=192, fp32 accumulators = 192 TMEM
 // columns), K in chunks of 64 through a 2-stage shared-memory ring; one elected thread issues the MMAs
 // and tcgen05.commit signals an mbarrier when a stage may be overwritten.
@@ -27,7 +27,7 @@ struct Tail {
   uint32_t tmem_base;
 };
 
-// rows x BK fp32 (global, row stride ld) -> bf16 hi (and lo) in the canonical no-swizzle K-major layout
+// rows x BK fp32 (global, row stride ld) -> fp16 hi (and lo) in the canonical no-swizzle K-major layout
 template <int ROWS, bool kSplit>
 __device__ __forceinline__ void stage_operand(const float* __restrict__ src, int64_t ld, int rows_valid, int k_valid,
                                               uint8_t* hi, uint8_t* lo, int tid) {
@@ -47,14 +47,14 @@ __device__ __forceinline__ void stage_operand(const float* __restrict__ src, int
     if (kSplit) {
       float h[8], l[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) tc::split_bf16(x[j], h[j], l[j]);
-      *reinterpret_cast<uint4*>(hi + off) = make_uint4(tc::pack_bf16(h[0], h[1]), tc::pack_bf16(h[2], h[3]),
-                                                       tc::pack_bf16(h[4], h[5]), tc::pack_bf16(h[6], h[7]));
-      *reinterpret_cast<uint4*>(lo + off) = make_uint4(tc::pack_bf16(l[0], l[1]), tc::pack_bf16(l[2], l[3]),
-                                                       tc::pack_bf16(l[4], l[5]), tc::pack_bf16(l[6], l[7]));
+      for (int j = 0; j < 8; ++j) tc::split_f16(x[j], h[j], l[j]);
+      *reinterpret_cast<uint4*>(hi + off) = make_uint4(tc::pack_f16(h[0], h[1]), tc::pack_f16(h[2], h[3]),
+                                                       tc::pack_f16(h[4], h[5]), tc::pack_f16(h[6], h[7]));
+      *reinterpret_cast<uint4*>(lo + off) = make_uint4(tc::pack_f16(l[0], l[1]), tc::pack_f16(l[2], l[3]),
+                                                       tc::pack_f16(l[4], l[5]), tc::pack_f16(l[6], l[7]));
     } else {
-      *reinterpret_cast<uint4*>(hi + off) = make_uint4(tc::pack_bf16(x[0], x[1]), tc::pack_bf16(x[2], x[3]),
-                                                       tc::pack_bf16(x[4], x[5]), tc::pack_bf16(x[6], x[7]));
+      *reinterpret_cast<uint4*>(hi + off) = make_uint4(tc::pack_f16(x[0], x[1]), tc::pack_f16(x[2], x[3]),
+                                                       tc::pack_f16(x[4], x[5]), tc::pack_f16(x[6], x[7]));
     }
   }
 }
@@ -84,7 +84,7 @@ gemm_tc_kernel(const float* __restrict__ A1, int64_t lda1, int K1, const float* 
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = tail.tmem_base;
-  constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN);
+  constexpr uint32_t idesc = tc::make_idesc_f16(BM, BN);
 
   const int chunks1 = (K1 + BK - 1) / BK, chunks2 = A2 ? (K2 + BK - 1) / BK : 0;
   const int chunks = chunks1 + chunks2;
@@ -110,13 +110,13 @@ gemm_tc_kernel(const float* __restrict__ A1, int64_t lda1, int K1, const float* 
       for (int j = 0; j < ksteps; ++j) {
         const uint64_t dah = tc::make_desc(tc::smem_u32(a_hi) + j * 2 * LBO, LBO, SBO);
         const uint64_t dbh = tc::make_desc(tc::smem_u32(b_hi) + j * 2 * LBO, LBO, SBO);
-        tc::mma_bf16(tmem, dah, dbh, idesc, !first);
+        tc::mma_f16(tmem, dah, dbh, idesc, !first);
         first = false;
         if (kSplit) {
           const uint64_t dal = tc::make_desc(tc::smem_u32(a_lo) + j * 2 * LBO, LBO, SBO);
           const uint64_t dbl = tc::make_desc(tc::smem_u32(b_lo) + j * 2 * LBO, LBO, SBO);
-          tc::mma_bf16(tmem, dah, dbl, idesc, true);
-          tc::mma_bf16(tmem, dal, dbh, idesc, true);
+          tc::mma_f16(tmem, dah, dbl, idesc, true);
+          tc::mma_f16(tmem, dal, dbh, idesc, true);
         }
       }
       tc::mma_commit(&tail.bar[s]);
@@ -164,7 +164,7 @@ gemm_tc_kernel(const float* __restrict__ A1, int64_t lda1, int K1, const float* 
 }  // namespace gemmtc
 }  // namespace ssb
 
-// Tensor-core projection GEMM; see the header comment.  passes = 1 (bf16) or 3 (split-bf16, fp32 grade).
+// Tensor-core projection GEMM; see the header comment.  passes = 1 (fp16) or 3 (split-fp16, fp32 grade).
 // Requirements: lda*, ldw, K1, K2 multiples of 4 floats and 16-byte aligned bases (true for 180/32/212/384).
 extern "C" int ssb_gemm_tc(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
                            const float* W, int64_t ldw, const float* bias, float* C, int64_t ldc,

@@ -65,8 +65,8 @@ __global__ void prepack_kernel(const float* __restrict__ Wa, const float* __rest
     }
     const int nt = n / BN, r = n % BN, kb = c / (KB / 8), kc = c % (KB / 8);
     uint8_t* dst = packed + ((size_t)(nt * nkb + kb)) * W_BLOCK + kc * CHUNK + (r >> 3) * 128 + (r & 7) * 16;
-    *reinterpret_cast<uint4*>(dst) = make_uint4(tc::pack_bf16(x[0], x[1]), tc::pack_bf16(x[2], x[3]),
-                                                tc::pack_bf16(x[4], x[5]), tc::pack_bf16(x[6], x[7]));
+    *reinterpret_cast<uint4*>(dst) = make_uint4(tc::pack_f16(x[0], x[1]), tc::pack_f16(x[2], x[3]),
+                                                tc::pack_f16(x[4], x[5]), tc::pack_f16(x[6], x[7]));
   }
 }
 
@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
   tc::fence_after_sync();
   const uint32_t tmem = ctl.tmem_base;
   const uint32_t a_u = tc::smem_u32(a_s), w_u = tc::smem_u32(w_s);
-  constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN);
+  constexpr uint32_t idesc = tc::make_idesc_f16(BM, BN);
   uint32_t w_it = 0, acc_it = 0;                             // running weight-block / accumulator counters (ring phases)
 
   const int m_tiles = (a.M + BM - 1) / BM;
@@ -147,8 +147,8 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
 #pragma unroll
         for (int u = 0; u < NB; ++u)
           if (dst[u] != 0xffffffffu)
-            *reinterpret_cast<uint4*>(a_s + dst[u]) = make_uint4(tc::pack_bf16(v0[u].x, v0[u].y), tc::pack_bf16(v0[u].z, v0[u].w),
-                                                                 tc::pack_bf16(v1[u].x, v1[u].y), tc::pack_bf16(v1[u].z, v1[u].w));
+            *reinterpret_cast<uint4*>(a_s + dst[u]) = make_uint4(tc::pack_f16(v0[u].x, v0[u].y), tc::pack_f16(v0[u].z, v0[u].w),
+                                                                 tc::pack_f16(v1[u].x, v1[u].y), tc::pack_f16(v1[u].z, v1[u].w));
       }
     }
     tc::fence_async_smem();
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
             for (int j = 0; j < KB / 16; ++j) {
               const uint64_t da = tc::make_desc(a_u + (kb * (KB / 8) + 2 * j) * CHUNK, CHUNK, 128);
               const uint64_t db = tc::make_desc(w_u + s * W_BLOCK + 2 * j * CHUNK, CHUNK, 128);
-              tc::mma_bf16(tmem + buf * BN, da, db, idesc, (kb | j) != 0);
+              tc::mma_f16(tmem + buf * BN, da, db, idesc, (kb | j) != 0);
             }
             tc::mma_commit(&ctl.empty[s]);
           }
@@ -233,8 +233,8 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
                 const float4 o1 = *reinterpret_cast<const float4*>(tile + r * TILE_LD + 8 * c8 + 4);
                 if ((live_mask >> r) & 1u)
                   *reinterpret_cast<uint4*>(c + (int64_t)r * a.ldc) =
-                      make_uint4(tc::pack_bf16(o0.x + b0.x, o0.y + b0.y), tc::pack_bf16(o0.z + b0.z, o0.w + b0.w),
-                                 tc::pack_bf16(o1.x + b1.x, o1.y + b1.y), tc::pack_bf16(o1.z + b1.z, o1.w + b1.w));
+                      make_uint4(tc::pack_f16(o0.x + b0.x, o0.y + b0.y), tc::pack_f16(o0.z + b0.z, o0.w + b0.w),
+                                 tc::pack_f16(o1.x + b1.x, o1.y + b1.y), tc::pack_f16(o1.z + b1.z, o1.w + b1.w));
               }
             }
             __syncwarp();

@@ -50,11 +50,11 @@ struct Tail {
 __device__ __forceinline__ void split_store(const float (&x)[8], float scale, uint8_t* hi, uint8_t* lo, uint32_t off) {
   float h[8], l[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) tc::split_bf16(x[j] * scale, h[j], l[j]);
-  *reinterpret_cast<uint4*>(hi + off) = make_uint4(tc::pack_bf16(h[0], h[1]), tc::pack_bf16(h[2], h[3]),
-                                                   tc::pack_bf16(h[4], h[5]), tc::pack_bf16(h[6], h[7]));
-  *reinterpret_cast<uint4*>(lo + off) = make_uint4(tc::pack_bf16(l[0], l[1]), tc::pack_bf16(l[2], l[3]),
-                                                   tc::pack_bf16(l[4], l[5]), tc::pack_bf16(l[6], l[7]));
+  for (int j = 0; j < 8; ++j) tc::split_f16(x[j] * scale, h[j], l[j]);
+  *reinterpret_cast<uint4*>(hi + off) = make_uint4(tc::pack_f16(h[0], h[1]), tc::pack_f16(h[2], h[3]),
+                                                   tc::pack_f16(h[4], h[5]), tc::pack_f16(h[6], h[7]));
+  *reinterpret_cast<uint4*>(lo + off) = make_uint4(tc::pack_f16(l[0], l[1]), tc::pack_f16(l[2], l[3]),
+                                                   tc::pack_f16(l[4], l[5]), tc::pack_f16(l[6], l[7]));
 }
 
 // One operand tile of ROWS output indices x BK contraction indices, held in registers between load and store.
@@ -132,7 +132,7 @@ gemm_tcx_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = tail.tmem_base;
-  constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN);
+  constexpr uint32_t idesc = tc::make_idesc_f16(BM, BN);
   float a_scale = 1.f, c_scale = 1.f;                   // power of two that lifts max|A| into [2048, 4096), and its inverse
   if (a_amax) {
     const float mx = __ldg(a_amax);
@@ -171,9 +171,9 @@ gemm_tcx_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
         const uint64_t dbh = tc::make_desc(tc::smem_u32(b_hi) + j * 2 * LBO, LBO, SBO);
         const uint64_t dal = tc::make_desc(tc::smem_u32(a_lo) + j * 2 * LBO, LBO, SBO);
         const uint64_t dbl = tc::make_desc(tc::smem_u32(b_lo) + j * 2 * LBO, LBO, SBO);
-        tc::mma_bf16(tmem, dah, dbh, idesc, !first);
-        tc::mma_bf16(tmem, dah, dbl, idesc, true);
-        tc::mma_bf16(tmem, dal, dbh, idesc, true);
+        tc::mma_f16(tmem, dah, dbh, idesc, !first);
+        tc::mma_f16(tmem, dah, dbl, idesc, true);
+        tc::mma_f16(tmem, dal, dbh, idesc, true);
         first = false;
       }
       tc::mma_commit(&tail.bar[s]);

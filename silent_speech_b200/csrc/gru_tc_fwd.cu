@@ -2,15 +2,15 @@
 //
 // Same semantics as gru_fwd.cu (packed-sequence nn.GRU, train_model_official.py:261-267, 301-305).
 // W_hh (576x192) does not fit one SM, so a cluster of 4 CTAs splits the 192 hidden units: CTA `rank`
-// owns units 48*rank..+47, i.e. 144 gate rows of W_hh, resident in shared memory as bf16 for the whole
+// owns units 48*rank..+47, i.e. 144 gate rows of W_hh, resident in shared memory as fp16 for the whole
 // sequence.  Per step every CTA computes D[128 clips x 144] = h[128 x 192] . W_slice^T with tcgen05.mma
 // (fp32 accumulators in TMEM), applies the gate non-linearities to its 48 units in registers (fp32
-// master copy of h stays in registers), writes the new h slice as bf16 into its own A-operand buffer and
+// master copy of h stays in registers), writes the new h slice as fp16 into its own A-operand buffer and
 // pushes that 12 KB slice to the three peers with ONE bulk DSMEM copy each (cp.async.bulk
 // shared::cta -> shared::cluster) that completes on the peer's mbarrier.  No cluster-wide barrier in the
 // loop: `full` (bytes landed) and `empty` (peer's MMA finished reading) mbarriers carry the dependencies.
 //
-// kSplit = false: bf16 operands (fast mode).  kSplit = true: split-bf16 (h = hi + lo, W = hi + lo,
+// kSplit = false: fp16 operands (fast mode).  kSplit = true: split-fp16 (h = hi + lo, W = hi + lo,
 // D += Ahi.Bhi + Ahi.Blo + Alo.Bhi) -- fp32-parity grade.
 //
 // gi must carry b_ih + (b_hr, b_hz, 0): the r/z parts of b_hh are folded into the projection bias
@@ -153,7 +153,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   const float* __restrict__ whh = dir ? whh_r : whh_f;
   const float* __restrict__ bhn = dir ? bhn_r : bhn_f;
 
-  // ---- one-time: W_hh slice -> bf16 (hi, lo) in the canonical K-major layout; h = 0
+  // ---- one-time: W_hh slice -> fp16 (hi, lo) in the canonical K-major layout; h = 0
   for (int p = tid; p < NG * KCH; p += THREADS) {
     const int n = p / KCH, kc = p % KCH;
     const int g = n / U, u = n % U;
@@ -163,12 +163,12 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
     const uint32_t off = kc * B_LBO + (n >> 3) * 128 + (n & 7) * 16;
     float hh[8], ll[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) tc::split_bf16(x[j], hh[j], ll[j]);
-    *reinterpret_cast<uint4*>(b_hi + off) = make_uint4(tc::pack_bf16(hh[0], hh[1]), tc::pack_bf16(hh[2], hh[3]),
-                                                       tc::pack_bf16(hh[4], hh[5]), tc::pack_bf16(hh[6], hh[7]));
+    for (int j = 0; j < 8; ++j) tc::split_f16(x[j], hh[j], ll[j]);
+    *reinterpret_cast<uint4*>(b_hi + off) = make_uint4(tc::pack_f16(hh[0], hh[1]), tc::pack_f16(hh[2], hh[3]),
+                                                       tc::pack_f16(hh[4], hh[5]), tc::pack_f16(hh[6], hh[7]));
     if (kSplit)
-      *reinterpret_cast<uint4*>(b_lo + off) = make_uint4(tc::pack_bf16(ll[0], ll[1]), tc::pack_bf16(ll[2], ll[3]),
-                                                         tc::pack_bf16(ll[4], ll[5]), tc::pack_bf16(ll[6], ll[7]));
+      *reinterpret_cast<uint4*>(b_lo + off) = make_uint4(tc::pack_f16(ll[0], ll[1]), tc::pack_f16(ll[2], ll[3]),
+                                                         tc::pack_f16(ll[4], ll[5]), tc::pack_f16(ll[6], ll[7]));
   }
   for (int i = tid; i < A_BYTES / 16; i += THREADS) {
     reinterpret_cast<uint4*>(a_hi)[i] = make_uint4(0, 0, 0, 0);
@@ -205,7 +205,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   const uint32_t tmem = ctl.tmem_base;
   tc::cluster_sync_all();                        // every CTA's barriers exist before any remote operation
 
-  constexpr uint32_t idesc = tc::make_idesc_bf16(BM, NG);
+  constexpr uint32_t idesc = tc::make_idesc_f16(BM, NG);
   constexpr uint32_t kTxBytes = (CL - 1) * SLICE * (kSplit ? 2 : 1);
 
   if (warp == EPI_THREADS / 32) {
@@ -233,12 +233,12 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
         for (int j = 0; j < H / 16; ++j) {
           const uint64_t dah = tc::make_desc(tc::smem_u32(a_hi) + j * 2 * A_LBO, A_LBO, 128);
           const uint64_t dbh = tc::make_desc(tc::smem_u32(b_hi) + j * 2 * B_LBO, B_LBO, 128);
-          tc::mma_bf16(tmem, dah, dbh, idesc, j > 0);
+          tc::mma_f16(tmem, dah, dbh, idesc, j > 0);
           if (kSplit) {
             const uint64_t dal = tc::make_desc(tc::smem_u32(a_lo) + j * 2 * A_LBO, A_LBO, 128);
             const uint64_t dbl = tc::make_desc(tc::smem_u32(b_lo) + j * 2 * B_LBO, B_LBO, 128);
-            tc::mma_bf16(tmem, dah, dbl, idesc, true);
-            tc::mma_bf16(tmem, dal, dbh, idesc, true);
+            tc::mma_f16(tmem, dah, dbl, idesc, true);
+            tc::mma_f16(tmem, dal, dbh, idesc, true);
           }
         }
         tc::mma_commit(&ctl.mma_done);
@@ -414,12 +414,12 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
           const uint32_t off = (uint32_t)((rank * U + ug * UT + c * 8) >> 3) * A_LBO + a_row_off;
           float hh[8], ll[8];
 #pragma unroll
-          for (int q = 0; q < 8; ++q) tc::split_bf16(h[c * 8 + q], hh[q], ll[q]);
-          *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(tc::pack_bf16(hh[0], hh[1]), tc::pack_bf16(hh[2], hh[3]),
-                                                             tc::pack_bf16(hh[4], hh[5]), tc::pack_bf16(hh[6], hh[7]));
+          for (int q = 0; q < 8; ++q) tc::split_f16(h[c * 8 + q], hh[q], ll[q]);
+          *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(tc::pack_f16(hh[0], hh[1]), tc::pack_f16(hh[2], hh[3]),
+                                                             tc::pack_f16(hh[4], hh[5]), tc::pack_f16(hh[6], hh[7]));
           if (kSplit)
-            *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(tc::pack_bf16(ll[0], ll[1]), tc::pack_bf16(ll[2], ll[3]),
-                                                               tc::pack_bf16(ll[4], ll[5]), tc::pack_bf16(ll[6], ll[7]));
+            *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(tc::pack_f16(ll[0], ll[1]), tc::pack_f16(ll[2], ll[3]),
+                                                               tc::pack_f16(ll[4], ll[5]), tc::pack_f16(ll[6], ll[7]));
         }
       }
       tc::fence_async_smem();                                    // slice visible to the async proxy (MMA, bulk copy)
@@ -476,7 +476,7 @@ extern "C" int ssb_gru_fold_bias(const float* bih_f, const float* bhh_f, const f
 // Tensor-core recurrence of one bidirectional layer.  gi [B,T,gi_ld] must already contain
 // b_ih + (b_hr, b_hz, 0) (ssb_gru_fold_bias); bhh_* are the full b_hh vectors (the n part is read).
 // order (nullable) = clip index per batch slot, e.g. sorted by length so that tiles are homogeneous.
-// passes = 1 (bf16) or 3 (split-bf16).  Output / gates layouts as ssb_gru_layer_fwd.
+// passes = 1 (fp16) or 3 (split-fp16).  Output / gates layouts as ssb_gru_layer_fwd.
 // gi_layout: 0 = columns [dir][gate][192]; 1 = GRU-blocked [dir][rank][gate][48] as written through
 // ssb_proj_prepack(.., gru_blocked = 1) + ssb_gru_fold_bias(.., gru_blocked = 1) (passes = 1, gates = NULL only);
 // 2 = the same order stored as fp16 (ssb_proj_gemm out_half = 1), double-buffered staging.

@@ -1,12 +1,20 @@
-// K2 v3 -- fused mouth-ROI CNN forward, all three convolutions on tcgen05, pooling folded into N (the v2
-// formulation below), re-organised for latency hiding: in fp16 mode FOUR independent frame slots of 128 threads
-// per CTA (one warp per TMEM lane quarter, one MMA-issuing thread per slot -- concurrent issuers reach ~40 cycles
-// per small-N MMA per SM against ~70 for a single issuer, profiles/microbench), frames handed out dynamically by
-// an atomic counter, the next frame's pixels prefetched into registers while the current one is in the tensor
-// core, all per-thread addressing hoisted out of the frame loop, and conv2's tiles committed one by one so the
-// epilogue of tile i overlaps the MMAs of tile i+1.
+// K2 v4 -- fused mouth-ROI CNN forward, all three convolutions on tcgen05, pooling folded into N.
 //
 // Arithmetic contract: train_model_official.py:286-294 + TinyROICNN (209-229); live semantics with standardize=0.
+//
+// Frame staging (r2): every frame slot owns a 4,608-byte shared-memory buffer that ONE `cp.async.bulk` (TMA, 1-D) fills
+// with the raw u8 frame straight from HBM, completing on the slot's mbarrier; the copy of a slot's NEXT frame is issued
+// as soon as the current frame's pixels have been consumed and travels under the rest of the frame (conv1 tail, conv2,
+// conv3).  Frames are handed out by an atomic counter; padded frames (t >= lengths[b]) are skipped by the acquiring warp,
+// which writes their zero embeddings itself.
+//
+// conv1 on EXACT inputs (r2): u8 pixels are exactly representable in fp16, so the A operand of conv1 is the RAW pixel
+// patch (built from the staged bytes with two PRMTs and two HSUB2 per four pixels, no fp32 arithmetic) and the per-frame
+// standardisation moves into the epilogue:  conv(w, (x - mu)/sigma) = (conv(w, x_raw) - mu * ws) / sigma, where ws is the
+// sum of the weights over the taps that fall inside the frame (a 3 x 3 table of border classes per output channel; zero
+// padding of the STANDARDISED frame means "mu" outside the raw one).  In split mode that removes the activation's lo part
+// and one of the two conv1 MMAs; in both modes it removes the standardised plane, the patch gather from it and a
+// synchronisation.  The fp32 statistics are exact integers (64-bit N*S2 - S1^2) as before.
 //
 // The two pooled convolutions are computed per POOLED pixel: the 2x2 window of conv outputs that a max-pool
 // cell covers depends on one 4x4 input patch, so the four sub-positions become four groups of output columns
@@ -20,11 +28,13 @@
 // pixel); conv2's input is kept in four (row parity, column parity) planes so that "pooled pixel m -> patch
 // element (r,c)" is base(r,c) + 16*m, i.e. a legal canonical K-major operand with SBO = 128 and one k-chunk
 // per patch element; a K=16 MMA takes two patch elements whose planes are LBO apart.  conv1's patches (32 B per
-// pooled pixel) are gathered from the standardised fp16 frame, 3 tiles (384 pooled pixels) at a time.
+// pooled pixel) are built two tiles (256 pooled pixels) at a time into a double buffer: the patches of round r+1 are
+// written while the tensor core works on round r.
 //
-// One CTA hosts kSlots independent "frame slots" of 256 threads (named barriers, own TMEM columns, own
-// activation buffers) that share one copy of the weight operands; while one slot waits for its MMAs the
-// other computes.  kSplit: operands are fp16 hi + lo; D += Ahi.Bhi + Ahi.Blo + Alo.Bhi (fp32-parity grade).
+// One CTA hosts kSlots independent "frame slots" (named barriers, own TMEM columns, own activation buffers) that share
+// one copy of the weight operands; while one slot waits for its MMAs the others compute.  fp16 mode: four 128-thread
+// slots; kSplit: two 256-thread slots, operands are fp16 hi + lo and D += Ahi.Bhi + Ahi.Blo + Alo.Bhi (fp32-parity grade;
+// conv1: x.Whi + x.Wlo with x exact).
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -38,30 +48,33 @@ constexpr int C3 = 24, C3P = 32, E = 32;
 // Training: activations handed to the backward kernel instead of being recomputed there (one record per frame, the
 // layout ssb_roi_cnn_bwd reads -- see roi_cnn.cuh: SAVED_*).
 constexpr int SV_A1 = 0, SV_A2 = 36864, SV_IDX1 = 55296, SV_IDX2 = 57600, SV_MASK3 = 58752, SV_MEAN3 = 59904, SV_BYTES = 60000;
-constexpr int PIX_LD = 100, PIX_ROWS = 50;             // standardised frame, fp16, interior at [1..48][1..96]
-constexpr int PIX_BYTES = PIX_ROWS * PIX_LD * 2;       // 10,000
+constexpr int RING_BYTES = NPIX;                       // raw u8 frame staged by one bulk copy
+constexpr int C1_ROUNDS = 5, C1_TPR = 2;               // conv1: 9 tiles in rounds of 2 (last round: 1)
+constexpr int PATCH_PX = C1_TPR * 128;                 // pooled pixels per round
+constexpr int PATCH_CHUNK = PATCH_PX * 16;             // 4,096: one k-chunk (two patch rows) of a round
+constexpr int PATCH_BUF = 2 * PATCH_CHUNK;             // 8,192 per round; two rounds in flight
+constexpr int PATCH_BYTES = 2 * PATCH_BUF;             // 16,384
 constexpr int P1_ROWS = 13, P1_COLS = 25;              // a1 parity plane: [13][25] pixels x 16 B
 constexpr int P1_PLANE = P1_ROWS * P1_COLS * 16;       // 5,200
 constexpr int A1_BYTES = 4 * P1_PLANE;                 // 20,800
 constexpr int PITCH2 = 26, ROWS2 = 18;                 // a2: 2 channel planes x [18][26] pixels x 16 B (as in v1)
 constexpr int PLANE2 = ROWS2 * PITCH2 * 16;            // 7,488
 constexpr int A2_BYTES = 2 * PLANE2;                   // 14,976
-constexpr int W1_CHUNK = 32 * 16, W2_CHUNK = 64 * 16;  // bytes per k-chunk of the weight operands
-constexpr int W1_BYTES = 2 * W1_CHUNK, W2_BYTES = 16 * W2_CHUNK;   // 1,024 and 16,384 per part
+constexpr int W2_CHUNK = 64 * 16;                      // bytes per k-chunk of the conv2 weight operand
+constexpr int W2_BYTES = 16 * W2_CHUNK;                // 16,384 per part
 
 template <bool kSplit>
 struct Lay {
   static constexpr int P = kSplit ? 2 : 1;
-  static constexpr int STRIP_TILES = kSplit ? 2 : 3;   // conv1 tiles (128 pooled pixels each) gathered per round
-  static constexpr int PATCH_CHUNK = STRIP_TILES * 128 * 16, PATCH_BYTES = 2 * PATCH_CHUNK;
   static constexpr int W3_ROWS = kSplit ? 64 : 32;     // conv3 keeps hi|lo stacked along N (v1 scheme)
   static constexpr int W3_CHUNK = W3_ROWS * 16, W3_BYTES = 18 * W3_CHUNK;
-  // per-slot region R0: {standardised frame, conv1 patches} during conv1, a2 afterwards
-  static constexpr int R0_A = P * (PIX_BYTES + PATCH_BYTES), R0_B = P * A2_BYTES;
+  static constexpr int W1_ROWS = kSplit ? 64 : 32;     // conv1 weights: hi|lo stacked along N in split mode (the input is exact)
+  static constexpr int W1_CHUNK = W1_ROWS * 16, W1_BYTES = 2 * W1_CHUNK;
+  // per-slot region R0: conv1 patch double buffer during conv1, a2 afterwards
+  static constexpr int R0_A = PATCH_BYTES, R0_B = P * A2_BYTES;
   static constexpr int R0_BYTES = ((R0_A > R0_B ? R0_A : R0_B) + 127) / 128 * 128;
   static constexpr int A1_ALLOC = (P * A1_BYTES + 1408 + 127) / 128 * 128;    // + over-read slack of the last conv2 tile (1,360 B)
-  static constexpr int SLOT_BYTES = R0_BYTES + A1_ALLOC;
-  static constexpr int OFF_PIX = 0, OFF_PATCH = P * PIX_BYTES;
+  static constexpr int SLOT_BYTES = RING_BYTES + R0_BYTES + A1_ALLOC;
 };
 
 struct SlotMisc {
@@ -69,6 +82,7 @@ struct SlotMisc {
 
   uint32_t red[16];
   uint64_t bar[3];
+  uint64_t rbar;                                       // frame ring: the bulk copy's bytes complete here
   long long next;                                      // next frame of this slot (dynamic hand-out)
 };
 
@@ -76,6 +90,7 @@ struct Shared {                                        // one per CTA, after the
   alignas(16) float b1[C1];
   alignas(16) float b2[C2];
   alignas(16) float b3[C3P];
+  alignas(16) float ws1[9][C1];                        // conv1: sum of the effective weights over the in-frame taps, per border class
   float wfc[E][C3];
   float bfc[E];
   uint32_t tmem_base;
@@ -86,7 +101,7 @@ struct Weights {
 };
 
 __device__ __forceinline__ uint4 pack8(const float* v) {
-  return make_uint4(tc::pack_bf16(v[0], v[1]), tc::pack_bf16(v[2], v[3]), tc::pack_bf16(v[4], v[5]), tc::pack_bf16(v[6], v[7]));
+  return make_uint4(tc::pack_f16(v[0], v[1]), tc::pack_f16(v[2], v[3]), tc::pack_f16(v[4], v[5]), tc::pack_f16(v[6], v[7]));
 }
 template <int ST>
 __device__ __forceinline__ void slot_sync(int slot) { asm volatile("bar.sync %0, %1;\n" ::"r"(slot + 1), "n"(ST) : "memory"); }
@@ -103,12 +118,12 @@ __device__ __forceinline__ void build_weights(uint8_t* w1op, uint8_t* w2op, uint
     for (int e = 0; e < 8; ++e) {
       const int r = kc * 2 + (e >> 2), c = e & 3, dy = r - i, dx = c - j;
       const float w = (dy >= 0 && dy < 3 && dx >= 0 && dx < 3) ? g.w1[co * 9 + dy * 3 + dx] : 0.f;
-      tc::split_bf16(w, hi[e], lo[e]);
+      tc::split_f16(w, hi[e], lo[e]);
     }
-    // split mode: rows [0,32) of a k-chunk = hi, rows [32,64) = lo, so that A_hi . [B_hi | B_lo] is ONE MMA with N = 64
-    const uint32_t off = kc * (L::P * W1_CHUNK) + (n >> 3) * 128 + (n & 7) * 16;
+    // split mode: rows [0,32) of a k-chunk = hi, rows [32,64) = lo, so that x . [W_hi | W_lo] is ONE MMA with N = 64
+    const uint32_t off = kc * L::W1_CHUNK + (n >> 3) * 128 + (n & 7) * 16;
     *reinterpret_cast<uint4*>(w1op + off) = pack8(hi);
-    if (kSplit) *reinterpret_cast<uint4*>(w1op + W1_CHUNK + off) = pack8(lo);
+    if (kSplit) *reinterpret_cast<uint4*>(w1op + 32 * 16 + off) = pack8(lo);
   }
   // conv2: row n = sub*16 + co, k-chunk = patch element r*4 + c, 8 input channels per chunk
   for (int idx = tid; idx < 64 * 16; idx += nthreads) {
@@ -117,7 +132,7 @@ __device__ __forceinline__ void build_weights(uint8_t* w1op, uint8_t* w2op, uint
     const bool in = dy >= 0 && dy < 3 && dx >= 0 && dx < 3;
     float hi[8], lo[8];
 #pragma unroll
-    for (int ci = 0; ci < 8; ++ci) tc::split_bf16(in ? g.w2[(co * C1 + ci) * 9 + dy * 3 + dx] : 0.f, hi[ci], lo[ci]);
+    for (int ci = 0; ci < 8; ++ci) tc::split_f16(in ? g.w2[(co * C1 + ci) * 9 + dy * 3 + dx] : 0.f, hi[ci], lo[ci]);
     const uint32_t off = kc * (L::P * W2_CHUNK) + (n >> 3) * 128 + (n & 7) * 16;     // split: rows [0,64) hi, [64,128) lo
     *reinterpret_cast<uint4*>(w2op + off) = pack8(hi);
     if (kSplit) *reinterpret_cast<uint4*>(w2op + W2_CHUNK + off) = pack8(lo);
@@ -128,10 +143,33 @@ __device__ __forceinline__ void build_weights(uint8_t* w1op, uint8_t* w2op, uint
     const int co = n & 31, part = n >> 5;
     float hi[8], lo[8];
 #pragma unroll
-    for (int c = 0; c < 8; ++c) tc::split_bf16(co < C3 ? g.w3[(co * C2 + pl * 8 + c) * 9 + tap] : 0.f, hi[c], lo[c]);
+    for (int c = 0; c < 8; ++c) tc::split_f16(co < C3 ? g.w3[(co * C2 + pl * 8 + c) * 9 + tap] : 0.f, hi[c], lo[c]);
     const uint32_t off = ch * L::W3_CHUNK + (n >> 3) * 128 + (n & 7) * 16;
     *reinterpret_cast<uint4*>(w3op + off) = part ? pack8(lo) : pack8(hi);
   }
+}
+
+// conv1 row order.  The 1,152 pooled pixels of a frame are handled as 288 groups of four x-adjacent pixels (one thread
+// builds a group's patches from one 8-byte + two 4-byte loads per image row).  Groups are ordered interior first
+// (rows 1..22, columns 4..43), then the 44 groups that touch the left / right frame border, then the 24 of the first and
+// last pooled row, so that the border-class arithmetic of the epilogue is confined to the last tiles; inside a 128-row
+// tile, row m = e*32 + l holds pixel e of the tile's group l, which makes both the patch stores of the builder (fixed e,
+// consecutive l) and the epilogue's TMEM lanes (warp = e, lane = l) contiguous.
+__device__ __forceinline__ void group_pos(int og, int& py, int& g) {
+  if (og < 220) { py = 1 + og / 10; g = 1 + og % 10; }
+  else if (og < 264) { const int k = og - 220; py = 1 + (k >> 1); g = (k & 1) ? 11 : 0; }
+  else { const int k = og - 264; py = k < 12 ? 0 : H1 - 1; g = k < 12 ? k : k - 12; }
+}
+
+// conv1's effective weight as the tensor core sees it: the fp16 value (single pass) or hi + lo (split mode)
+template <bool kSplit>
+__device__ __forceinline__ float eff_weight(float w) {
+  float hi, lo;
+  tc::split_f16(w, hi, lo);
+  if (!kSplit) return hi;
+  float lh, ll;
+  tc::split_f16(lo, lh, ll);            // lo is rounded to fp16 once more when it is packed
+  return hi + lh;
 }
 
 template <bool kSplit, int kSlots, int ST, bool kSave>
@@ -141,21 +179,21 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
                    unsigned int* __restrict__ counter, uint8_t* __restrict__ saved) {
   using L = Lay<kSplit>;
   constexpr int NWG = ST / 128;                        // warps per TMEM lane quarter
-  constexpr int WPT = (NPIX / 4 + ST - 1) / ST;        // 4-pixel words per thread: 9 (ST=128) or 5 (ST=256)
   constexpr int TMEM_PER_SLOT = 512 / kSlots;
   constexpr bool kPipe2 = TMEM_PER_SLOT < 3 * (kSplit ? 128 : 64);   // conv2's three tiles do not fit: commit tile by tile
   static_assert(TMEM_PER_SLOT >= 2 * (kSplit ? 128 : 64), "a slot needs two conv2 tiles of TMEM columns");
   static_assert(kPipe2, "the non-pipelined conv2 path was removed");
-  constexpr int GIT = L::STRIP_TILES * 256 / ST;       // gather items per thread in a full conv1 round
-  constexpr int E1 = (L::STRIP_TILES + NWG - 1) / NWG; // conv1 epilogue tiles per thread in a full round
+  constexpr int E1 = C1_TPR / NWG;                     // conv1 epilogue tiles per thread and round: 2 (ST=128) or 1 (ST=256)
+  static_assert(C1_TPR % NWG == 0 && ST >= 64, "conv1 round / slot shape");
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* w1op = smem + kSlots * L::SLOT_BYTES;
-  uint8_t* w2op = w1op + L::P * W1_BYTES;
+  uint8_t* w2op = w1op + L::W1_BYTES;
   uint8_t* w3op = w2op + L::P * W2_BYTES;
   SlotMisc* smz = reinterpret_cast<SlotMisc*>(w3op + L::W3_BYTES);
   Shared& sh = *reinterpret_cast<Shared*>(smz + kSlots);
   const int slot = threadIdx.x / ST, tid = threadIdx.x % ST, warp = tid >> 5, lane = tid & 31;
-  uint8_t* r0 = smem + slot * L::SLOT_BYTES;           // pix / patches, later a2
+  uint8_t* ring = smem + slot * L::SLOT_BYTES;         // raw u8 frame (bulk-copy destination)
+  uint8_t* r0 = ring + RING_BYTES;                     // conv1 patches, later a2
   uint8_t* a1 = r0 + L::R0_BYTES;
   SlotMisc& mz = smz[slot];
 
@@ -166,56 +204,42 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   if (threadIdx.x < C2) sh.b2[threadIdx.x] = gw.b2[threadIdx.x];
   if (threadIdx.x < C3P) sh.b3[threadIdx.x] = threadIdx.x < C3 ? gw.b3[threadIdx.x] : 0.f;
   if (threadIdx.x < E) sh.bfc[threadIdx.x] = gw.bfc[threadIdx.x];
+  if (threadIdx.x >= 128 && threadIdx.x < 128 + 9 * C1) {
+    // border-class table of conv1: class (rc, cc) in {first, interior, last} x {first, interior, last} row / column of the
+    // frame; ws = sum of the effective weights over the taps whose input pixel lies inside the frame
+    const int e = (threadIdx.x - 128) / C1, co = (threadIdx.x - 128) % C1, rc = e / 3, cc = e % 3;
+    float acc = 0.f;
+    for (int dy = 0; dy < 3; ++dy)
+      for (int dx = 0; dx < 3; ++dx) {
+        const bool in = !(rc == 0 && dy == 0) && !(rc == 2 && dy == 2) && !(cc == 0 && dx == 0) && !(cc == 2 && dx == 2);
+        if (in) acc += eff_weight<kSplit>(gw.w1[co * 9 + dy * 3 + dx]);
+      }
+    sh.ws1[e][co] = acc;
+  }
   for (int i = tid; i < L::A1_ALLOC / 16; i += ST) reinterpret_cast<uint4*>(a1)[i] = make_uint4(0, 0, 0, 0);
   if (threadIdx.x < 32) tc::tmem_alloc<512>(&sh.tmem_base);
-  if (tid == 32) { tc::mbar_init(&mz.bar[0], 1); tc::mbar_init(&mz.bar[1], 1); tc::mbar_init(&mz.bar[2], 1); tc::mbar_fence_init(); }
+  if (tid == 32) {
+    tc::mbar_init(&mz.bar[0], 1); tc::mbar_init(&mz.bar[1], 1); tc::mbar_init(&mz.bar[2], 1); tc::mbar_init(&mz.rbar, 1);
+    tc::mbar_fence_init();
+  }
   tc::fence_async_smem();
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = sh.tmem_base + slot * TMEM_PER_SLOT;
-  const uint32_t r0_u = tc::smem_u32(r0), a1_u = tc::smem_u32(a1);
+  const uint32_t r0_u = tc::smem_u32(r0), a1_u = tc::smem_u32(a1), ring_u = tc::smem_u32(ring);
   const uint32_t w1_u = tc::smem_u32(w1op), w2_u = tc::smem_u32(w2op), w3_u = tc::smem_u32(w3op);
-  constexpr uint32_t idesc1 = tc::make_idesc_bf16(128, 32), idesc2 = tc::make_idesc_bf16(128, 64);
-  constexpr uint32_t idesc1s = tc::make_idesc_bf16(128, 64), idesc2s = tc::make_idesc_bf16(128, 128);   // hi|lo stacked along N
+  constexpr uint32_t idesc1 = tc::make_idesc_f16(128, kSplit ? 64 : 32), idesc2 = tc::make_idesc_f16(128, 64);
+  constexpr uint32_t idesc2s = tc::make_idesc_f16(128, 128);            // hi|lo stacked along N
   constexpr int C1W = kSplit ? 64 : 32, C2W = kSplit ? 128 : 64;        // TMEM columns per conv1 / conv2 tile
-  constexpr uint32_t idesc3_hi = tc::make_idesc_bf16(128, kSplit ? 64 : 32), idesc3_lo = tc::make_idesc_bf16(128, 32);
+  constexpr uint32_t idesc3_hi = tc::make_idesc_f16(128, kSplit ? 64 : 32), idesc3_lo = tc::make_idesc_f16(128, 32);
   constexpr int COLS3 = kSplit ? 64 : 32;
-  uint32_t ph0 = 0, ph1 = 0, ph2 = 0;
+  uint32_t ph0 = 0, ph1 = 0, ph2 = 0, rph = 0;
   const int q = warp & 3, wg = warp >> 2;
   const int row = q * 32 + lane;                       // this thread's row of every 128-row tile (= TMEM lane)
   const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16);
+  const uint32_t* ring32 = reinterpret_cast<const uint32_t*>(ring);
 
-  // ---- per-thread addressing, hoisted out of the frame loop
-  // 4-pixel words of the frame per thread.  ST == 128: every warp owns 12 whole rows (288 words = 9 x 32), so the
-  // left neighbour of a word is the previous lane (or lane 31 of the previous iteration) and each thread can
-  // store ONE aligned 8-byte group [left neighbour's last pixel, a, b, c] -- the 1-pixel border shift of the
-  // padded plane costs a shuffle instead of three misaligned stores.
-  constexpr bool kRowWarp = (ST == 128);
-  auto word_of = [&](int j) { return kRowWarp ? 288 * warp + 32 * j + lane : tid + j * ST; };
-  uint32_t pixoff[WPT];                                // byte offset of word j's store in the padded frame plane
-  uint32_t rowend = 0, rowstart = 0;                   // bit j: word j is the last / first of its row
-#pragma unroll
-  for (int j = 0; j < WPT; ++j) {
-    const int word = word_of(j), y = word / (W0 / 4), x = (word % (W0 / 4)) * 4;
-    pixoff[j] = ((y + 1) * PIX_LD + x + (kRowWarp ? 0 : 1)) * 2;
-    if (word % (W0 / 4) == W0 / 4 - 1) rowend |= 1u << j;
-    if (word % (W0 / 4) == 0) rowstart |= 1u << j;
-  }
-  uint32_t gsrc[GIT], gdst[GIT];                       // conv1 patch gather of round 0 (rounds advance by 8 pooled rows)
-#pragma unroll
-  for (int k = 0; k < GIT; ++k) {
-    const int idx = tid + k * ST, kc = idx / (L::STRIP_TILES * 128), pxs = idx % (L::STRIP_TILES * 128);
-    const int py = pxs / W1, px = pxs % W1;
-    gsrc[k] = ((2 * py + 2 * kc) * PIX_LD + 2 * px) * 2;
-    gdst[k] = L::OFF_PATCH + kc * L::PATCH_CHUNK + pxs * 16;
-  }
-  uint32_t a1off[E1];                                  // conv1 epilogue destination of round 0's tiles wg, wg+NWG, ..
-#pragma unroll
-  for (int k = 0; k < E1; ++k) {
-    const int Pp = (wg + k * NWG) * 128 + row, rr = Pp / W1 + 1, cc = Pp % W1 + 1;
-    a1off[k] = ((rr & 1) * 2 + (cc & 1)) * P1_PLANE + ((rr >> 1) * P1_COLS + (cc >> 1)) * 16;
-  }
   int a2off[3];                                        // conv2 epilogue destination per tile (-1: virtual pixel)
 #pragma unroll
   for (int tl = 0; tl < 3; ++tl) {
@@ -225,243 +249,242 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 
   const long long frames = (long long)B * T;
   const long long handout_base = (long long)gridDim.x * kSlots;
-  uint32_t wv[WPT];
-  bool live = false;
-  auto fetch = [&](long long fr) {                     // pixels of frame fr -> registers (loads stay in flight)
-    live = fr < frames;
-    if (live && lengths) live = (int)(fr % T) < (int)lengths[fr / T];
-    if (live) {
-#pragma unroll
-      for (int j = 0; j < WPT; ++j) {
-        const int word = word_of(j);
-        wv[j] = word < NPIX / 4 ? __ldg(reinterpret_cast<const uint32_t*>(R + fr * NPIX) + word) : 0u;
-      }
+  // ---- frame hand-out (warp 1 of the slot, all lanes): first live frame at or after `cand` in hand-out order; the
+  // padded frames passed on the way get their zero embedding here (E = 32 = one lane per output)
+  auto acquire = [&](long long cand) -> long long {
+    while (cand < frames) {
+      const bool lv = !lengths || (int)(cand % T) < (int)lengths[cand / T];
+      if (lv) break;
+      out[cand * out_stride + lane] = 0.f;
+      unsigned int h = 0;
+      if (lane == 0) h = atomicAdd(counter, 1u);
+      cand = handout_base + __shfl_sync(0xffffffffu, h, 0);
+    }
+    return cand;
+  };
+  auto start_copy = [&](long long fr) {                // one TMA bulk copy: HBM frame -> this slot's ring buffer
+    if (lane == 0 && fr < frames) {
+      tc::mbar_arrive_expect_tx(&mz.rbar, RING_BYTES);
+      tc::bulk_copy_g2s(ring_u, R + fr * NPIX, RING_BYTES, &mz.rbar);
     }
   };
-  long long f = (long long)blockIdx.x * kSlots + slot;
-  fetch(f);
+  // ---- conv1 patches of round r (groups 64 r .. 64 r + 63): item = (k-chunk, group); a chunk holds two patch rows of
+  // four raw pixels each, converted u8 -> fp16 exactly (0x6400 | b is 1024 + b; minus 1024).  A group's four pooled pixels
+  // need image columns 8g-1 .. 8g+8 of each row: bytes 3 of word 2g-1, words 2g and 2g+1, byte 0 of word 2g+2.
+  auto build = [&](int r) {
+    const int ng = (r == C1_ROUNDS - 1) ? 32 : 64;     // groups of this round (last round: one tile)
+    if (tid < 2 * ng) {
+      const int kc = tid >= ng ? 1 : 0, gl = tid - kc * ng;
+      int py, g;
+      group_pos(r * 64 + gl, py, g);
+      const int y0 = 2 * py - 1 + 2 * kc;              // patch rows 2kc, 2kc+1 = image rows y0, y0+1
+      uint32_t o[4][4];
+#pragma unroll
+      for (int rr = 0; rr < 2; ++rr) {
+        const int y = y0 + rr;
+        uint32_t wm = 0, wp = 0;
+        uint2 w01 = make_uint2(0u, 0u);
+        if ((unsigned)y < (unsigned)H0) {
+          const uint32_t* rp = ring32 + y * (W0 / 4) + 2 * g;
+          w01 = *reinterpret_cast<const uint2*>(rp);
+          if (g > 0) wm = rp[-1];
+          if (g < W1 / 4 - 1) wp = rp[2];
+        }
+        uint32_t b4[4];
+        b4[0] = __funnelshift_r(wm, w01.x, 24);        // columns 8g-1 .. 8g+2
+        b4[1] = __funnelshift_r(w01.x, w01.y, 8);      //         8g+1 .. 8g+4
+        b4[2] = __funnelshift_r(w01.x, w01.y, 24);     //         8g+3 .. 8g+6
+        b4[3] = __funnelshift_r(w01.y, wp, 8);         //         8g+5 .. 8g+8
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          uint32_t h01 = __byte_perm(b4[e], 0x64646464u, 0x5140), h23 = __byte_perm(b4[e], 0x64646464u, 0x5342);
+          asm("sub.f16x2 %0, %0, %1;" : "+r"(h01) : "r"(0x64006400u));
+          asm("sub.f16x2 %0, %0, %1;" : "+r"(h23) : "r"(0x64006400u));
+          o[e][2 * rr] = h01; o[e][2 * rr + 1] = h23;
+        }
+      }
+      uint8_t* pb = r0 + (r & 1) * PATCH_BUF + kc * PATCH_CHUNK + ((gl >> 5) * 128 + (gl & 31)) * 16;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) *reinterpret_cast<uint4*>(pb + e * 32 * 16) = make_uint4(o[e][0], o[e][1], o[e][2], o[e][3]);
+    }
+  };
+  auto conv1_issue = [&](int r) {                      // tid 0: the round's tiles, one MMA each (K = 16, N = 32 or hi|lo 64)
+    const int nt = (r == C1_ROUNDS - 1) ? 1 : C1_TPR;
+    for (int tl = 0; tl < nt; ++tl) {
+      const uint64_t da = tc::make_desc(r0_u + (r & 1) * PATCH_BUF + tl * 2048, PATCH_CHUNK, 128);
+      const uint64_t db = tc::make_desc(w1_u, L::W1_CHUNK, 128);
+      tc::mma_f16(tmem + (r & 1) * (C1_TPR * C1W) + tl * C1W, da, db, idesc1, false);
+    }
+    tc::mma_commit(&mz.bar[r & 1]);
+  };
+
+  long long f = frames;
+  if (warp == 1) {
+    f = acquire((long long)blockIdx.x * kSlots + slot);
+    start_copy(f);
+    if (lane == 0) mz.next = f;
+  }
+  slot_sync<ST>(slot);
+  f = mz.next;
   while (f < frames) {
     unsigned int handout = 0;
-    if (tid == 0) handout = atomicAdd(counter, 1u);    // this slot's NEXT frame; consumed after the first barrier
+    if (warp == 1 && lane == 0) handout = atomicAdd(counter, 1u);      // candidate for this slot's NEXT frame
     float* o = out + f * out_stride;
-    if (!live) {                                       // padded frame (t >= lengths[b]): zero embedding, no work
-      if (tid < E) o[tid] = 0.f;
-      if (tid == 0) mz.next = handout_base + handout;
-      slot_sync<ST>(slot);
-      f = mz.next;
-      slot_sync<ST>(slot);
-      fetch(f);
-      continue;
-    }
-    // ================= P0: exact integer statistics, standardised fp16 frame (pixel (y,x) at [y+1][x+1])
+    tc::mbar_wait_bounded(&mz.rbar, rph);              // the frame's bytes have landed
+    rph ^= 1;
+    // ================= P0: exact integer statistics of the raw frame; first round of conv1 patches
     {
       uint32_t s1 = 0, s2 = 0;
 #pragma unroll
-      for (int j = 0; j < WPT; ++j) {
-        s1 = __dp4a(wv[j], 0x01010101u, s1);
-        s2 = __dp4a(wv[j], wv[j], s2);
+      for (int i = 0; i < (NPIX / 4 + ST - 1) / ST; ++i) {
+        const int w = i * ST + tid;
+        const uint32_t v = (NPIX / 4) % ST == 0 || w < NPIX / 4 ? ring32[w] : 0u;
+        s1 = __dp4a(v, 0x01010101u, s1);
+        s2 = __dp4a(v, v, s2);
       }
       s1 = __reduce_add_sync(0xffffffffu, s1);
       s2 = __reduce_add_sync(0xffffffffu, s2);
       if (lane == 0) { mz.red[warp] = s1; mz.red[8 + warp] = s2; }
-      if (tid == 0) mz.next = handout_base + handout;
-      // zero border of the frame plane(s): region R0 held a2 a moment ago
-      if (tid < PIX_LD / 2) {
-#pragma unroll
-        for (int p = 0; p < L::P; ++p) {
-          uint32_t* pw = reinterpret_cast<uint32_t*>(r0 + p * PIX_BYTES);
-          pw[tid] = 0; pw[(PIX_ROWS - 1) * (PIX_LD / 2) + tid] = 0;                 // rows 0 and 49
-          if (!kRowWarp) {
-            uint16_t* ph = reinterpret_cast<uint16_t*>(r0 + p * PIX_BYTES);
-            ph[tid * PIX_LD] = 0; ph[tid * PIX_LD + W0 + 1] = 0;                    // columns 0 and 97
-          }
-        }
-      }
-      slot_sync<ST>(slot);
-      float mean_u = 0.f, inv_s = 1.0f / 255.0f;
-      if (standardize) {
-        uint32_t t1 = 0, t2 = 0;
-#pragma unroll
-        for (int i = 0; i < ST / 32; ++i) { t1 += mz.red[i]; t2 += mz.red[8 + i]; }
-        // N*S2 - S1^2 is an exact 64-bit integer (< 2^41), so the cancellation happens before any rounding and the rest
-        // is fp32: unbiased variance in raw pixel units, std clamped at 1e-6 * 255 (train_model_official.py:289-291)
-        const unsigned long long d = (unsigned long long)NPIX * t2 - (unsigned long long)t1 * t1;
-        const float var_u = (float)d * (1.0f / ((float)NPIX * (float)(NPIX - 1)));
-        mean_u = (float)t1 * (1.0f / (float)NPIX);               // t1 < 2^24 and NPIX = 9 * 2^9: one rounding
-        inv_s = 1.0f / fmaxf(sqrtf(var_u), 255.0e-6f);
-      }
-      const float nmean = -mean_u * inv_s;
-      uint32_t carry_hi = 0, carry_lo = 0;             // lane 31's last pixel of the previous iteration (kRowWarp)
-#pragma unroll
-      for (int j = 0; j < WPT; ++j) {
-        if (WPT * ST == NPIX / 4 || word_of(j) < NPIX / 4) {
-          float hi[4], lo[4];
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            // byte k -> float through the 2^23 + b bit pattern (one PRMT, one exact FADD), then one FFMA
-            const float xf = __uint_as_float(__byte_perm(wv[j], 0x4B000000u, 0x7440 + k)) - 8388608.0f;
-            hi[k] = fmaf(xf, inv_s, nmean);
-            if (kSplit) tc::split_bf16(hi[k], hi[k], lo[k]);
-          }
-          uint8_t* d = r0 + pixoff[j];
-          if (kRowWarp) {
-            // [left neighbour's d | a] [b | c] as one 8-byte store; the row's last word also stores [d | 0]
-#pragma unroll
-            for (int p = 0; p < L::P; ++p) {
-              const float* v = p ? lo : hi;
-              uint32_t& carry = p ? carry_lo : carry_hi;
-              const uint32_t ad = tc::pack_bf16(v[0], v[3]);                       // a low half, d high half
-              uint32_t left = __shfl_up_sync(0xffffffffu, ad, 1);
-              if (lane == 0) left = carry;
-              if ((rowstart >> j) & 1u) left = 0u;                                 // column 0 of the padded plane
-              carry = __shfl_sync(0xffffffffu, ad, 31);
-              *reinterpret_cast<uint2*>(d + p * PIX_BYTES) = make_uint2(__byte_perm(left, ad, 0x5432), tc::pack_bf16(v[1], v[2]));
-              if ((rowend >> j) & 1u) *reinterpret_cast<uint32_t*>(d + p * PIX_BYTES + 8) = ad >> 16;   // [d | column 97 = 0]
-            }
-          } else {
-            const uint32_t ad = tc::pack_bf16(hi[0], hi[3]);                        // column x+1 is odd: a | (b,c) | d
-            *reinterpret_cast<uint16_t*>(d) = (uint16_t)(ad & 0xffffu);
-            *reinterpret_cast<uint32_t*>(d + 2) = tc::pack_bf16(hi[1], hi[2]);
-            *reinterpret_cast<uint16_t*>(d + 6) = (uint16_t)(ad >> 16);
-            if (kSplit) {
-              const uint32_t al = tc::pack_bf16(lo[0], lo[3]);
-              *reinterpret_cast<uint16_t*>(d + PIX_BYTES) = (uint16_t)(al & 0xffffu);
-              *reinterpret_cast<uint32_t*>(d + PIX_BYTES + 2) = tc::pack_bf16(lo[1], lo[2]);
-              *reinterpret_cast<uint16_t*>(d + PIX_BYTES + 6) = (uint16_t)(al >> 16);
-            }
-          }
-        }
-      }
     }
-    const long long fnext = mz.next;
-    fetch(fnext);                                      // next frame's pixels travel while this one is convolved
+    build(0);
+    tc::fence_async_smem();
     slot_sync<ST>(slot);
+    if (tid == 0) { tc::fence_after_sync(); conv1_issue(0); }
+    float mean_u = 0.f, inv_s = 1.0f / 255.0f;
+    if (standardize) {
+      uint32_t t1 = 0, t2 = 0;
+#pragma unroll
+      for (int i = 0; i < ST / 32; ++i) { t1 += mz.red[i]; t2 += mz.red[8 + i]; }
+      // N*S2 - S1^2 is an exact 64-bit integer (< 2^41), so the cancellation happens before any rounding and the rest
+      // is fp32: unbiased variance in raw pixel units, std clamped at 1e-6 * 255 (train_model_official.py:289-291)
+      const unsigned long long d = (unsigned long long)NPIX * t2 - (unsigned long long)t1 * t1;
+      const float var_u = (float)d * (1.0f / ((float)NPIX * (float)(NPIX - 1)));
+      mean_u = (float)t1 * (1.0f / (float)NPIX);               // t1 < 2^24 and NPIX = 9 * 2^9: one rounding
+      inv_s = 1.0f / fmaxf(sqrtf(var_u), 255.0e-6f);
+    }
+    const float nmean = -mean_u;
+    float cint[8];                                     // interior pixels: relu(inv_s * max_sub(v) + cint), cint = b1 - mu/sigma * ws(interior)
+    {
+      float wsi[8], bb[8];
+      *reinterpret_cast<float4*>(wsi) = *reinterpret_cast<const float4*>(sh.ws1[4]);
+      *reinterpret_cast<float4*>(wsi + 4) = *reinterpret_cast<const float4*>(sh.ws1[4] + 4);
+      *reinterpret_cast<float4*>(bb) = *reinterpret_cast<const float4*>(sh.b1);
+      *reinterpret_cast<float4*>(bb + 4) = *reinterpret_cast<const float4*>(sh.b1 + 4);
+#pragma unroll
+      for (int co = 0; co < 8; ++co) cint[co] = fmaf(nmean * inv_s, wsi[co], bb[co]);
+    }
 
-    // ================= conv1 + ReLU + pool: rounds of STRIP_TILES tiles of 128 pooled pixels
+    // ================= conv1 + ReLU + pool: 5 rounds of 2 tiles (last: 1); the patches of round r+1 are built while
+    // the tensor core works on round r; TMEM columns and patch buffers alternate
+    long long fnext = frames;
 #pragma unroll 1
-    for (int tile0 = 0, rnd = 0; tile0 < 9; tile0 += L::STRIP_TILES, ++rnd) {
-      const int ntiles = min(L::STRIP_TILES, 9 - tile0);
-      if (9 % L::STRIP_TILES == 0) {                   // full rounds only: hoisted addressing (+16 frame rows per round)
-        const uint32_t radd = rnd * (16 * PIX_LD * 2);
-        // all loads first, then all stores: source and destination live in the same buffer, so the compiler would
-        // otherwise keep every load behind the previous store and expose the LDS latency once per item
-#pragma unroll
-        for (int p = 0; p < L::P; ++p) {
-          uint4 v[GIT];
-#pragma unroll
-          for (int k = 0; k < GIT; ++k) {
-            const uint8_t* src = r0 + p * PIX_BYTES + gsrc[k] + radd;
-            v[k].x = *reinterpret_cast<const uint32_t*>(src);
-            v[k].y = *reinterpret_cast<const uint32_t*>(src + 4);
-            v[k].z = *reinterpret_cast<const uint32_t*>(src + PIX_LD * 2);
-            v[k].w = *reinterpret_cast<const uint32_t*>(src + PIX_LD * 2 + 4);
-          }
-#pragma unroll
-          for (int k = 0; k < GIT; ++k) *reinterpret_cast<uint4*>(r0 + p * L::PATCH_BYTES + gdst[k]) = v[k];
-        }
-      } else {
-        // gather the 4x4 patches: item = (k-chunk, pooled pixel); chunk kc holds patch rows 2kc, 2kc+1
-        for (int idx = tid; idx < ntiles * 256; idx += ST) {
-          const int kc = idx / (ntiles * 128), pxs = idx % (ntiles * 128);
-          const int Pp = tile0 * 128 + pxs, py = Pp / W1, px = Pp % W1;
-#pragma unroll
-          for (int p = 0; p < L::P; ++p) {
-            const uint8_t* src = r0 + p * PIX_BYTES + ((2 * py + 2 * kc) * PIX_LD + 2 * px) * 2;
-            uint4 v;
-            v.x = *reinterpret_cast<const uint32_t*>(src);
-            v.y = *reinterpret_cast<const uint32_t*>(src + 4);
-            v.z = *reinterpret_cast<const uint32_t*>(src + PIX_LD * 2);
-            v.w = *reinterpret_cast<const uint32_t*>(src + PIX_LD * 2 + 4);
-            *reinterpret_cast<uint4*>(r0 + L::OFF_PATCH + p * L::PATCH_BYTES + kc * L::PATCH_CHUNK + pxs * 16) = v;
-          }
-        }
-      }
-      tc::fence_async_smem();
-      slot_sync<ST>(slot);
-      if (tid == 0) {
-        tc::fence_after_sync();
-        for (int tl = 0; tl < ntiles; ++tl) {
-          const uint64_t ah = tc::make_desc(r0_u + L::OFF_PATCH + tl * 2048, L::PATCH_CHUNK, 128);
-          const uint64_t bh = tc::make_desc(w1_u, L::P * W1_CHUNK, 128);
-          if (kSplit) {
-            // columns [0,32) = A_hi.B_hi (+ A_lo.B_hi), columns [32,64) = A_hi.B_lo; the epilogue adds the halves
-            const uint64_t al = tc::make_desc(r0_u + L::OFF_PATCH + L::PATCH_BYTES + tl * 2048, L::PATCH_CHUNK, 128);
-            tc::mma_bf16(tmem + tl * C1W, ah, bh, idesc1s, false);
-            tc::mma_bf16(tmem + tl * C1W, al, bh, idesc1, true);
-          } else {
-            tc::mma_bf16(tmem + tl * C1W, ah, bh, idesc1, false);
-          }
-        }
-        tc::mma_commit(&mz.bar[0]);
-      }
-      tc::mbar_wait_bounded(&mz.bar[0], ph0);
-      ph0 ^= 1;
+    for (int r = 0; r < C1_ROUNDS; ++r) {
+      if (r + 1 < C1_ROUNDS) build(r + 1);
+      if (r & 1) { tc::mbar_wait_bounded(&mz.bar[1], ph1); ph1 ^= 1; } else { tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1; }
       tc::fence_after_sync();
+      const int nt = (r == C1_ROUNDS - 1) ? 1 : C1_TPR;
 #pragma unroll
       for (int k = 0; k < E1; ++k) {
-        const int tl = wg + k * NWG;
-        if (tl < ntiles) {
+        const int tl = NWG == 1 ? k : wg;
+        if (tl < nt) {
           float v[32];
-          tc::tmem_ld32(tq + tl * C1W, v);
+          const uint32_t tcol = tq + (r & 1) * (C1_TPR * C1W) + tl * C1W;
+          tc::tmem_ld32(tcol, v);
           if (kSplit) {
             float w[32];
-            tc::tmem_ld32(tq + tl * C1W + 32, w);
+            tc::tmem_ld32(tcol + 32, w);
             tc::tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] += w[i];
+            for (int i = 0; i < 32; ++i) v[i] += w[i];             // x.W_hi + x.W_lo
           } else {
             tc::tmem_ld_wait();
           }
-          float hi[8], lo[8], bb[8];
-          // biases as 16-byte broadcast loads (a scalar LDS per use made them a tenth of the kernel's shared-memory wavefronts)
-          *reinterpret_cast<float4*>(bb) = *reinterpret_cast<const float4*>(sh.b1);
-          *reinterpret_cast<float4*>(bb + 4) = *reinterpret_cast<const float4*>(sh.b1 + 4);
-          if (kSave) {                                                    // fp32 activations + pool argmax for the backward pass
-            float a[8];
-            uint32_t am = 0;
+          int py, g;
+          group_pos((r * C1_TPR + tl) * 32 + lane, py, g);
+          const int px = 4 * g + q, Pp = py * W1 + px;                    // this thread's pooled pixel (row m = q*32 + lane of the tile)
+          const bool border = py == 0 || py == H1 - 1 || px == 0 || px == W1 - 1;
+          float hi[8], lo[8];
+          uint32_t am = 0;
+          if (!__any_sync(0xffffffffu, border)) {
+            // all four conv pixels of every lane are interior: one class, the maximum commutes with the affine map
 #pragma unroll
-            for (int co = 0; co < 8; ++co) {                              // first maximum in row-major order (ATen's choice)
+            for (int co = 0; co < 8; ++co) {
               float m = v[co];
-              uint32_t arg = 0;
-              if (v[8 + co] > m) { m = v[8 + co]; arg = 1; }
-              if (v[16 + co] > m) { m = v[16 + co]; arg = 2; }
-              if (v[24 + co] > m) { m = v[24 + co]; arg = 3; }
-              am |= arg << (2 * co);
-              a[co] = fmaxf(m + bb[co], 0.f);
+              if (!kSave) {
+                m = fmaxf(fmaxf(m, v[8 + co]), fmaxf(v[16 + co], v[24 + co]));
+              } else {                                                    // first maximum in row-major order (ATen's choice)
+                uint32_t arg = 0;
+                if (v[8 + co] > m) { m = v[8 + co]; arg = 1; }
+                if (v[16 + co] > m) { m = v[16 + co]; arg = 2; }
+                if (v[24 + co] > m) { m = v[24 + co]; arg = 3; }
+                am |= arg << (2 * co);
+              }
+              hi[co] = fmaxf(fmaf(m, inv_s, cint[co]), 0.f);
             }
-            const int Pp = (tile0 + tl) * 128 + row;
+          } else {
+            // border class of the four conv pixels (2py + i, 2px + j) of this pooled pixel
+            const int rc0 = py == 0 ? 0 : 1, rc1 = py == H1 - 1 ? 2 : 1, cc0 = px == 0 ? 0 : 1, cc1 = px == W1 - 1 ? 2 : 1;
+            float m[8];
+#pragma unroll
+            for (int sub = 0; sub < 4; ++sub) {
+              const int e = ((sub >> 1) ? rc1 : rc0) * 3 + ((sub & 1) ? cc1 : cc0);
+              float ws[8];
+              *reinterpret_cast<float4*>(ws) = *reinterpret_cast<const float4*>(sh.ws1[e]);
+              *reinterpret_cast<float4*>(ws + 4) = *reinterpret_cast<const float4*>(sh.ws1[e] + 4);
+#pragma unroll
+              for (int co = 0; co < 8; ++co) {
+                const float x = fmaf(nmean, ws[co], v[sub * 8 + co]);    // conv(w, x_raw) - mu * (sum of in-frame weights)
+                if (sub == 0) m[co] = x;
+                else if (!kSave) m[co] = fmaxf(m[co], x);
+                else if (x > m[co]) { m[co] = x; am = (am & ~(3u << (2 * co))) | ((uint32_t)sub << (2 * co)); }
+              }
+            }
+            float bb[8];
+            *reinterpret_cast<float4*>(bb) = *reinterpret_cast<const float4*>(sh.b1);
+            *reinterpret_cast<float4*>(bb + 4) = *reinterpret_cast<const float4*>(sh.b1 + 4);
+#pragma unroll
+            for (int co = 0; co < 8; ++co) hi[co] = fmaxf(fmaf(m[co], inv_s, bb[co]), 0.f);  // 1/sigma > 0 commutes with the max
+          }
+          if (kSave) {                                                    // fp32 activations + pool argmax for the backward pass
             uint8_t* rec = saved + f * SV_BYTES;
-            reinterpret_cast<float4*>(rec + SV_A1)[2 * Pp] = make_float4(a[0], a[1], a[2], a[3]);
-            reinterpret_cast<float4*>(rec + SV_A1)[2 * Pp + 1] = make_float4(a[4], a[5], a[6], a[7]);
+            reinterpret_cast<float4*>(rec + SV_A1)[2 * Pp] = make_float4(hi[0], hi[1], hi[2], hi[3]);
+            reinterpret_cast<float4*>(rec + SV_A1)[2 * Pp + 1] = make_float4(hi[4], hi[5], hi[6], hi[7]);
             reinterpret_cast<uint16_t*>(rec + SV_IDX1)[Pp] = (uint16_t)am;
           }
+          if (kSplit) {
 #pragma unroll
-          for (int co = 0; co < 8; ++co) {
-            const float m4 = fmaxf(fmaxf(v[co], v[8 + co]), fmaxf(v[16 + co], v[24 + co]));
-            hi[co] = fmaxf(m4 + bb[co], 0.f);
-            if (kSplit) tc::split_bf16(hi[co], hi[co], lo[co]);          // single pass: pack8 rounds once
+            for (int co = 0; co < 8; ++co) tc::split_f16(hi[co], hi[co], lo[co]);           // single pass: pack8 rounds once
           }
-          uint32_t off;
-          if (9 % L::STRIP_TILES == 0) {
-            off = a1off[k] + rnd * (4 * P1_COLS * 16);                  // 8 pooled rows further = 4 plane rows
-          } else {
-            const int Pp = (tile0 + tl) * 128 + row;                    // pooled pixel -> a1 padded (py+1, px+1)
-            const int rr = Pp / W1 + 1, cc = Pp % W1 + 1;
-            off = ((rr & 1) * 2 + (cc & 1)) * P1_PLANE + ((rr >> 1) * P1_COLS + (cc >> 1)) * 16;
-          }
+          const int rr = py + 1, cc = px + 1;                            // pooled pixel -> a1 padded parity planes
+          const uint32_t off = ((rr & 1) * 2 + (cc & 1)) * P1_PLANE + ((rr >> 1) * P1_COLS + (cc >> 1)) * 16;
           *reinterpret_cast<uint4*>(a1 + off) = pack8(hi);
           if (kSplit) *reinterpret_cast<uint4*>(a1 + A1_BYTES + off) = pack8(lo);
         }
       }
       tc::fence_before_sync();
-      slot_sync<ST>(slot);                              // patches and TMEM columns are reused by the next round
+      tc::fence_async_smem();
+      slot_sync<ST>(slot);                              // patches of round r+1 complete; round r's TMEM columns and patch buffer free
+      if (tid == 0 && r + 1 < C1_ROUNDS) { tc::fence_after_sync(); conv1_issue(r + 1); }
+      if (r == C1_ROUNDS - 2 && warp == 1) {
+        // the last patches are built: the ring buffer is free (every reader passed the barrier above, after its
+        // fence.proxy.async) -- find this slot's next frame and start its copy; it travels under the rest of this frame
+        fnext = acquire(handout_base + __shfl_sync(0xffffffffu, handout, 0));
+        start_copy(fnext);
+        if (lane == 0) mz.next = fnext;
+      }
     }
 
     // ================= conv2 + ReLU + pool: 3 tiles of 128 virtual pooled pixels (v = py*25 + px)
-    // region R0 becomes a2: clear it (its zero border is conv3's padding); the frame plane and patches are dead
-    for (int i = tid; i < L::P * A2_BYTES / 16; i += ST) reinterpret_cast<uint4*>(r0)[i] = make_uint4(0, 0, 0, 0);
+    // region R0 becomes a2: zero its border cells (conv3's padding; the interior is overwritten by the epilogue below, the
+    // rows past 13 only feed output rows that are never read); the patches are dead
+    for (int i = tid; i < L::P * 2 * 76; i += ST) {
+      const int pl = i / 76, c = i % 76;               // plane (part, channel half), border cell
+      const int cell = c < 26 ? c : c < 52 ? 13 * PITCH2 + (c - 26) : (1 + ((c - 52) >> 1)) * PITCH2 + ((c & 1) ? PITCH2 - 1 : 0);
+      reinterpret_cast<uint4*>(r0 + pl * PLANE2)[cell] = make_uint4(0, 0, 0, 0);
+    }
     tc::fence_async_smem();
     slot_sync<ST>(slot);
+    fnext = mz.next;
     auto conv2_issue = [&](int tl, uint32_t dcol) {
 #pragma unroll
       for (int r = 0; r < 4; ++r)
@@ -475,10 +498,10 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           if (kSplit) {
             // columns [0,64) = A_hi.B_hi + A_lo.B_hi, columns [64,128) = A_hi.B_lo
             const uint64_t al = tc::make_desc(a1_u + A1_BYTES + a_off, P1_PLANE, 128);
-            tc::mma_bf16(tmem + dcol, ah, bh, idesc2s, (r | h) != 0);
-            tc::mma_bf16(tmem + dcol, al, bh, idesc2, true);
+            tc::mma_f16(tmem + dcol, ah, bh, idesc2s, (r | h) != 0);
+            tc::mma_f16(tmem + dcol, al, bh, idesc2, true);
           } else {
-            tc::mma_bf16(tmem + dcol, ah, bh, idesc2, (r | h) != 0);
+            tc::mma_f16(tmem + dcol, ah, bh, idesc2, (r | h) != 0);
           }
         }
     };
@@ -509,7 +532,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           *reinterpret_cast<float4*>(bb) = *reinterpret_cast<const float4*>(sh.b2 + wg * 8);
           *reinterpret_cast<float4*>(bb + 4) = *reinterpret_cast<const float4*>(sh.b2 + wg * 8 + 4);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) tc::split_bf16(fmaxf(m4[i] + bb[i], 0.f), hi[i], lo[i]);
+          for (int i = 0; i < 8; ++i) tc::split_f16(fmaxf(m4[i] + bb[i], 0.f), hi[i], lo[i]);
           const uint32_t off = (uint32_t)a2off[tl] + wg * PLANE2;
           if (kSave) {
             const int vp = tl * 128 + row, pix = (vp / P1_COLS) * W2 + vp % P1_COLS;
@@ -585,8 +608,8 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           const int dy = tap / 3, dx = tap % 3;
           const uint32_t a_off = (dy * PITCH2 + tx * 8 + dx) * 16;
           const uint64_t db = tc::make_desc(w3_u + 2 * tap * L::W3_CHUNK, L::W3_CHUNK, 128);
-          tc::mma_bf16(tmem + tx * COLS3, tc::make_desc(r0_u + a_off, PLANE2, PITCH2 * 16), db, idesc3_hi, tap > 0);
-          if (kSplit) tc::mma_bf16(tmem + tx * COLS3, tc::make_desc(r0_u + A2_BYTES + a_off, PLANE2, PITCH2 * 16), db, idesc3_lo, true);
+          tc::mma_f16(tmem + tx * COLS3, tc::make_desc(r0_u + a_off, PLANE2, PITCH2 * 16), db, idesc3_hi, tap > 0);
+          if (kSplit) tc::mma_f16(tmem + tx * COLS3, tc::make_desc(r0_u + A2_BYTES + a_off, PLANE2, PITCH2 * 16), db, idesc3_lo, true);
         }
         tc::mma_commit(&mz.bar[tx]);
       }
@@ -664,7 +687,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 
 template <bool kSplit, int kSlots>
 constexpr size_t smem_total() {
-  return kSlots * Lay<kSplit>::SLOT_BYTES + Lay<kSplit>::P * (W1_BYTES + W2_BYTES) + Lay<kSplit>::W3_BYTES +
+  return kSlots * Lay<kSplit>::SLOT_BYTES + Lay<kSplit>::W1_BYTES + Lay<kSplit>::P * W2_BYTES + Lay<kSplit>::W3_BYTES +
          kSlots * sizeof(SlotMisc) + sizeof(Shared);
 }
 
@@ -687,7 +710,7 @@ extern "C" int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int
   SSB_REQUIRE(out_stride >= E, "out_stride < 32");
   SSB_REQUIRE(passes == 1 || passes == 3, "passes must be 1 or 3");
   for (int i = 0; i < 8; ++i) SSB_REQUIRE(weights[i], "null weight pointer");
-  SSB_REQUIRE(((uintptr_t)R & 3) == 0, "R must be 4-byte aligned");
+  SSB_REQUIRE(((uintptr_t)R & 15) == 0, "R must be 16-byte aligned (frames are staged by 4,608-byte bulk copies)");
   if (B * T == 0) return SSB_OK;
   Weights gw{weights[0], weights[1], weights[2], weights[3], weights[4], weights[5], weights[6], weights[7]};
   const int64_t frames = B * T;

@@ -1,6 +1,6 @@
 // tcgen05 / TMEM / mbarrier primitives for sm_100a (inline PTX; no CUTLASS dependency).
 //
-// Operand convention used throughout: bf16, K-major, NO swizzle ("interleave") canonical layout:
+// Operand convention used throughout: fp16 (tc::kOperandFp16; bf16 when that switch is off), K-major, NO swizzle ("interleave") canonical layout:
 // 8x8 core matrices of 8 rows x 16 bytes, element (r, k) of an operand tile at byte
 //     (r/8)*SBO + (k/8)*LBO + (r%8)*16 + (k%8)*2
 // A kind::f16 MMA consumes K=16 = two core matrices LBO apart.  Accumulators are fp32 in TMEM:
@@ -33,7 +33,7 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_b
 constexpr bool kOperandFp16 = true;
 
 // ---- instruction descriptor for kind::f16, (fp16|bf16) x (fp16|bf16) -> fp32, both operands K-major
-__host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N) {
+__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
   return (1u << 4)                    // c_format = F32
        | ((kOperandFp16 ? 0u : 1u) << 7)     // a_format: 0 = F16, 1 = BF16
        | ((kOperandFp16 ? 0u : 1u) << 10)    // b_format
@@ -41,7 +41,7 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N) {
        | ((uint32_t)(M >> 4) << 24);  // m_dim
 }
 
-__device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, bool accumulate) {
+__device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, bool accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
@@ -182,8 +182,8 @@ __device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity
   }
 }
 
-// ---- fp32 -> bf16 hi / lo split:  x ~= hi + lo with |x - hi - lo| <= 2^-17 |x|
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {        // two fp32 -> packed 16-bit operand pair
+// ---- fp32 -> 16-bit hi / lo split:  x ~= hi + lo with |x - hi - lo| <= 2^-22 |x| (fp16 operands; 2^-17 with bf16)
+__device__ __forceinline__ uint32_t pack_f16(float a, float b) {        // two fp32 -> packed 16-bit operand pair
   if (kOperandFp16) {
     uint32_t r;
     asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;\n" : "=r"(r) : "f"(b), "f"(a));   // first source -> upper half
@@ -192,7 +192,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {        // two 
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
 }
-__device__ __forceinline__ void split_bf16(float x, float& hi, float& lo) {   // x ~= hi + lo, both representable
+__device__ __forceinline__ void split_f16(float x, float& hi, float& lo) {   // x ~= hi + lo, both representable
   if (kOperandFp16) {
     uint16_t h;
     asm("cvt.rn.satfinite.f16.f32 %0, %1;\n" : "=h"(h) : "f"(x));
