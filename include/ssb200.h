@@ -194,6 +194,17 @@ int ssb_proj_prepack(const float* W_a, const float* W_b, int64_t ldw, int64_t n_
 int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
                   const void* packed, const float* bias, void* C, int64_t ldc, int64_t M, int64_t N,
                   const int64_t* lengths, int64_t T, int32_t out_half, void* stream);
+/* K3a v2, fp32-parity grade (the default precision of BiGRUClassifier, the training mode): the same persistent GEMM with
+ * both operands split x = hi + lo (fp16 each) and D += W_hi.A_hi + W_lo.A_hi + W_hi.A_lo.  ssb_proj_prepack_split writes
+ * every 16 KB weight block followed by the block of its fp16 residuals (ssb_proj_packed_bytes_split bytes); the kernel
+ * keeps a 64-row activation tile (hi and lo) resident, uses the weights as the M = 128 operand and stores the transposed
+ * accumulator as full 128-byte row segments.  C is fp32. */
+int64_t ssb_proj_packed_bytes_split(int64_t N, int64_t K1, int64_t K2);
+int ssb_proj_prepack_split(const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int64_t K1, int64_t K2,
+                           int32_t gru_blocked, void* packed, void* stream);
+int ssb_proj_gemm_split(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                        const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
+                        const int64_t* lengths, int64_t T, void* stream);
 
 /* K6: batched mouth-ROI crop + BGR->gray + resize to 96x48, bit-exact with OpenCV 4.13.
  * Replaces crop_roi_gray (live_infer_official.py:171-187; flavor 0: INTER_AREA, box in double arithmetic) and

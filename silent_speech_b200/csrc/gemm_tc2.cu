@@ -39,8 +39,9 @@ __host__ __device__ constexpr int round_up(int x, int m) { return (x + m - 1) / 
 __host__ __device__ constexpr int kp_of(int K1, int K2) { return round_up(round_up(K1, 8) + round_up(K2, 8), KB); }
 
 // packed[(nt * nkb + kb) * W_BLOCK + (k/8) * CHUNK + (r/8) * 128 + (r%8) * 16 + (k%8) * 2]  for row nt*128 + r, column kb*64 + k
+// split != 0: every 16 KB block is followed by the block of the fp16 residuals (w - fp16(w)), i.e. 32 KB per (nt, kb)
 __global__ void prepack_kernel(const float* __restrict__ Wa, const float* __restrict__ Wb, int64_t ldw, int n_each,
-                               int K1, int K2, int N, int gru_blocked, uint8_t* __restrict__ packed) {
+                               int K1, int K2, int N, int gru_blocked, int split, uint8_t* __restrict__ packed) {
   const int K1p = round_up(K1, 8), Kp = kp_of(K1, K2), nkb = Kp / KB;
   const int items = round_up(N, BN) * (Kp / 8);          // one item = 8 consecutive k of one row
   for (int it = blockIdx.x * blockDim.x + threadIdx.x; it < items; it += gridDim.x * blockDim.x) {
@@ -64,7 +65,14 @@ __global__ void prepack_kernel(const float* __restrict__ Wa, const float* __rest
       x[j] = v;
     }
     const int nt = n / BN, r = n % BN, kb = c / (KB / 8), kc = c % (KB / 8);
-    uint8_t* dst = packed + ((size_t)(nt * nkb + kb)) * W_BLOCK + kc * CHUNK + (r >> 3) * 128 + (r & 7) * 16;
+    uint8_t* dst = packed + ((size_t)(nt * nkb + kb)) * (split ? 2 : 1) * W_BLOCK + kc * CHUNK + (r >> 3) * 128 + (r & 7) * 16;
+    if (split) {
+      float lo[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) tc::split_f16(x[j], x[j], lo[j]);
+      *reinterpret_cast<uint4*>(dst + W_BLOCK) = make_uint4(tc::pack_f16(lo[0], lo[1]), tc::pack_f16(lo[2], lo[3]),
+                                                            tc::pack_f16(lo[4], lo[5]), tc::pack_f16(lo[6], lo[7]));
+    }
     *reinterpret_cast<uint4*>(dst) = make_uint4(tc::pack_f16(x[0], x[1]), tc::pack_f16(x[2], x[3]),
                                                 tc::pack_f16(x[4], x[5]), tc::pack_f16(x[6], x[7]));
   }
@@ -265,6 +273,183 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
   if (warp == 0) tc::tmem_dealloc<TMEM_COLS>(tmem);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Split mode (fp32-parity grade): C = A . W^T with A = A_hi + A_lo, W = W_hi + W_lo (fp16 each) and
+// D += W_hi.A_hi + W_lo.A_hi + W_hi.A_lo.  The operand roles are SWAPPED with respect to the kernel above: the weights are
+// the M = 128 operand (streamed: 32 KB hi|lo blocks through a 3-stage ring), the activations the N = 64 operand (a 64-row
+// tile, hi and lo, resident: 96 KB at K = 384 -- a 128-row tile would not fit), so every MMA runs at the full M = 128
+// rate and the accumulator comes out TRANSPOSED: TMEM lane = output column n, TMEM column = tile row m.  The epilogue
+// therefore needs no shared-memory transpose: a warp's 32 lanes hold 32 consecutive n of one row, i.e. every store
+// instruction writes one full 128-byte row segment of C.
+constexpr int SBM = 64;                                  // activation rows per tile
+constexpr int SCHUNK = SBM * 16;                         // one k-chunk (8 k) of 64 rows
+constexpr int SSTAGES = 3;
+constexpr int STMEM_COLS = 128;                          // two 64-column accumulators
+
+__global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int K1p = round_up(a.K1, 8), Kp = kp_of(a.K1, a.K2), nkb = Kp / KB, nnt = (a.N + BN - 1) / BN;
+  uint8_t* act_hi = smem;                                    // Kp/8 chunks x 1024 B
+  uint8_t* act_lo = act_hi + (Kp / 8) * SCHUNK;
+  uint8_t* w_s = act_lo + (Kp / 8) * SCHUNK;                 // SSTAGES x (16 KB hi + 16 KB lo)
+  float* bias_s = reinterpret_cast<float*>(w_s + SSTAGES * 2 * W_BLOCK);   // nnt * 128 floats
+  uint8_t* live_s = reinterpret_cast<uint8_t*>(bias_s + nnt * BN);         // 64 bytes
+  Ctl& ctl = *reinterpret_cast<Ctl*>(live_s + SBM);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  for (int i = tid; i < nnt * BN; i += THREADS) bias_s[i] = (a.bias && i < a.N) ? a.bias[i] : 0.f;
+  if (warp == 0) tc::tmem_alloc<STMEM_COLS>(&ctl.tmem_base);
+  if (tid == 32) {
+    for (int s = 0; s < SSTAGES; ++s) { tc::mbar_init(&ctl.full[s], 1); tc::mbar_init(&ctl.empty[s], 1); }
+    for (int b = 0; b < 2; ++b) { tc::mbar_init(&ctl.accfull[b], 1); tc::mbar_init(&ctl.accempty[b], EPI_WARPS); }
+    tc::mbar_fence_init();
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = ctl.tmem_base;
+  const uint32_t ah_u = tc::smem_u32(act_hi), al_u = tc::smem_u32(act_lo), w_u = tc::smem_u32(w_s);
+  constexpr uint32_t idesc = tc::make_idesc_f16(BN, SBM);     // M = 128 weight rows, N = 64 activation rows
+  uint32_t w_it = 0, acc_it = 0;
+
+  const int m_tiles = (a.M + SBM - 1) / SBM;
+  for (int mt = blockIdx.x; mt < m_tiles; mt += gridDim.x) {
+    const int m0 = mt * SBM;
+    int live = 0;
+    if (tid < SBM) {
+      const int m = m0 + tid;
+      live = m < a.M && (!a.lengths || (m % a.T) < (int)a.lengths[m / a.T]);
+      live_s[tid] = (uint8_t)live;
+    }
+    if (!__syncthreads_or(live)) continue;                  // also: every MMA of the previous tile has completed
+    // ---- activation tile: fp32 global -> fp16 hi / lo, canonical K-major, once per tile (a warp covers 8 rows x 4
+    // chunks per pass: 128 B contiguous per row from global, conflict-free 16-byte stores)
+    {
+      const int items = SBM * (Kp / 8);
+      constexpr int NB = 4;
+      for (int base = tid; base < items; base += NB * THREADS) {
+        float4 v0[NB], v1[NB];
+        uint32_t dst[NB];
+#pragma unroll
+        for (int u = 0; u < NB; ++u) {
+          const int idx = base + u * THREADS;
+          const int r8 = idx & 7, c4 = (idx >> 3) & 3, rest = idx >> 5, rg = rest & 7, cg = rest >> 3;
+          const int row = rg * 8 + r8, chunk = cg * 4 + c4, kk = chunk * 8;
+          v0[u] = make_float4(0.f, 0.f, 0.f, 0.f); v1[u] = v0[u];
+          dst[u] = idx < items ? (uint32_t)(chunk * SCHUNK + rg * 128 + r8 * 16) : 0xffffffffu;
+          if (idx < items && m0 + row < a.M) {
+            if (kk < K1p) {
+              const float* g = a.A1 + (int64_t)(m0 + row) * a.lda1 + kk;
+              if (kk < a.K1) v0[u] = __ldg(reinterpret_cast<const float4*>(g));
+              if (kk + 4 < a.K1) v1[u] = __ldg(reinterpret_cast<const float4*>(g + 4));
+            } else if (kk - K1p < a.K2) {
+              const int k2 = kk - K1p;
+              const float* g = a.A2 + (int64_t)(m0 + row) * a.lda2 + k2;
+              v0[u] = __ldg(reinterpret_cast<const float4*>(g));
+              if (k2 + 4 < a.K2) v1[u] = __ldg(reinterpret_cast<const float4*>(g + 4));
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < NB; ++u)
+          if (dst[u] != 0xffffffffu) {
+            float x[8] = {v0[u].x, v0[u].y, v0[u].z, v0[u].w, v1[u].x, v1[u].y, v1[u].z, v1[u].w}, l[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) tc::split_f16(x[j], x[j], l[j]);
+            *reinterpret_cast<uint4*>(act_hi + dst[u]) = make_uint4(tc::pack_f16(x[0], x[1]), tc::pack_f16(x[2], x[3]),
+                                                                    tc::pack_f16(x[4], x[5]), tc::pack_f16(x[6], x[7]));
+            *reinterpret_cast<uint4*>(act_lo + dst[u]) = make_uint4(tc::pack_f16(l[0], l[1]), tc::pack_f16(l[2], l[3]),
+                                                                    tc::pack_f16(l[4], l[5]), tc::pack_f16(l[6], l[7]));
+          }
+      }
+    }
+    tc::fence_async_smem();
+    __syncthreads();
+
+    if (warp == EPI_WARPS) {
+      // =============================== weight producer ===============================
+      if (lane == 0) {
+        for (int nt = 0; nt < nnt; ++nt)
+          for (int kb = 0; kb < nkb; ++kb, ++w_it) {
+            const uint32_t s = w_it % SSTAGES, ph = (w_it / SSTAGES) & 1;
+            tc::mbar_wait_bounded(&ctl.empty[s], ph ^ 1);
+            tc::mbar_arrive_expect_tx(&ctl.full[s], 2 * W_BLOCK);
+            tc::bulk_copy_g2s(w_u + s * 2 * W_BLOCK, a.Wp + (size_t)(nt * nkb + kb) * 2 * W_BLOCK, 2 * W_BLOCK, &ctl.full[s]);
+          }
+      } else {
+        w_it += nnt * nkb;
+      }
+      w_it = __shfl_sync(0xffffffffu, w_it, 0);
+    } else if (warp == EPI_WARPS + 1) {
+      // =============================== MMA issuer ===============================
+      if (lane == 0) {
+        for (int nt = 0; nt < nnt; ++nt, ++acc_it) {
+          const uint32_t buf = acc_it & 1;
+          tc::mbar_wait_bounded(&ctl.accempty[buf], ((acc_it >> 1) & 1) ^ 1);
+          tc::fence_after_sync();
+          for (int kb = 0; kb < nkb; ++kb, ++w_it) {
+            const uint32_t s = w_it % SSTAGES, ph = (w_it / SSTAGES) & 1;
+            tc::mbar_wait_bounded(&ctl.full[s], ph);
+            tc::fence_after_sync();
+#pragma unroll
+            for (int j = 0; j < KB / 16; ++j) {
+              const uint32_t koff = (kb * (KB / 8) + 2 * j) * SCHUNK;
+              const uint64_t dwh = tc::make_desc(w_u + s * 2 * W_BLOCK + 2 * j * CHUNK, CHUNK, 128);
+              const uint64_t dwl = tc::make_desc(w_u + s * 2 * W_BLOCK + W_BLOCK + 2 * j * CHUNK, CHUNK, 128);
+              const uint64_t dah = tc::make_desc(ah_u + koff, SCHUNK, 128);
+              const uint64_t dal = tc::make_desc(al_u + koff, SCHUNK, 128);
+              tc::mma_f16(tmem + buf * SBM, dwh, dah, idesc, (kb | j) != 0);
+              tc::mma_f16(tmem + buf * SBM, dwl, dah, idesc, true);
+              tc::mma_f16(tmem + buf * SBM, dwh, dal, idesc, true);
+            }
+            tc::mma_commit(&ctl.empty[s]);
+          }
+          tc::mma_commit(&ctl.accfull[buf]);
+        }
+      } else {
+        w_it += nnt * nkb; acc_it += nnt;
+      }
+      w_it = __shfl_sync(0xffffffffu, w_it, 0);
+      acc_it = __shfl_sync(0xffffffffu, acc_it, 0);
+    } else {
+      // =============================== epilogue warps ===============================
+      // warp w reads TMEM lanes 32 (w % 4) .. (= output columns nt*128 + 32 (w % 4) + lane) and the 32 accumulator columns
+      // (= tile rows) 32 (w / 4) ..; one store instruction per row: 32 lanes x 4 B = one 128-byte segment of C
+      const int q = warp & 3, half = warp >> 2;
+      const uint32_t tlane = tmem + ((uint32_t)(q * 32) << 16);
+      uint32_t live_mask = 0;
+      for (int r = 0; r < 32; ++r) live_mask |= (live_s[half * 32 + r] != 0 ? 1u : 0u) << r;
+      for (int nt = 0; nt < nnt; ++nt, ++acc_it) {
+        const uint32_t buf = acc_it & 1;
+        tc::mbar_wait_bounded(&ctl.accfull[buf], (acc_it >> 1) & 1);
+        tc::fence_after_sync();
+        float v[32];
+        tc::tmem_ld32(tlane + buf * SBM + half * 32, v);
+        tc::tmem_ld_wait();
+        tc::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&ctl.accempty[buf]);     // the values are in registers: the accumulator may be reused
+        const int n = nt * BN + q * 32 + lane;
+        if (n < a.N) {
+          const float bv = bias_s[n];
+          float* c = a.C + (int64_t)(m0 + half * 32) * a.ldc + n;
+#pragma unroll
+          for (int r = 0; r < 32; ++r)
+            if ((live_mask >> r) & 1u) c[(int64_t)r * a.ldc] = v[r] + bv;
+        }
+      }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc<STMEM_COLS>(tmem);
+}
+
+inline size_t smem_bytes_split(int Kp, int nnt) {
+  return (size_t)2 * (Kp / 8) * SCHUNK + SSTAGES * 2 * W_BLOCK + (size_t)nnt * BN * 4 + SBM + sizeof(Ctl);
+}
+
 inline size_t smem_bytes(int Kp, int nnt) {
   return (size_t)(Kp / 8) * CHUNK + STAGES * W_BLOCK + EPI_WARPS * 32 * TILE_LD * 4 + (size_t)nnt * BN * 4 + BM + sizeof(Ctl);
 }
@@ -277,14 +462,16 @@ extern "C" int64_t ssb_proj_packed_bytes(int64_t N, int64_t K1, int64_t K2) {
   using namespace ssb::gemm2;
   return (int64_t)round_up((int)N, BN) * kp_of((int)K1, (int)K2) * 2;
 }
+// same for the split (hi | lo) packing of ssb_proj_prepack_split
+extern "C" int64_t ssb_proj_packed_bytes_split(int64_t N, int64_t K1, int64_t K2) { return 2 * ssb_proj_packed_bytes(N, K1, K2); }
 
 // Packs [W_a ; W_b] (n_each rows each, row stride ldw, K1+K2 columns; W_b may be NULL with N = n_each) into the
 // fp16 block layout ssb_proj_gemm streams.  A derived cache of the state-dict tensors: rebuild after they change.
 // gru_blocked = 1 (n_each = 3 * hidden, hidden % 4 == 0): output column order becomes [dir][rank 0..3][gate r,z,n][hidden/4]
 // instead of [dir][gate][hidden], so that the 3 x 48 values one GRU cluster CTA needs of a row are contiguous
 // (ssb_gru_layer_fwd_tc gi_layout = 1); the bias passed to ssb_proj_gemm must use the same order (ssb_gru_fold_bias).
-extern "C" int ssb_proj_prepack(const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int64_t K1, int64_t K2,
-                                int32_t gru_blocked, void* packed, void* stream) {
+static int proj_prepack_impl(const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int64_t K1, int64_t K2,
+                             int32_t gru_blocked, int32_t split, void* packed, void* stream) {
   using namespace ssb;
   using namespace ssb::gemm2;
   SSB_REQUIRE(W_a && packed, "null pointer");
@@ -295,9 +482,19 @@ extern "C" int ssb_proj_prepack(const float* W_a, const float* W_b, int64_t ldw,
   SSB_REQUIRE(kp_of((int)K1, (int)K2) <= MAX_KP && N <= MAX_N, "K > 384 or N > 1152 not supported");
   const int items = round_up(N, BN) * (kp_of((int)K1, (int)K2) / 8);
   prepack_kernel<<<cdiv(items, 256), 256, 0, (cudaStream_t)stream>>>(W_a, W_b ? W_b : W_a, ldw, (int)n_each, (int)K1, (int)K2, N, gru_blocked,
-                                                                   reinterpret_cast<uint8_t*>(packed));
+                                                                   split, reinterpret_cast<uint8_t*>(packed));
   SSB_LAUNCH_CHECK();
   return SSB_OK;
+}
+extern "C" int ssb_proj_prepack(const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int64_t K1, int64_t K2,
+                                int32_t gru_blocked, void* packed, void* stream) {
+  return proj_prepack_impl(W_a, W_b, ldw, n_each, K1, K2, gru_blocked, 0, packed, stream);
+}
+// Split packing for ssb_proj_gemm_split: every 16 KB fp16 block is followed by the block of residuals w - fp16(w)
+// (ssb_proj_packed_bytes_split bytes).
+extern "C" int ssb_proj_prepack_split(const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int64_t K1, int64_t K2,
+                                      int32_t gru_blocked, void* packed, void* stream) {
+  return proj_prepack_impl(W_a, W_b, ldw, n_each, K1, K2, gru_blocked, 1, packed, stream);
 }
 
 // C[M, N] = [A1 | A2] . packed^T + bias (fp16 operands, fp32 accumulation in TMEM).  lengths/T (optional): rows of
@@ -327,6 +524,36 @@ extern "C" int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const fl
   const int m_tiles = cdiv(M, BM);
   SSB_CUDA(cudaFuncSetAttribute(proj_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   proj_gemm_kernel<<<m_tiles < kSMs ? m_tiles : kSMs, THREADS, smem, (cudaStream_t)stream>>>(a);
+  SSB_LAUNCH_CHECK();
+  return SSB_OK;
+}
+
+// C[M, N] = [A1 | A2] . W^T + bias at fp32-parity grade (fp16 hi/lo split of both operands, three products, fp32 accumulation
+// in TMEM): the input projection of the split-mode recurrence for both directions in one persistent launch.  packed comes
+// from ssb_proj_prepack_split.  Same alignment rules as ssb_proj_gemm; C is fp32.
+extern "C" int ssb_proj_gemm_split(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                                   const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
+                                   const int64_t* lengths, int64_t T, void* stream) {
+  using namespace ssb;
+  using namespace ssb::gemm2;
+  SSB_REQUIRE(A1 && packed && C, "null pointer");
+  SSB_REQUIRE(K1 > 0 && K1 % 4 == 0 && lda1 % 4 == 0, "K1/lda1 must be multiples of 4");
+  SSB_REQUIRE(!A2 || (K2 > 0 && K2 % 4 == 0 && lda2 % 4 == 0), "K2/lda2 must be multiples of 4");
+  SSB_REQUIRE(((uintptr_t)A1 & 15) == 0 && ((uintptr_t)A2 & 15) == 0 && ((uintptr_t)packed & 15) == 0, "operands must be 16-byte aligned");
+  SSB_REQUIRE(!lengths || T > 0, "row mask needs T");
+  SSB_REQUIRE(((uintptr_t)C & 3) == 0, "C must be 4-byte aligned");
+  if (!A2) K2 = 0;
+  const int Kp = kp_of((int)K1, (int)K2);
+  SSB_REQUIRE(Kp <= MAX_KP && N <= MAX_N && N > 0, "K > 384 or N > 1152 not supported");
+  SSB_REQUIRE(M < (int64_t)1 << 31, "M too large");
+  if (M == 0) return SSB_OK;
+  Args a{A1, lda1, (int)K1, A2, lda2, (int)K2, reinterpret_cast<const uint8_t*>(packed), bias, C, ldc, (int)M, (int)N, 0, lengths, (int)T};
+  const int nnt = cdiv(N, BN);
+  const size_t smem = smem_bytes_split(Kp, nnt);
+  SSB_REQUIRE(smem <= 232448, "shared-memory budget");
+  const int m_tiles = cdiv(M, SBM);
+  SSB_CUDA(cudaFuncSetAttribute(proj_gemm_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  proj_gemm_split_kernel<<<m_tiles < kSMs ? m_tiles : kSMs, THREADS, smem, (cudaStream_t)stream>>>(a);
   SSB_LAUNCH_CHECK();
   return SSB_OK;
 }

@@ -35,6 +35,8 @@
 // one copy of the weight operands; while one slot waits for its MMAs the others compute.  fp16 mode: four 128-thread
 // slots; kSplit: two 256-thread slots, operands are fp16 hi + lo and D += Ahi.Bhi + Ahi.Blo + Alo.Bhi (fp32-parity grade;
 // conv1: x.Whi + x.Wlo with x exact).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -49,11 +51,11 @@ constexpr int C3 = 24, C3P = 32, E = 32;
 // layout ssb_roi_cnn_bwd reads -- see roi_cnn.cuh: SAVED_*).
 constexpr int SV_A1 = 0, SV_A2 = 36864, SV_IDX1 = 55296, SV_IDX2 = 57600, SV_MASK3 = 58752, SV_MEAN3 = 59904, SV_BYTES = 60000;
 constexpr int RING_BYTES = NPIX;                       // raw u8 frame staged by one bulk copy
-constexpr int C1_ROUNDS = 5, C1_TPR = 2;               // conv1: 9 tiles in rounds of 2 (last round: 1)
+constexpr int C1_ROUNDS = 3, C1_TPR = 4;               // conv1: 9 tiles in rounds of 4 (last round: 1) -- every round is a
+                                                       // trip through the tensor pipe's queue behind the other slots' batches
 constexpr int PATCH_PX = C1_TPR * 128;                 // pooled pixels per round
-constexpr int PATCH_CHUNK = PATCH_PX * 16;             // 4,096: one k-chunk (two patch rows) of a round
-constexpr int PATCH_BUF = 2 * PATCH_CHUNK;             // 8,192 per round; two rounds in flight
-constexpr int PATCH_BYTES = 2 * PATCH_BUF;             // 16,384
+constexpr int PATCH_CHUNK = PATCH_PX * 16;             // 8,192: one k-chunk (two patch rows) of a round
+constexpr int PATCH_BUF = 2 * PATCH_CHUNK;             // 16,384 per round
 constexpr int P1_ROWS = 13, P1_COLS = 25;              // a1 parity plane: [13][25] pixels x 16 B
 constexpr int P1_PLANE = P1_ROWS * P1_COLS * 16;       // 5,200
 constexpr int A1_BYTES = 4 * P1_PLANE;                 // 20,800
@@ -68,10 +70,13 @@ struct Lay {
   static constexpr int P = kSplit ? 2 : 1;
   static constexpr int W3_ROWS = kSplit ? 64 : 32;     // conv3 keeps hi|lo stacked along N (v1 scheme)
   static constexpr int W3_CHUNK = W3_ROWS * 16, W3_BYTES = 18 * W3_CHUNK;
-  static constexpr int W1_ROWS = kSplit ? 64 : 32;     // conv1 weights: hi|lo stacked along N in split mode (the input is exact)
+  static constexpr int W1_ROWS = kSplit ? 64 : 32;     // conv1 weights: rows [0,32) hi, [32,64) lo (split mode; the input is exact)
   static constexpr int W1_CHUNK = W1_ROWS * 16, W1_BYTES = 2 * W1_CHUNK;
-  // per-slot region R0: conv1 patch double buffer during conv1, a2 afterwards
-  static constexpr int R0_A = PATCH_BYTES, R0_B = P * A2_BYTES;
+  // conv1 double buffering (patches and TMEM columns of round r+1 while round r is in the tensor core / epilogue): split
+  // mode only -- its slots have 256 TMEM columns and R0 is 30 KB anyway; the four fp16-mode slots have 128 columns each
+  static constexpr int NBUF1 = kSplit ? 2 : 1;
+  // per-slot region R0: conv1 patch buffer(s) during conv1, a2 afterwards
+  static constexpr int R0_A = NBUF1 * PATCH_BUF, R0_B = P * A2_BYTES;
   static constexpr int R0_BYTES = ((R0_A > R0_B ? R0_A : R0_B) + 127) / 128 * 128;
   static constexpr int A1_ALLOC = (P * A1_BYTES + 1408 + 127) / 128 * 128;    // + over-read slack of the last conv2 tile (1,360 B)
   static constexpr int SLOT_BYTES = RING_BYTES + R0_BYTES + A1_ALLOC;
@@ -91,6 +96,7 @@ struct Shared {                                        // one per CTA, after the
   alignas(16) float b2[C2];
   alignas(16) float b3[C3P];
   alignas(16) float ws1[9][C1];                        // conv1: sum of the effective weights over the in-frame taps, per border class
+  uint32_t gtab[288];                                  // conv1 group order: [0,13) a1 cell offset of pixel 4g-1, bit 15 (py+1)&1, [16,21) py, [21,25) g
   float wfc[E][C3];
   float bfc[E];
   uint32_t tmem_base;
@@ -183,7 +189,8 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   constexpr bool kPipe2 = TMEM_PER_SLOT < 3 * (kSplit ? 128 : 64);   // conv2's three tiles do not fit: commit tile by tile
   static_assert(TMEM_PER_SLOT >= 2 * (kSplit ? 128 : 64), "a slot needs two conv2 tiles of TMEM columns");
   static_assert(kPipe2, "the non-pipelined conv2 path was removed");
-  constexpr int E1 = C1_TPR / NWG;                     // conv1 epilogue tiles per thread and round: 2 (ST=128) or 1 (ST=256)
+  constexpr int E1 = C1_TPR / NWG;                     // conv1 epilogue tiles per thread and round: 4 (ST=128) or 2 (ST=256)
+  constexpr int NB1 = L::NBUF1;
   static_assert(C1_TPR % NWG == 0 && ST >= 64, "conv1 round / slot shape");
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* w1op = smem + kSlots * L::SLOT_BYTES;
@@ -216,6 +223,12 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       }
     sh.ws1[e][co] = acc;
   }
+  for (int og = threadIdx.x; og < 288; og += ST * kSlots) {
+    int py, g;
+    group_pos(og, py, g);
+    const int rr = py + 1;
+    sh.gtab[og] = (uint32_t)(((rr >> 1) * P1_COLS + 2 * g) * 16) | ((uint32_t)(rr & 1) << 15) | ((uint32_t)py << 16) | ((uint32_t)g << 21);
+  }
   for (int i = tid; i < L::A1_ALLOC / 16; i += ST) reinterpret_cast<uint4*>(a1)[i] = make_uint4(0, 0, 0, 0);
   if (threadIdx.x < 32) tc::tmem_alloc<512>(&sh.tmem_base);
   if (tid == 32) {
@@ -229,9 +242,10 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   const uint32_t tmem = sh.tmem_base + slot * TMEM_PER_SLOT;
   const uint32_t r0_u = tc::smem_u32(r0), a1_u = tc::smem_u32(a1), ring_u = tc::smem_u32(ring);
   const uint32_t w1_u = tc::smem_u32(w1op), w2_u = tc::smem_u32(w2op), w3_u = tc::smem_u32(w3op);
-  constexpr uint32_t idesc1 = tc::make_idesc_f16(128, kSplit ? 64 : 32), idesc2 = tc::make_idesc_f16(128, 64);
+  constexpr uint32_t idesc1 = tc::make_idesc_f16(128, 32), idesc2 = tc::make_idesc_f16(128, 64);
   constexpr uint32_t idesc2s = tc::make_idesc_f16(128, 128);            // hi|lo stacked along N
-  constexpr int C1W = kSplit ? 64 : 32, C2W = kSplit ? 128 : 64;        // TMEM columns per conv1 / conv2 tile
+  constexpr int C1W = 32, C2W = kSplit ? 128 : 64;                      // TMEM columns per conv1 / conv2 tile
+  static_assert(NB1 * C1_TPR * C1W <= TMEM_PER_SLOT, "conv1 rounds do not fit the slot's TMEM columns");
   constexpr uint32_t idesc3_hi = tc::make_idesc_f16(128, kSplit ? 64 : 32), idesc3_lo = tc::make_idesc_f16(128, 32);
   constexpr int COLS3 = kSplit ? 64 : 32;
   uint32_t ph0 = 0, ph1 = 0, ph2 = 0, rph = 0;
@@ -272,11 +286,14 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   // four raw pixels each, converted u8 -> fp16 exactly (0x6400 | b is 1024 + b; minus 1024).  A group's four pooled pixels
   // need image columns 8g-1 .. 8g+8 of each row: bytes 3 of word 2g-1, words 2g and 2g+1, byte 0 of word 2g+2.
   auto build = [&](int r) {
-    const int ng = (r == C1_ROUNDS - 1) ? 32 : 64;     // groups of this round (last round: one tile)
-    if (tid < 2 * ng) {
-      const int kc = tid >= ng ? 1 : 0, gl = tid - kc * ng;
-      int py, g;
-      group_pos(r * 64 + gl, py, g);
+    const int ng = (r == C1_ROUNDS - 1) ? 32 : 32 * C1_TPR;     // groups of this round (last round: one tile)
+#pragma unroll
+    for (int it0 = 0; it0 < 2 * 32 * C1_TPR; it0 += ST) {
+      const int it = it0 + tid;
+      if (it >= 2 * ng) break;
+      const int kc = it >= ng ? 1 : 0, gl = it - kc * ng;
+      const uint32_t gt = sh.gtab[r * 32 * C1_TPR + gl];
+      const int py = (gt >> 16) & 31, g = gt >> 21;
       const int y0 = 2 * py - 1 + 2 * kc;              // patch rows 2kc, 2kc+1 = image rows y0, y0+1
       uint32_t o[4][4];
 #pragma unroll
@@ -303,19 +320,20 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           o[e][2 * rr] = h01; o[e][2 * rr + 1] = h23;
         }
       }
-      uint8_t* pb = r0 + (r & 1) * PATCH_BUF + kc * PATCH_CHUNK + ((gl >> 5) * 128 + (gl & 31)) * 16;
+      uint8_t* pb = r0 + (r % NB1) * PATCH_BUF + kc * PATCH_CHUNK + ((gl >> 5) * 128 + (gl & 31)) * 16;
 #pragma unroll
       for (int e = 0; e < 4; ++e) *reinterpret_cast<uint4*>(pb + e * 32 * 16) = make_uint4(o[e][0], o[e][1], o[e][2], o[e][3]);
     }
   };
-  auto conv1_issue = [&](int r) {                      // tid 0: the round's tiles, one MMA each (K = 16, N = 32 or hi|lo 64)
+  auto conv1_issue = [&](int r) {                      // tid 0: the round's tiles, K = 16, N = 32: x.W (fp16) or x.W_hi + x.W_lo
     const int nt = (r == C1_ROUNDS - 1) ? 1 : C1_TPR;
     for (int tl = 0; tl < nt; ++tl) {
-      const uint64_t da = tc::make_desc(r0_u + (r & 1) * PATCH_BUF + tl * 2048, PATCH_CHUNK, 128);
-      const uint64_t db = tc::make_desc(w1_u, L::W1_CHUNK, 128);
-      tc::mma_f16(tmem + (r & 1) * (C1_TPR * C1W) + tl * C1W, da, db, idesc1, false);
+      const uint64_t da = tc::make_desc(r0_u + (r % NB1) * PATCH_BUF + tl * 2048, PATCH_CHUNK, 128);
+      const uint32_t dcol = tmem + (r % NB1) * (C1_TPR * C1W) + tl * C1W;
+      tc::mma_f16(dcol, da, tc::make_desc(w1_u, L::W1_CHUNK, 128), idesc1, false);
+      if (kSplit) tc::mma_f16(dcol, da, tc::make_desc(w1_u + 32 * 16, L::W1_CHUNK, 128), idesc1, true);
     }
-    tc::mma_commit(&mz.bar[r & 1]);
+    tc::mma_commit(&mz.bar[r % NB1]);
   };
 
   long long f = frames;
@@ -374,33 +392,27 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       for (int co = 0; co < 8; ++co) cint[co] = fmaf(nmean * inv_s, wsi[co], bb[co]);
     }
 
-    // ================= conv1 + ReLU + pool: 5 rounds of 2 tiles (last: 1); the patches of round r+1 are built while
-    // the tensor core works on round r; TMEM columns and patch buffers alternate
-    long long fnext = frames;
+    // ================= conv1 + ReLU + pool: rounds of 4, 4 and 1 tiles.  Split mode: the patches of round r+1 are built
+    // while the tensor core works on round r, TMEM columns and patch buffers alternate.  fp16 mode (one buffer): the
+    // patches of round r+1 are built as soon as round r's MMAs have consumed theirs, before its epilogue.
+    long long fnext = frames, cand = frames;
+    int64_t cand_len = 0;
 #pragma unroll 1
     for (int r = 0; r < C1_ROUNDS; ++r) {
-      if (r + 1 < C1_ROUNDS) build(r + 1);
-      if (r & 1) { tc::mbar_wait_bounded(&mz.bar[1], ph1); ph1 ^= 1; } else { tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1; }
+      if (NB1 == 2 && r + 1 < C1_ROUNDS) build(r + 1);
+      if (NB1 == 2 && (r & 1)) { tc::mbar_wait_bounded(&mz.bar[1], ph1); ph1 ^= 1; } else { tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1; }
       tc::fence_after_sync();
+      if (NB1 == 1 && r + 1 < C1_ROUNDS) build(r + 1);
       const int nt = (r == C1_ROUNDS - 1) ? 1 : C1_TPR;
 #pragma unroll
       for (int k = 0; k < E1; ++k) {
-        const int tl = NWG == 1 ? k : wg;
+        const int tl = k * NWG + wg;
         if (tl < nt) {
           float v[32];
-          const uint32_t tcol = tq + (r & 1) * (C1_TPR * C1W) + tl * C1W;
-          tc::tmem_ld32(tcol, v);
-          if (kSplit) {
-            float w[32];
-            tc::tmem_ld32(tcol + 32, w);
-            tc::tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] += w[i];             // x.W_hi + x.W_lo
-          } else {
-            tc::tmem_ld_wait();
-          }
-          int py, g;
-          group_pos((r * C1_TPR + tl) * 32 + lane, py, g);
+          tc::tmem_ld32(tq + (r % NB1) * (C1_TPR * C1W) + tl * C1W, v);
+          tc::tmem_ld_wait();
+          const uint32_t gt = sh.gtab[(r * C1_TPR + tl) * 32 + lane];
+          const int py = (gt >> 16) & 31, g = gt >> 21;
           const int px = 4 * g + q, Pp = py * W1 + px;                    // this thread's pooled pixel (row m = q*32 + lane of the tile)
           const bool border = py == 0 || py == H1 - 1 || px == 0 || px == W1 - 1;
           float hi[8], lo[8];
@@ -455,8 +467,8 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
 #pragma unroll
             for (int co = 0; co < 8; ++co) tc::split_f16(hi[co], hi[co], lo[co]);           // single pass: pack8 rounds once
           }
-          const int rr = py + 1, cc = px + 1;                            // pooled pixel -> a1 padded parity planes
-          const uint32_t off = ((rr & 1) * 2 + (cc & 1)) * P1_PLANE + ((rr >> 1) * P1_COLS + (cc >> 1)) * 16;
+          // pooled pixel -> a1 padded parity planes: row parity from the table, column parity (q+1)&1, cell 2g + (q+1)/2
+          const uint32_t off = (((gt >> 15) & 1) * 2 + ((q + 1) & 1)) * P1_PLANE + (gt & 0x7fffu) + ((q + 1) >> 1) * 16;
           *reinterpret_cast<uint4*>(a1 + off) = pack8(hi);
           if (kSplit) *reinterpret_cast<uint4*>(a1 + A1_BYTES + off) = pack8(lo);
         }
@@ -465,12 +477,26 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       tc::fence_async_smem();
       slot_sync<ST>(slot);                              // patches of round r+1 complete; round r's TMEM columns and patch buffer free
       if (tid == 0 && r + 1 < C1_ROUNDS) { tc::fence_after_sync(); conv1_issue(r + 1); }
-      if (r == C1_ROUNDS - 2 && warp == 1) {
-        // the last patches are built: the ring buffer is free (every reader passed the barrier above, after its
-        // fence.proxy.async) -- find this slot's next frame and start its copy; it travels under the rest of this frame
-        fnext = acquire(handout_base + __shfl_sync(0xffffffffu, handout, 0));
-        start_copy(fnext);
-        if (lane == 0) mz.next = fnext;
+      if (warp == 1) {
+        if (r == 0) {
+          // hand-out, split in two so that neither global round trip is waited for: the atomic was issued at the top of
+          // the frame, the candidate's clip length is requested here and first looked at a round later
+          cand = handout_base + __shfl_sync(0xffffffffu, handout, 0);
+          cand_len = (lengths && cand < frames) ? lengths[cand / T] : (int64_t)T;
+        }
+        if (r == C1_ROUNDS - 2) {
+          // the last patches are built: the ring buffer is free (every reader passed the barrier above, after its
+          // fence.proxy.async) -- start the copy of this slot's next frame; it travels under the rest of this frame
+          fnext = cand;
+          if (cand < frames && (int64_t)(cand % T) >= cand_len) {        // a padded frame: zero embedding, look further
+            out[cand * out_stride + lane] = 0.f;
+            unsigned int h = 0;
+            if (lane == 0) h = atomicAdd(counter, 1u);
+            fnext = acquire(handout_base + __shfl_sync(0xffffffffu, h, 0));
+          }
+          start_copy(fnext);
+          if (lane == 0) mz.next = fnext;
+        }
       }
     }
 
@@ -699,6 +725,13 @@ constexpr size_t smem_total() {
 // saved (nullable, passes = 3): B*T records of ssb_roi_cnn_saved_bytes() bytes that receive the pooled activations, pool
 // argmax maps, conv3 ReLU mask and channel means of every valid frame, for ssb_roi_cnn_bwd.
 extern "C" int64_t ssb_roi_cnn_saved_bytes(void) { return ssb::cnn3::SV_BYTES; }
+int ssb_roi_cnn_fwd_v3_(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T, const float* const* weights,
+                        int32_t standardize, float* out, int64_t out_stride, void* stream);
+// passes = 1 runs K2 v3 unless SSB_K2_FP16_V4=1 (A/B switch for tools/bench_stage.py; read once)
+static bool ssb_k2_single_pass_v4_() {
+  static const bool v4 = [] { const char* e = getenv("SSB_K2_FP16_V4"); return e && e[0] == '1'; }();
+  return v4;
+}
 extern "C" int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
                                    int32_t roi_h, int32_t roi_w, const float* const* weights, int32_t standardize,
                                    float* out, int64_t out_stride, int32_t passes, void* saved, void* stream) {
@@ -732,6 +765,8 @@ extern "C" int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int
       roi_cnn_tc3_kernel<true, kSlots, ST, false><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride,
                                                                                  counter, nullptr);
     }
+  } else if (!ssb_k2_single_pass_v4_()) {
+    return ssb_roi_cnn_fwd_v3_(R, lengths, B, T, weights, standardize, out, out_stride, stream);   // roi_cnn_v3.cu
   } else {
     constexpr int kSlots = 4, ST = 128;
     constexpr size_t smem = smem_total<false, kSlots>();

@@ -92,9 +92,10 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
             ops.proj_gemm(A2d, packed, fold, g.view(B * T, 2 * G3), 2 * G3, A2=extra, lengths=lengths, T=T)
             return ops.gru_layer_fwd_tc(g, lengths, pl["weight_hh"][0], pl["bias_hh"][0], pl["weight_hh"][1],
                                         pl["bias_hh"][1], passes=passes, order=order, gates=gates, gi_blocked=blk)
-        for d in (0, 1):
-            ops.gemm_tc(A2d, pl["weight_ih"][d], fold[d * G3:(d + 1) * G3], gi2d, A2=extra, passes=passes,
-                        lengths=lengths, T=T, c_col0=d * G3)
+        # split mode (fp32-parity grade): the same persistent GEMM with hi/lo operands, both directions in one launch
+        packed = ops.proj_prepack(pl["weight_ih"][0], pl["weight_ih"][1], A2d.shape[1], 0 if extra is None else extra.shape[1],
+                                  split=True)
+        ops.proj_gemm(A2d, packed, fold, gi2d, 2 * G3, A2=extra, lengths=lengths, T=T, split=True)
         return ops.gru_layer_fwd_tc(gi, lengths, pl["weight_hh"][0], pl["bias_hh"][0], pl["weight_hh"][1],
                                     pl["bias_hh"][1], passes=passes, order=order, gates=gates)
 

@@ -275,8 +275,10 @@ def gemm_tc(A1: torch.Tensor, W: torch.Tensor, bias, C2d: torch.Tensor, A2: Opti
     return C2d
 
 
-def proj_prepack(W_a: torch.Tensor, W_b: Optional[torch.Tensor], K1: int, K2: int = 0, gru_blocked: bool = False) -> torch.Tensor:
-    """[W_a ; W_b] (each [n_each, K1+K2] fp32) -> fp16 block layout streamed by proj_gemm (a derived cache)."""
+def proj_prepack(W_a: torch.Tensor, W_b: Optional[torch.Tensor], K1: int, K2: int = 0, gru_blocked: bool = False,
+                 split: bool = False) -> torch.Tensor:
+    """[W_a ; W_b] (each [n_each, K1+K2] fp32) -> fp16 block layout streamed by proj_gemm (a derived cache).
+    split: hi | lo blocks for proj_gemm(..., split=True) (fp32-parity grade)."""
     _need(W_a, torch.float32, "W_a")
     if W_b is not None:
         _need(W_b, torch.float32, "W_b")
@@ -284,19 +286,29 @@ def proj_prepack(W_a: torch.Tensor, W_b: Optional[torch.Tensor], K1: int, K2: in
     N = n_each * (2 if W_b is not None else 1)
     L = _lib.lib()
     L.ssb_proj_packed_bytes.restype = i64
-    nbytes = L.ssb_proj_packed_bytes(i64(N), i64(K1), i64(K2))
+    L.ssb_proj_packed_bytes_split.restype = i64
+    nbytes = (L.ssb_proj_packed_bytes_split if split else L.ssb_proj_packed_bytes)(i64(N), i64(K1), i64(K2))
     packed = torch.empty(nbytes, device=W_a.device, dtype=torch.uint8)
-    check(L.ssb_proj_prepack(ptr(W_a), ptr(W_b), i64(W_a.stride(0)), i64(n_each), i64(K1), i64(K2),
-                             i32(1 if gru_blocked else 0), ptr(packed), stream_ptr()))
+    fn = L.ssb_proj_prepack_split if split else L.ssb_proj_prepack
+    check(fn(ptr(W_a), ptr(W_b), i64(W_a.stride(0)), i64(n_each), i64(K1), i64(K2),
+             i32(1 if gru_blocked else 0), ptr(packed), stream_ptr()))
     return packed
 
 
 def proj_gemm(A1: torch.Tensor, packed: torch.Tensor, bias, C2d: torch.Tensor, N: int, A2: Optional[torch.Tensor] = None,
-              lengths=None, T: int = 0):
+              lengths=None, T: int = 0, split: bool = False):
     # C2d may be float32 or float16 (fp16 gi for the single-pass recurrence)
-    """C[:, :N] = [A1 | A2] @ packed^T + bias: both directions' input projections in one persistent tcgen05 GEMM."""
+    """C[:, :N] = [A1 | A2] @ packed^T + bias: both directions' input projections in one persistent tcgen05 GEMM.
+    split: fp32-parity grade (hi/lo split of both operands; packed from proj_prepack(..., split=True); C fp32)."""
     M, K1 = A1.shape
     K2 = 0 if A2 is None else A2.shape[1]
+    if split:
+        if not (C2d.is_cuda and C2d.dtype == torch.float32 and C2d.stride(1) == 1):
+            raise _lib.SsbError("split projection: C must be a CUDA float32 matrix with unit column stride")
+        check(_lib.lib().ssb_proj_gemm_split(ptr(A1), i64(A1.stride(0)), i64(K1), ptr(A2), i64(0 if A2 is None else A2.stride(0)),
+                                             i64(K2), ptr(packed), ptr(bias), ptr(C2d), i64(C2d.stride(0)), i64(M), i64(N),
+                                             ptr(lengths), i64(T), stream_ptr()))
+        return C2d
     check(_lib.lib().ssb_proj_gemm(ptr(A1), i64(A1.stride(0)), i64(K1), ptr(A2), i64(0 if A2 is None else A2.stride(0)),
                                    i64(K2), ptr(packed), ptr(bias), ptr(C2d), i64(C2d.stride(0)), i64(M), i64(N),
                                    ptr(lengths), i64(T), i32(1 if C2d.dtype == torch.float16 else 0), stream_ptr()))

@@ -237,6 +237,49 @@ def test_proj_gemm_vs_fp64(M, n_each, K1, K2, T):
         assert torch.equal(h[live][:, :N], C2.cpu()[live].half())
 
 
+@pytest.mark.parametrize("M,n_each,K1,K2,T", [(64, 576, 180, 32, 0), (1000, 576, 384, 0, 10), (77, 576, 180, 0, 0),
+                                              (39960, 576, 180, 32, 90), (300, 200, 64, 0, 0), (130, 576, 384, 0, 0)])
+def test_proj_gemm_split_vs_fp64(M, n_each, K1, K2, T):
+    """The fp32-parity projection GEMM (hi/lo split of both operands, weights as the M = 128 operand, transposed
+    accumulator): within 2e-6 of the fp64 product of the raw fp32 operands (tolerance of the 1e-4 parity budget),
+    rows of padded frames and the columns past N untouched."""
+    dev = _cuda()
+    from silent_speech_b200 import ops
+    g = torch.Generator().manual_seed(M + K1 + 1)
+    A1 = torch.randn(M, K1, generator=g)
+    A2 = torch.randn(M, K2, generator=g) if K2 else None
+    Wa = torch.randn(n_each, K1 + K2, generator=g) * 0.1
+    Wb = torch.randn(n_each, K1 + K2, generator=g) * 0.1
+    b = torch.randn(2 * n_each, generator=g)
+    A = A1 if A2 is None else torch.cat([A1, A2], 1)
+    ref = A.double() @ torch.cat([Wa, Wb], 0).double().T + b.double()
+    N = 2 * n_each
+    C = torch.full((M, N + 4), -7.0, device=dev)
+    L = None
+    if T:
+        Lh = torch.randint(1, T + 1, (M // T,), generator=g)
+        Lh[0] = T
+        L = Lh.to(dev)
+    packed = ops.proj_prepack(Wa.to(dev), Wb.to(dev), K1, K2, split=True)
+    ops.proj_gemm(A1.to(dev), packed, b.to(dev), C[:, :N], N, A2=None if A2 is None else A2.to(dev), lengths=L, T=T, split=True)
+    torch.cuda.synchronize()
+    out = C.cpu()
+    assert torch.all(out[:, N:] == -7.0)
+    live = torch.ones(M, dtype=torch.bool)
+    if T:
+        Mr = (M // T) * T
+        live = torch.zeros(M, dtype=torch.bool)
+        live[:Mr] = (torch.arange(T)[None, :] < Lh[:, None]).reshape(-1)
+        assert torch.all(out[~live][:, :N] == -7.0)
+    e = rel_err(out[live][:, :N], ref[live])
+    print(f"proj split M={M} K={K1}+{K2}: rel err {e:.2e}")
+    assert e < 2e-6
+    # repeated launches are bit-identical (ring phases, accumulator hand-over)
+    C2 = torch.full((M, N + 4), -7.0, device=dev)
+    ops.proj_gemm(A1.to(dev), packed, b.to(dev), C2[:, :N], N, A2=None if A2 is None else A2.to(dev), lengths=L, T=T, split=True)
+    assert torch.equal(C2.cpu(), out)
+
+
 @pytest.mark.parametrize("use_roi,B,chunk,pinned", [(True, 70, 16, True), (True, 37, 512, False), (False, 90, 8, True)])
 def test_infer_host_matches_device_forward(use_roi, B, chunk, pinned):
     """The host-buffer entry (bench.py's e2e arm): chunked, copy/compute-overlapped inference from host tensors returns

@@ -77,9 +77,8 @@ elif a.stage == "proj":
         packed = ops.proj_prepack(Wa, Wb, K1, K2)
         fn = lambda: ops.proj_gemm(A1, packed, bias, gi, 2 * G3, A2=A2, lengths=L, T=T)
     else:
-        def fn():
-            for d, W in enumerate((Wa, Wb)):
-                ops.gemm_tc(A1, W, bias[d * G3:(d + 1) * G3], gi, A2=A2, passes=3, lengths=L, T=T, c_col0=d * G3)
+        packed = ops.proj_prepack(Wa, Wb, K1, K2, split=True)
+        fn = lambda: ops.proj_gemm(A1, packed, bias, gi, 2 * G3, A2=A2, lengths=L, T=T, split=True)
     best, mean = timeit(fn)
     by = B * T * (2 * G3 + K1 + K2) * 4
     print(f"proj layer {a.layer} {a.precision} B={B}: best {best:.3f} ms mean {mean:.3f} ms  {by / best / 1e6:.0f} GB/s algorithmic (A read + C write)")
