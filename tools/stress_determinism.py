@@ -1,12 +1,14 @@
-"""Repeat each tensor-core stage on fixed inputs and report run-to-run deviations (race hunting; GPU only)."""
+"""Repeat each tensor-core stage on fixed inputs and report run-to-run deviations (race hunting; GPU only).
+compute-sanitizer is closed on this GPU pool, so bit-identity of repeated launches under allocator churn, together with
+the oracle comparisons of the test-suite, is the race check: every stage below is deterministic by construction
+(fixed reduction orders), so ANY differing bit is a synchronisation bug.  usage: python tools/stress_determinism.py [reps]"""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from oracle import ref_model
 from silent_speech_b200 import ops, synth
 
 dev = torch.device("cuda")
-p = ref_model.synth_params(7, use_roi=False)
+p = synth.synth_params(7, use_roi=False)
 B, T = 260, 64
 d = synth.clip_batch(B, T, mode="uniform", seed=9, use_roi=False)
 X = torch.from_numpy(d["X"]).to(dev); L = torch.from_numpy(d["lengths"]).to(dev)
@@ -72,3 +74,44 @@ for Bs, Ts in ((128, 3), (129, 5), (260, 64), (700, 40)):
                 bad += 1
     torch.cuda.synchronize()
     print(f"gi staging B={Bs} T={Ts}: {2 * reps} runs (standard / blocked alternating), mismatches {bad}")
+
+
+# K2 (TMA frame ring, named barriers per slot, TMEM ping-pong, dynamic frame hand-out) and the persistent projection GEMMs
+pr = {k: v.to(dev).contiguous() for k, v in synth.synth_params(13).items()}
+names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "roi_cnn.net.3.bias",
+         "roi_cnn.net.6.weight", "roi_cnn.net.6.bias", "roi_cnn.fc.weight", "roi_cnn.fc.bias"]
+wc = [pr[n] for n in names]
+dr = synth.clip_batch(200, 90, mode="uniform", seed=4)
+Rd, Ld = torch.from_numpy(dr["R"]).to(dev), torch.from_numpy(dr["lengths"]).to(dev)
+for passes in (3, 1):
+    first, bad = None, 0
+    for it in range(reps):
+        junk = torch.randn(1 << 20, device=dev) * 1e3
+        e = ops.roi_cnn_fwd(Rd, Ld, wc, passes=passes)
+        if first is None:
+            first = e.clone()
+        elif not torch.equal(e, first):
+            bad += 1
+            print(f"K2 passes={passes} it={it}: differs, max abs {float((e - first).abs().max()):.3e}")
+        del junk
+    torch.cuda.synchronize()
+    print(f"K2 passes={passes}: {reps} reps over {int(Ld.sum())} frames, mismatches {bad}")
+A = torch.randn(260 * 64, 384, device=dev)
+Wa, Wb = pr["gru.weight_ih_l1"], pr["gru.weight_ih_l1_reverse"]
+bias = torch.randn(2 * G3, device=dev)
+for split in (True, False):
+    packed = ops.proj_prepack(Wa, Wb, 384, 0, split=split)
+    first, bad = None, 0
+    for it in range(reps):
+        junk = torch.randn(1 << 20, device=dev) * 1e3
+        c = torch.full((260 * 64, 2 * G3), float("nan"), device=dev)
+        ops.proj_gemm(A, packed, bias, c, 2 * G3, lengths=L, T=T, split=split)
+        c = torch.where(mask.reshape(-1, 1), c, torch.zeros_like(c))
+        if first is None:
+            first = c.clone()
+        elif not torch.equal(c, first):
+            bad += 1
+            print(f"proj_gemm split={split} it={it}: differs")
+        del junk
+    torch.cuda.synchronize()
+    print(f"proj_gemm split={split}: {reps} reps, mismatches {bad}")
