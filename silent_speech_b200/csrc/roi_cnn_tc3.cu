@@ -248,6 +248,10 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   static_assert(NB1 * C1_TPR * C1W <= TMEM_PER_SLOT, "conv1 rounds do not fit the slot's TMEM columns");
   constexpr uint32_t idesc3_hi = tc::make_idesc_f16(128, kSplit ? 64 : 32), idesc3_lo = tc::make_idesc_f16(128, 32);
   constexpr int COLS3 = kSplit ? 64 : 32;
+  // base descriptors, built once: the issuing thread only adds compile-time offsets to them
+  const uint64_t d_patch = tc::make_desc(r0_u, PATCH_CHUNK, 128), d_w1 = tc::make_desc(w1_u, L::W1_CHUNK, 128);
+  const uint64_t d_a1 = tc::make_desc(a1_u, P1_PLANE, 128), d_w2 = tc::make_desc(w2_u, L::P * W2_CHUNK, 128);
+  const uint64_t d_a2 = tc::make_desc(r0_u, PLANE2, PITCH2 * 16), d_w3 = tc::make_desc(w3_u, L::W3_CHUNK, 128);
   uint32_t ph0 = 0, ph1 = 0, ph2 = 0, rph = 0;
   const int q = warp & 3, wg = warp >> 2;
   const int row = q * 32 + lane;                       // this thread's row of every 128-row tile (= TMEM lane)
@@ -328,10 +332,10 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   auto conv1_issue = [&](int r) {                      // tid 0: the round's tiles, K = 16, N = 32: x.W (fp16) or x.W_hi + x.W_lo
     const int nt = (r == C1_ROUNDS - 1) ? 1 : C1_TPR;
     for (int tl = 0; tl < nt; ++tl) {
-      const uint64_t da = tc::make_desc(r0_u + (r % NB1) * PATCH_BUF + tl * 2048, PATCH_CHUNK, 128);
+      const uint64_t da = tc::desc_add(d_patch, (r % NB1) * PATCH_BUF + tl * 2048);
       const uint32_t dcol = tmem + (r % NB1) * (C1_TPR * C1W) + tl * C1W;
-      tc::mma_f16(dcol, da, tc::make_desc(w1_u, L::W1_CHUNK, 128), idesc1, false);
-      if (kSplit) tc::mma_f16(dcol, da, tc::make_desc(w1_u + 32 * 16, L::W1_CHUNK, 128), idesc1, true);
+      tc::mma_f16(dcol, da, d_w1, idesc1, false);
+      if (kSplit) tc::mma_f16(dcol, da, tc::desc_add(d_w1, 32 * 16), idesc1, true);
     }
     tc::mma_commit(&mz.bar[r % NB1]);
   };
@@ -519,11 +523,11 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           // patch elements (r, 2h) and (r, 2h+1): column-parity planes 0 and 1 of row-parity plane r&1
           const uint32_t a_off = (r & 1) * 2 * P1_PLANE + ((r >> 1) * P1_COLS + h) * 16 + tl * 2048;
           const uint32_t b_off = (r * 4 + 2 * h) * (L::P * W2_CHUNK);
-          const uint64_t ah = tc::make_desc(a1_u + a_off, P1_PLANE, 128);
-          const uint64_t bh = tc::make_desc(w2_u + b_off, L::P * W2_CHUNK, 128);
+          const uint64_t ah = tc::desc_add(d_a1, a_off);
+          const uint64_t bh = tc::desc_add(d_w2, b_off);
           if (kSplit) {
             // columns [0,64) = A_hi.B_hi + A_lo.B_hi, columns [64,128) = A_hi.B_lo
-            const uint64_t al = tc::make_desc(a1_u + A1_BYTES + a_off, P1_PLANE, 128);
+            const uint64_t al = tc::desc_add(d_a1, A1_BYTES + a_off);
             tc::mma_f16(tmem + dcol, ah, bh, idesc2s, (r | h) != 0);
             tc::mma_f16(tmem + dcol, al, bh, idesc2, true);
           } else {
@@ -633,9 +637,9 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         for (int tap = 0; tap < 9; ++tap) {
           const int dy = tap / 3, dx = tap % 3;
           const uint32_t a_off = (dy * PITCH2 + tx * 8 + dx) * 16;
-          const uint64_t db = tc::make_desc(w3_u + 2 * tap * L::W3_CHUNK, L::W3_CHUNK, 128);
-          tc::mma_f16(tmem + tx * COLS3, tc::make_desc(r0_u + a_off, PLANE2, PITCH2 * 16), db, idesc3_hi, tap > 0);
-          if (kSplit) tc::mma_f16(tmem + tx * COLS3, tc::make_desc(r0_u + A2_BYTES + a_off, PLANE2, PITCH2 * 16), db, idesc3_lo, true);
+          const uint64_t db = tc::desc_add(d_w3, 2 * tap * L::W3_CHUNK);
+          tc::mma_f16(tmem + tx * COLS3, tc::desc_add(d_a2, a_off), db, idesc3_hi, tap > 0);
+          if (kSplit) tc::mma_f16(tmem + tx * COLS3, tc::desc_add(d_a2, A2_BYTES + a_off), db, idesc3_lo, true);
         }
         tc::mma_commit(&mz.bar[tx]);
       }

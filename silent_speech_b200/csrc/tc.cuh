@@ -26,6 +26,11 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_b
   return d;
 }
 
+// descriptor of the same layout `bytes` further into shared memory (bytes % 16 == 0): the start-address field is the low
+// 14 bits and shared memory ends below 2^18, so a plain add never carries into the next field -- one IADD instead of
+// rebuilding the descriptor (the MMA-issuing thread is a single instruction stream on every kernel's critical path)
+__device__ __forceinline__ uint64_t desc_add(uint64_t desc, uint32_t bytes) { return desc + (uint64_t)(bytes >> 4); }
+
 // 16-bit operand format of every tensor-core path: IEEE fp16 (11-bit significand: one pass is 8x more
 // accurate than bf16, and the hi/lo split reaches 2^-22) with saturating conversion; the operands of this
 // network (standardised pixels, ReLU maps, h in [-1,1], weights < 1, landmark features < 1e3) sit far inside
