@@ -49,7 +49,7 @@ FEAT_BYTES_ROWS = 478 * 12 + 720        # 6,456 B/frame when whole 5,736-byte la
 CPU_CHUNK = 64                          # clips per CPU-arm step (a bounded sample of the 4096-clip batch)
 DTYPE = {"fp32": "f32", "tc3": "f16 hi/lo split operands x3, f32 accumulate (f32-parity grade: logits within 1e-4 of the f32 CPU reference)",
          "fp16": "f16 operands, f32 accumulate (stated tolerance 1e-3)"}
-K2_NAME = {0: "roi_cnn_fwd_kernel", 1: "roi_cnn_tc3_kernel<split=false>", 3: "roi_cnn_tc3_kernel<split=true>"}
+K2_NAME = {0: "roi_cnn_fwd_kernel", 1: "roi_cnn_v3_kernel<split=false,4 slots x 128> (K2 v3)", 3: "roi_cnn_tc3_kernel<split=true,2 slots x 256> (K2 v4)"}
 PASSES = {"fp32": 0, "tc3": 3, "fp16": 1}
 
 

@@ -1,6 +1,7 @@
-"""Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per-kernel count, total and share."""
+"""Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per-kernel count, total and share.
+    python profiles/summarise_launches.py launches.csv [skip [count]]"""
 import csv, sys, collections, re
-def main(path, skip=0):
+def main(path, skip=0, count=None):
     rows = []
     with open(path) as f:
         lines = [l for l in f if not l.startswith("==")]
@@ -9,7 +10,7 @@ def main(path, skip=0):
             v = float(r["Metric Value"].replace(",", "")); u = r["Metric Unit"]
             ns = v * {"ns": 1, "us": 1e3, "ms": 1e6, "s": 1e9}.get(u, 1)
             rows.append((re.sub(r"\(.*", "", r["Kernel Name"])[:70], ns))
-    rows = rows[skip:]
+    rows = rows[skip:] if count is None else rows[skip:skip + count]
     agg = collections.OrderedDict()
     for k, ns in rows:
         c, t = agg.get(k, (0, 0.0)); agg[k] = (c + 1, t + ns)
@@ -19,4 +20,4 @@ def main(path, skip=0):
     for k, (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         print(f"{k:70s} {c:5d} {t/1e6:10.3f} {t/c/1e3:10.1f} {100*t/tot:6.1f}%")
 if __name__ == "__main__":
-    main(sys.argv[1], int(sys.argv[2]) if len(sys.argv) > 2 else 0)
+    main(sys.argv[1], int(sys.argv[2]) if len(sys.argv) > 2 else 0, int(sys.argv[3]) if len(sys.argv) > 3 else None)
