@@ -206,6 +206,22 @@ int ssb_proj_gemm_split(const float* A1, int64_t lda1, int64_t K1, const float* 
                         const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
                         const int64_t* lengths, int64_t T, void* stream);
 
+/* K3a v2 without any allocation: ssb_proj_prepack + ssb_proj_gemm in one call, the packed-weight workspace being a
+ * file-scope static device array of the library instead of caller-owned memory.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The call performs no cudaMalloc / cudaFree / allocating library call.
+ * Limit: the packed weights must fit ssb_proj_static_max_bytes() = 884,736 bytes, i.e. N = (W_b ? 2 : 1) * n_each <= 1152
+ * and round_up(K1, 8) + round_up(K2, 8) <= 384 (rounded up to 64); larger shapes are rejected with SSB_ERR_ARG and a
+ * message.  Every GPU that loads the library holds the array until exit.  All calls on a device share it and it keeps
+ * the last call's contents (every byte the GEMM reads is rewritten by the call's own pack kernel first, so nothing needs
+ * clearing); calls that overlap on the GPU race on it -- serialise them on one stream.
+ * W_a / W_b fp32 [n_each, K1 + K2] with row stride ldw (W_b nullable); every other argument as for ssb_proj_gemm. */
+int64_t ssb_proj_static_max_bytes(void);
+int ssb_proj_gemm_static(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                         const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int32_t gru_blocked,
+                         const float* bias, void* C, int64_t ldc, int64_t M,
+                         const int64_t* lengths, int64_t T, int32_t out_half, void* stream);
+
 /* K6: batched mouth-ROI crop + BGR->gray + resize to 96x48, bit-exact with OpenCV 4.13.
  * Replaces crop_roi_gray (live_infer_official.py:171-187; flavor 0: INTER_AREA, box in double arithmetic) and
  * crop_roi (record_landmarks_official.py:102-118; flavor 1: INTER_LINEAR, box in float32 arithmetic).

@@ -557,3 +557,59 @@ extern "C" int ssb_proj_gemm_split(const float* A1, int64_t lda1, int64_t K1, co
   SSB_LAUNCH_CHECK();
   return SSB_OK;
 }
+
+// ------------------------------------------------------------------------------------------------- no-allocation variant
+// ssb_proj_gemm_static: ssb_proj_prepack + ssb_proj_gemm in one call whose packed-weight workspace is NOT caller- or
+// cudaMalloc-owned: it lives in the file-scope device array below (kStaticPackedBytes = 884,736 bytes, the packing of the
+// largest shape the kernel takes: N = 1152, K1p + K2p = 384; every GPU that loads the library holds it until exit).
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  The call
+// itself allocates nothing: no cudaMalloc / cudaFree / allocating library routine.
+//   - The array is shared by every call on the device and keeps the last call's contents.  Nothing has to start at zero:
+//     the pack kernel rewrites every byte the GEMM reads (zero padding included) before the GEMM, in stream order.
+//   - Calls that overlap on the GPU (two streams, two host threads) race on the array; serialise them.
+#include <mutex>
+namespace ssb { namespace gemm2 {
+constexpr size_t kStaticPackedBytes = (size_t)MAX_N * MAX_KP * 2;
+static __device__ __align__(256) uint8_t g_static_packed[kStaticPackedBytes];
+
+// Device address of g_static_packed on the current device.  In host code the array's name is only a handle, so the
+// address is looked up once per device (with that device current) through cudaGetSymbolAddress and cached.
+static int static_packed_ptr(uint8_t** out) {
+  constexpr int kMaxDev = 64;
+  static uint8_t* cache[kMaxDev] = {};
+  static std::mutex mu;
+  int dev = 0;
+  SSB_CUDA(cudaGetDevice(&dev));
+  SSB_REQUIRE(dev >= 0 && dev < kMaxDev, "device index out of range");
+  std::lock_guard<std::mutex> g(mu);
+  if (!cache[dev]) {
+    void* p = nullptr;
+    SSB_CUDA(cudaGetSymbolAddress(&p, g_static_packed));
+    SSB_REQUIRE(p && ((uintptr_t)p & 255) == 0, "static workspace address");
+    cache[dev] = reinterpret_cast<uint8_t*>(p);
+  }
+  *out = cache[dev];
+  return SSB_OK;
+}
+}}  // namespace ssb::gemm2
+
+extern "C" int64_t ssb_proj_static_max_bytes(void) { return (int64_t)ssb::gemm2::kStaticPackedBytes; }
+
+extern "C" int ssb_proj_gemm_static(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                                    const float* W_a, const float* W_b, int64_t ldw, int64_t n_each, int32_t gru_blocked,
+                                    const float* bias, void* C, int64_t ldc, int64_t M,
+                                    const int64_t* lengths, int64_t T, int32_t out_half, void* stream) {
+  using namespace ssb;
+  using namespace ssb::gemm2;
+  SSB_REQUIRE(A1 && W_a && C, "null pointer");
+  SSB_REQUIRE(K1 > 0 && n_each > 0 && K2 >= 0, "bad shape");
+  if (!A2) K2 = 0;
+  const int64_t N = W_b ? 2 * n_each : n_each;
+  SSB_REQUIRE(K1 <= MAX_KP && K2 <= MAX_KP && N <= MAX_N && ssb_proj_packed_bytes(N, K1, K2) <= (int64_t)kStaticPackedBytes,
+              "ssb_proj_gemm_static: packed weights exceed the 884,736-byte static workspace (N <= 1152 and "
+              "round_up(K1, 8) + round_up(K2, 8) <= 384); use ssb_proj_prepack + ssb_proj_gemm with a caller-owned workspace");
+  uint8_t* packed = nullptr;
+  if (int rc = static_packed_ptr(&packed)) return rc;
+  if (int rc = proj_prepack_impl(W_a, W_b, ldw, n_each, K1, K2, gru_blocked, 0, packed, stream)) return rc;
+  return ssb_proj_gemm(A1, lda1, K1, A2, lda2, K2, packed, bias, C, ldc, M, N, lengths, T, out_half, stream);
+}

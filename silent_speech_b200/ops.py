@@ -447,3 +447,20 @@ def augment_clips(X: torch.Tensor, lengths: torch.Tensor, R: Optional[torch.Tens
                                        f32(p_noise), f32(noise_std), f32(p_drop), i32(drop_max), ptr(Xo), ptr(lo), ptr(dec),
                                        stream_ptr()))
     return Xo, lo, dec
+
+
+# ----------------------------------------------------------------------------- no-allocation projection
+def proj_gemm_static(A1: torch.Tensor, W_a: torch.Tensor, W_b: Optional[torch.Tensor], bias, C2d: torch.Tensor,
+                     A2: Optional[torch.Tensor] = None, gru_blocked: bool = False, lengths=None, T: int = 0):
+    """proj_prepack + proj_gemm in one C-ABI call that allocates nothing: the packed weights live in the library's
+    static device array (884,736 bytes; N <= 1152, K <= 384).  Calls share that array: do not overlap them on the GPU.
+    C2d (caller-owned, fp32 or fp16) receives [A1 | A2] @ [W_a ; W_b]^T + bias."""
+    K1 = A1.shape[1]
+    K2 = 0 if A2 is None else A2.shape[1]
+    check(_lib.lib().ssb_proj_gemm_static(ptr(A1), i64(A1.stride(0)), i64(K1), ptr(A2), i64(0 if A2 is None else A2.stride(0)),
+                                          i64(K2), ptr(W_a), ptr(W_b), i64(W_a.stride(0)), i64(W_a.shape[0]),
+                                          i32(1 if gru_blocked else 0), ptr(bias), ptr(C2d), i64(C2d.stride(0)),
+                                          i64(A1.shape[0]), ptr(lengths), i64(T),
+                                          i32(1 if C2d.dtype == torch.float16 else 0), stream_ptr()))
+    _lib._launches += 1          # two kernels: pack, GEMM
+    return C2d
