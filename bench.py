@@ -47,9 +47,12 @@ FWD_FLOP_PER_FRAME = CNN_FLOP_PER_FRAME + GRU_FLOP_PER_FRAME
 FEAT_BYTES_ALGO = 88 * 8 + 720          # 1,424 B/frame: 88 (x, y) pairs read + the 180-float row written
 FEAT_BYTES_ROWS = 478 * 12 + 720        # 6,456 B/frame when whole 5,736-byte landmark rows are streamed
 CPU_CHUNK = 64                          # clips per CPU-arm step (a bounded sample of the 4096-clip batch)
-DTYPE = {"fp32": "f32", "tc3": "f16 hi/lo split operands x3, f32 accumulate (f32-parity grade: logits within 1e-4 of the f32 CPU reference)",
+DTYPE = {"fp32": "f32", "tc3": "f16 hi/lo split operands, f32 accumulate (f32-parity grade: logits within 1e-4 of the f32 CPU reference; projections, "
+                          "recurrences and every training kernel split both operands x3, the inference ROI CNN splits the weights x2 over fp16 activations)",
          "fp16": "f16 operands, f32 accumulate (stated tolerance 1e-3)"}
-K2_NAME = {0: "roi_cnn_fwd_kernel", 1: "roi_cnn_v3_kernel<split=false,4 slots x 128> (K2 v3)", 3: "roi_cnn_tc3_kernel<split=true,2 slots x 256> (K2 v4)"}
+K2_NAME = {0: "roi_cnn_fwd_kernel", 1: "roi_cnn_v3_kernel<split=false,4 slots x 128> (K2 v3)",
+           2: "roi_cnn_tc3_kernel<split weights, fp16 activations> (K2 v4, the tc3 inference form)",
+           3: "roi_cnn_tc3_kernel<split weights and activations,2 slots x 256> (K2 v4, the tc3 training form)"}
 PASSES = {"fp32": 0, "tc3": 3, "fp16": 1}
 
 
@@ -324,15 +327,16 @@ def infer_block(cx, model, precision, dev_batch, host_batch, frames, steps, warm
         e2e["note"] = ("PCIe-bound: h2d_peak_gbs = plain pinned cudaMemcpyAsync rate per GPU with all ranks copying at once; "
                        "frac_of_h2d = this arm's input bytes/s per GPU over that rate")
 
-    passes = PASSES[precision]
+    from silent_speech_b200.functional import cnn_passes
+    passes = cnn_passes(model)                  # what model(X, L, R) launches in this precision (tc3 inference: 2)
     w = model.roi_cnn.tensors()
     cnn_ms = cx.kernel_ms(lambda: ops.roi_cnn_fwd(R, L, w, passes=passes))
     achieved = CNN_FLOP_PER_FRAME * frames / (cnn_ms / 1e3) / 1e12
     peaks = cx.peaks
     roofline = {"kernel": K2_NAME[passes], "bound": "tensor", "achieved": achieved, "peak": peaks["tensor_burst"],
                 "unit": "TFLOP/s", "frac": achieved / peaks["tensor_burst"],
-                "traffic": ncu_traffic(precision, B, args.lengths),
-                "peak_src": f"{peaks['src']} bf16 burst (kernel timed alone)", "ms_per_launch": cnn_ms,
+                "traffic": ncu_traffic({2: "tc3-infer", 3: "tc3"}.get(passes, precision), B, args.lengths),
+                "peak_src": f"{peaks['src']} bf16 burst (kernel timed alone)", "ms_per_launch": cnn_ms, "passes": passes,
                 "note": "K2 (fused ROI CNN), algorithmic 5,309,952 FLOP/frame x %d frames; step-level: %.1f TFLOP/s over %.0f MFLOP/clip" % (
                     frames, FWD_FLOP_PER_FRAME * frames * world * steps / (ms / 1e3) / 1e12, FWD_FLOP_PER_FRAME * T_FRAMES / 1e6)}
     return {"value": value, "unit": "clips/s", "ms_per_step": ms / steps, "e2e": e2e, "gpu_launches": launches,

@@ -51,11 +51,8 @@ constexpr int C3 = 24, C3P = 32, E = 32;
 // layout ssb_roi_cnn_bwd reads -- see roi_cnn.cuh: SAVED_*).
 constexpr int SV_A1 = 0, SV_A2 = 36864, SV_IDX1 = 55296, SV_IDX2 = 57600, SV_MASK3 = 58752, SV_MEAN3 = 59904, SV_BYTES = 60000;
 constexpr int RING_BYTES = NPIX;                       // raw u8 frame staged by one bulk copy
-constexpr int C1_ROUNDS = 3, C1_TPR = 4;               // conv1: 9 tiles in rounds of 4 (last round: 1) -- every round is a
-                                                       // trip through the tensor pipe's queue behind the other slots' batches
-constexpr int PATCH_PX = C1_TPR * 128;                 // pooled pixels per round
-constexpr int PATCH_CHUNK = PATCH_PX * 16;             // 8,192: one k-chunk (two patch rows) of a round
-constexpr int PATCH_BUF = 2 * PATCH_CHUNK;             // 16,384 per round
+constexpr int C1_ROUNDS = 3;                           // conv1: 9 tiles in three rounds -- every round is a trip through the
+                                                       // tensor pipe's queue behind the other slots' batches
 constexpr int P1_ROWS = 13, P1_COLS = 25;              // a1 parity plane: [13][25] pixels x 16 B
 constexpr int P1_PLANE = P1_ROWS * P1_COLS * 16;       // 5,200
 constexpr int A1_BYTES = 4 * P1_PLANE;                 // 20,800
@@ -65,20 +62,30 @@ constexpr int A2_BYTES = 2 * PLANE2;                   // 14,976
 constexpr int W2_CHUNK = 64 * 16;                      // bytes per k-chunk of the conv2 weight operand
 constexpr int W2_BYTES = 16 * W2_CHUNK;                // 16,384 per part
 
-template <bool kSplit>
+// kSplit: weights as fp16 hi + lo.  kALo: activations as hi + lo too (passes = 3; false = passes 2: activations rounded to
+// fp16 once, products x.W_hi + x.W_lo).  kWide: 256-thread slots (two per CTA) with hi|lo stacked along N; narrow slots
+// (128 threads, four per CTA, 128 TMEM columns each) issue the hi and lo products as two MMAs into the same columns.
+template <bool kSplit, bool kALo = kSplit, bool kWide = kSplit>
 struct Lay {
-  static constexpr int P = kSplit ? 2 : 1;
+  static_assert(!kALo || (kSplit && kWide), "activation lo parts exist in the wide split mode only");
+  static constexpr int TPR = kWide ? 4 : 3;            // conv1 tiles per round: 4 + 4 + 1 (wide) or 3 + 3 + 3 (narrow: smaller patch buffer)
+  static constexpr int LAST_TILES = 9 - 2 * TPR;
+  static constexpr int PATCH_PX = TPR * 128;           // pooled pixels per round
+  static constexpr int PATCH_CHUNK = PATCH_PX * 16;    // one k-chunk (two patch rows) of a round
+  static constexpr int PATCH_BUF = 2 * PATCH_CHUNK;    // 16,384 / 12,288 per round
+  static constexpr int P = kSplit ? 2 : 1;             // weight parts
+  static constexpr int PA = kALo ? 2 : 1;              // activation parts
   static constexpr int W3_ROWS = kSplit ? 64 : 32;     // conv3 keeps hi|lo stacked along N (v1 scheme)
   static constexpr int W3_CHUNK = W3_ROWS * 16, W3_BYTES = 18 * W3_CHUNK;
   static constexpr int W1_ROWS = kSplit ? 64 : 32;     // conv1 weights: rows [0,32) hi, [32,64) lo (split mode; the input is exact)
   static constexpr int W1_CHUNK = W1_ROWS * 16, W1_BYTES = 2 * W1_CHUNK;
   // conv1 double buffering (patches and TMEM columns of round r+1 while round r is in the tensor core / epilogue): split
   // mode only -- its slots have 256 TMEM columns and R0 is 30 KB anyway; the four fp16-mode slots have 128 columns each
-  static constexpr int NBUF1 = kSplit ? 2 : 1;
+  static constexpr int NBUF1 = kWide ? 2 : 1;
   // per-slot region R0: conv1 patch buffer(s) during conv1, a2 afterwards
-  static constexpr int R0_A = NBUF1 * PATCH_BUF, R0_B = P * A2_BYTES;
+  static constexpr int R0_A = NBUF1 * PATCH_BUF, R0_B = PA * A2_BYTES;
   static constexpr int R0_BYTES = ((R0_A > R0_B ? R0_A : R0_B) + 127) / 128 * 128;
-  static constexpr int A1_ALLOC = (P * A1_BYTES + 1408 + 127) / 128 * 128;    // + over-read slack of the last conv2 tile (1,360 B)
+  static constexpr int A1_ALLOC = (PA * A1_BYTES + 1408 + 127) / 128 * 128;    // + over-read slack of the last conv2 tile (1,360 B)
   static constexpr int SLOT_BYTES = RING_BYTES + R0_BYTES + A1_ALLOC;
 };
 
@@ -178,17 +185,20 @@ __device__ __forceinline__ float eff_weight(float w) {
   return hi + lh;
 }
 
-template <bool kSplit, int kSlots, int ST, bool kSave>
+template <bool kSplit, bool kALo, int kSlots, int ST, bool kSave>
 __global__ void __launch_bounds__(ST * kSlots, 1)
 roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ lengths, int B, int T,
                    Weights gw, int standardize, float* __restrict__ out, int64_t out_stride,
                    unsigned int* __restrict__ counter, uint8_t* __restrict__ saved) {
-  using L = Lay<kSplit>;
+  constexpr bool kWide = ST == 256, kStack = kSplit && kWide;
+  static_assert(ST == 128 || kStack, "256-thread slots exist in split mode only");
+  static_assert(!kSave || kALo, "saved activations come from the full split mode");
+  using L = Lay<kSplit, kALo, kWide>;
   constexpr int NWG = ST / 128;                        // warps per TMEM lane quarter
+  constexpr int C1_TPR = L::TPR, C1_LAST = L::LAST_TILES, PATCH_CHUNK = L::PATCH_CHUNK, PATCH_BUF = L::PATCH_BUF;
   constexpr int TMEM_PER_SLOT = 512 / kSlots;
-  constexpr bool kPipe2 = TMEM_PER_SLOT < 3 * (kSplit ? 128 : 64);   // conv2's three tiles do not fit: commit tile by tile
-  static_assert(TMEM_PER_SLOT >= 2 * (kSplit ? 128 : 64), "a slot needs two conv2 tiles of TMEM columns");
-  static_assert(kPipe2, "the non-pipelined conv2 path was removed");
+  constexpr int C1W = 32, C2W = kStack ? 128 : 64;     // TMEM columns per conv1 / conv2 tile
+  static_assert(TMEM_PER_SLOT >= 2 * C2W && TMEM_PER_SLOT < 3 * C2W, "conv2 runs two tiles of TMEM columns, committed tile by tile");
   constexpr int E1 = C1_TPR / NWG;                     // conv1 epilogue tiles per thread and round: 4 (ST=128) or 2 (ST=256)
   constexpr int NB1 = L::NBUF1;
   static_assert(C1_TPR % NWG == 0 && ST >= 64, "conv1 round / slot shape");
@@ -244,10 +254,9 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   const uint32_t w1_u = tc::smem_u32(w1op), w2_u = tc::smem_u32(w2op), w3_u = tc::smem_u32(w3op);
   constexpr uint32_t idesc1 = tc::make_idesc_f16(128, 32), idesc2 = tc::make_idesc_f16(128, 64);
   constexpr uint32_t idesc2s = tc::make_idesc_f16(128, 128);            // hi|lo stacked along N
-  constexpr int C1W = 32, C2W = kSplit ? 128 : 64;                      // TMEM columns per conv1 / conv2 tile
   static_assert(NB1 * C1_TPR * C1W <= TMEM_PER_SLOT, "conv1 rounds do not fit the slot's TMEM columns");
-  constexpr uint32_t idesc3_hi = tc::make_idesc_f16(128, kSplit ? 64 : 32), idesc3_lo = tc::make_idesc_f16(128, 32);
-  constexpr int COLS3 = kSplit ? 64 : 32;
+  constexpr uint32_t idesc3_hi = tc::make_idesc_f16(128, kStack ? 64 : 32), idesc3_lo = tc::make_idesc_f16(128, 32);
+  constexpr int COLS3 = kStack ? 64 : 32;
   // base descriptors, built once: the issuing thread only adds compile-time offsets to them
   const uint64_t d_patch = tc::make_desc(r0_u, PATCH_CHUNK, 128), d_w1 = tc::make_desc(w1_u, L::W1_CHUNK, 128);
   const uint64_t d_a1 = tc::make_desc(a1_u, P1_PLANE, 128), d_w2 = tc::make_desc(w2_u, L::P * W2_CHUNK, 128);
@@ -290,7 +299,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   // four raw pixels each, converted u8 -> fp16 exactly (0x6400 | b is 1024 + b; minus 1024).  A group's four pooled pixels
   // need image columns 8g-1 .. 8g+8 of each row: bytes 3 of word 2g-1, words 2g and 2g+1, byte 0 of word 2g+2.
   auto build = [&](int r) {
-    const int ng = (r == C1_ROUNDS - 1) ? 32 : 32 * C1_TPR;     // groups of this round (last round: one tile)
+    const int ng = (r == C1_ROUNDS - 1) ? 32 * C1_LAST : 32 * C1_TPR;     // groups of this round
 #pragma unroll
     for (int it0 = 0; it0 < 2 * 32 * C1_TPR; it0 += ST) {
       const int it = it0 + tid;
@@ -330,7 +339,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     }
   };
   auto conv1_issue = [&](int r) {                      // tid 0: the round's tiles, K = 16, N = 32: x.W (fp16) or x.W_hi + x.W_lo
-    const int nt = (r == C1_ROUNDS - 1) ? 1 : C1_TPR;
+    const int nt = (r == C1_ROUNDS - 1) ? C1_LAST : C1_TPR;
     for (int tl = 0; tl < nt; ++tl) {
       const uint64_t da = tc::desc_add(d_patch, (r % NB1) * PATCH_BUF + tl * 2048);
       const uint32_t dcol = tmem + (r % NB1) * (C1_TPR * C1W) + tl * C1W;
@@ -407,7 +416,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       if (NB1 == 2 && (r & 1)) { tc::mbar_wait_bounded(&mz.bar[1], ph1); ph1 ^= 1; } else { tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1; }
       tc::fence_after_sync();
       if (NB1 == 1 && r + 1 < C1_ROUNDS) build(r + 1);
-      const int nt = (r == C1_ROUNDS - 1) ? 1 : C1_TPR;
+      const int nt = (r == C1_ROUNDS - 1) ? C1_LAST : C1_TPR;
 #pragma unroll
       for (int k = 0; k < E1; ++k) {
         const int tl = k * NWG + wg;
@@ -467,14 +476,14 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
             reinterpret_cast<float4*>(rec + SV_A1)[2 * Pp + 1] = make_float4(hi[4], hi[5], hi[6], hi[7]);
             reinterpret_cast<uint16_t*>(rec + SV_IDX1)[Pp] = (uint16_t)am;
           }
-          if (kSplit) {
+          if (kALo) {
 #pragma unroll
-            for (int co = 0; co < 8; ++co) tc::split_f16(hi[co], hi[co], lo[co]);           // single pass: pack8 rounds once
+            for (int co = 0; co < 8; ++co) tc::split_f16(hi[co], hi[co], lo[co]);           // otherwise pack8 rounds once
           }
           // pooled pixel -> a1 padded parity planes: row parity from the table, column parity (q+1)&1, cell 2g + (q+1)/2
           const uint32_t off = (((gt >> 15) & 1) * 2 + ((q + 1) & 1)) * P1_PLANE + (gt & 0x7fffu) + ((q + 1) >> 1) * 16;
           *reinterpret_cast<uint4*>(a1 + off) = pack8(hi);
-          if (kSplit) *reinterpret_cast<uint4*>(a1 + A1_BYTES + off) = pack8(lo);
+          if (kALo) *reinterpret_cast<uint4*>(a1 + A1_BYTES + off) = pack8(lo);
         }
       }
       tc::fence_before_sync();
@@ -507,7 +516,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     // ================= conv2 + ReLU + pool: 3 tiles of 128 virtual pooled pixels (v = py*25 + px)
     // region R0 becomes a2: zero its border cells (conv3's padding; the interior is overwritten by the epilogue below, the
     // rows past 13 only feed output rows that are never read); the patches are dead
-    for (int i = tid; i < L::P * 2 * 76; i += ST) {
+    for (int i = tid; i < L::PA * 2 * 76; i += ST) {
       const int pl = i / 76, c = i % 76;               // plane (part, channel half), border cell
       const int cell = c < 26 ? c : c < 52 ? 13 * PITCH2 + (c - 26) : (1 + ((c - 52) >> 1)) * PITCH2 + ((c & 1) ? PITCH2 - 1 : 0);
       reinterpret_cast<uint4*>(r0 + pl * PLANE2)[cell] = make_uint4(0, 0, 0, 0);
@@ -525,18 +534,18 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           const uint32_t b_off = (r * 4 + 2 * h) * (L::P * W2_CHUNK);
           const uint64_t ah = tc::desc_add(d_a1, a_off);
           const uint64_t bh = tc::desc_add(d_w2, b_off);
-          if (kSplit) {
-            // columns [0,64) = A_hi.B_hi + A_lo.B_hi, columns [64,128) = A_hi.B_lo
-            const uint64_t al = tc::desc_add(d_a1, A1_BYTES + a_off);
+          if (kStack) {
+            // columns [0,64) = A_hi.B_hi (+ A_lo.B_hi), columns [64,128) = A_hi.B_lo
             tc::mma_f16(tmem + dcol, ah, bh, idesc2s, (r | h) != 0);
-            tc::mma_f16(tmem + dcol, al, bh, idesc2, true);
+            if (kALo) tc::mma_f16(tmem + dcol, tc::desc_add(d_a1, A1_BYTES + a_off), bh, idesc2, true);
           } else {
             tc::mma_f16(tmem + dcol, ah, bh, idesc2, (r | h) != 0);
+            if (kSplit) tc::mma_f16(tmem + dcol, ah, tc::desc_add(bh, W2_CHUNK), idesc2, true);      // + A.B_lo, same columns
           }
         }
     };
     auto conv2_epilogue = [&](int tl, uint32_t dcol) {
-      if (kSplit) {
+      if (kStack) {
         // 256-thread slots: warpgroup wg owns output channels 8wg..8wg+7 (= channel plane wg of a2); per sub-position
         // it adds the A_hi.B_lo half (columns 64..) to the main half, then max / bias / ReLU / hi-lo split
         float m4[8];
@@ -557,12 +566,14 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         }
         if (a2off[tl] >= 0) {
           float hi[8], lo[8];
-#pragma unroll
           float bb[8];
           *reinterpret_cast<float4*>(bb) = *reinterpret_cast<const float4*>(sh.b2 + wg * 8);
           *reinterpret_cast<float4*>(bb + 4) = *reinterpret_cast<const float4*>(sh.b2 + wg * 8 + 4);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) tc::split_f16(fmaxf(m4[i] + bb[i], 0.f), hi[i], lo[i]);
+          for (int i = 0; i < 8; ++i) {
+            hi[i] = fmaxf(m4[i] + bb[i], 0.f);
+            if (kALo) tc::split_f16(hi[i], hi[i], lo[i]);
+          }
           const uint32_t off = (uint32_t)a2off[tl] + wg * PLANE2;
           if (kSave) {
             const int vp = tl * 128 + row, pix = (vp / P1_COLS) * W2 + vp % P1_COLS;
@@ -573,7 +584,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
             reinterpret_cast<uint16_t*>(rec + SV_IDX2)[pix * 2 + wg] = (uint16_t)am;
           }
           *reinterpret_cast<uint4*>(r0 + off) = pack8(hi);
-          *reinterpret_cast<uint4*>(r0 + A2_BYTES + off) = pack8(lo);
+          if (kALo) *reinterpret_cast<uint4*>(r0 + A2_BYTES + off) = pack8(lo);
         }
       } else {
         float v[32], w[32];
@@ -639,7 +650,8 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
           const uint32_t a_off = (dy * PITCH2 + tx * 8 + dx) * 16;
           const uint64_t db = tc::desc_add(d_w3, 2 * tap * L::W3_CHUNK);
           tc::mma_f16(tmem + tx * COLS3, tc::desc_add(d_a2, a_off), db, idesc3_hi, tap > 0);
-          if (kSplit) tc::mma_f16(tmem + tx * COLS3, tc::desc_add(d_a2, A2_BYTES + a_off), db, idesc3_lo, true);
+          if (kALo) tc::mma_f16(tmem + tx * COLS3, tc::desc_add(d_a2, A2_BYTES + a_off), db, idesc3_lo, true);
+          if (kSplit && !kStack) tc::mma_f16(tmem + tx * COLS3, tc::desc_add(d_a2, a_off), tc::desc_add(db, 32 * 16), idesc3_lo, true);
         }
         tc::mma_commit(&mz.bar[tx]);
       }
@@ -657,7 +669,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       if (q < 3 && tx % NWG == wg) {
         float v[32];
         tc::tmem_ld32(tq + tx * COLS3, v);
-        if (kSplit) {
+        if (kStack) {
           float w[32];
           tc::tmem_ld32(tq + tx * COLS3 + 32, w);
           tc::tmem_ld_wait();
@@ -715,10 +727,10 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   if (threadIdx.x < 32) tc::tmem_dealloc<512>(sh.tmem_base);
 }
 
-template <bool kSplit, int kSlots>
+template <bool kSplit, bool kALo, int kSlots>
 constexpr size_t smem_total() {
-  return kSlots * Lay<kSplit>::SLOT_BYTES + Lay<kSplit>::W1_BYTES + Lay<kSplit>::P * W2_BYTES + Lay<kSplit>::W3_BYTES +
-         kSlots * sizeof(SlotMisc) + sizeof(Shared);
+  using L = Lay<kSplit, kALo, kSlots == 2>;
+  return kSlots * L::SLOT_BYTES + L::W1_BYTES + L::P * W2_BYTES + L::W3_BYTES + kSlots * sizeof(SlotMisc) + sizeof(Shared);
 }
 
 }  // namespace cnn3
@@ -736,6 +748,28 @@ static bool ssb_k2_single_pass_v4_() {
   static const bool v4 = [] { const char* e = getenv("SSB_K2_FP16_V4"); return e && e[0] == '1'; }();
   return v4;
 }
+// passes = 2 runs four 128-thread slots; SSB_K2_TC2_SLOTS=2 picks the two-slot x 256-thread instance (A/B switch, read once)
+static int ssb_k2_tc2_slots_() {
+  static const int n = [] { const char* e = getenv("SSB_K2_TC2_SLOTS"); return e && e[0] == '4' ? 4 : e && e[0] == '2' ? 2 : 0; }();
+  return n;
+}
+namespace ssb { namespace cnn3 {
+template <bool kSplit, bool kALo, int kSlots, int ST, bool kSave>
+static int launch_k2(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T, const Weights& gw, int32_t standardize,
+                     float* out, int64_t out_stride, unsigned int* counter, void* saved, cudaStream_t st) {
+  constexpr size_t smem = smem_total<kSplit, kALo, kSlots>();
+  static_assert(smem <= 232448, "shared-memory budget of one CTA");
+  static_assert((kSlots == 2) == (ST == 256), "two wide or four narrow slots");
+  const int64_t want = (B * T + kSlots - 1) / kSlots;
+  const int grid = (int)(want < kSMs ? want : kSMs);
+  auto kern = roi_cnn_tc3_kernel<kSplit, kALo, kSlots, ST, kSave>;
+  SSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride, counter,
+                                        reinterpret_cast<uint8_t*>(saved));
+  SSB_LAUNCH_CHECK();
+  return SSB_OK;
+}
+}}  // namespace ssb::cnn3
 extern "C" int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
                                    int32_t roi_h, int32_t roi_w, const float* const* weights, int32_t standardize,
                                    float* out, int64_t out_stride, int32_t passes, void* saved, void* stream) {
@@ -745,41 +779,23 @@ extern "C" int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int
   SSB_REQUIRE(!saved || (passes == 3 && ((uintptr_t)saved & 15) == 0), "saved activations: split mode only, 16-byte aligned");
   SSB_REQUIRE(roi_h == H0 && roi_w == W0, "ROI must be 48x96 (train_model_official.py:38)");
   SSB_REQUIRE(out_stride >= E, "out_stride < 32");
-  SSB_REQUIRE(passes == 1 || passes == 3, "passes must be 1 or 3");
+  SSB_REQUIRE(passes >= 1 && passes <= 3, "passes must be 1, 2 or 3");
   for (int i = 0; i < 8; ++i) SSB_REQUIRE(weights[i], "null weight pointer");
   SSB_REQUIRE(((uintptr_t)R & 15) == 0, "R must be 16-byte aligned (frames are staged by 4,608-byte bulk copies)");
   if (B * T == 0) return SSB_OK;
   Weights gw{weights[0], weights[1], weights[2], weights[3], weights[4], weights[5], weights[6], weights[7]};
-  const int64_t frames = B * T;
   cudaStream_t st = (cudaStream_t)stream;
   unsigned int* counter = nullptr;
   if (int rc = ssb_scratch_counter_(st, &counter)) return rc;
-  if (passes == 3) {
-    constexpr int kSlots = 2, ST = 256;
-    constexpr size_t smem = smem_total<true, kSlots>();
-    static_assert(smem <= 232448, "split-mode smem budget");
-    const int64_t want = (frames + kSlots - 1) / kSlots;
-    const int grid = (int)(want < kSMs ? want : kSMs);
-    if (saved) {
-      SSB_CUDA(cudaFuncSetAttribute(roi_cnn_tc3_kernel<true, kSlots, ST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      roi_cnn_tc3_kernel<true, kSlots, ST, true><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride,
-                                                                                counter, reinterpret_cast<uint8_t*>(saved));
-    } else {
-      SSB_CUDA(cudaFuncSetAttribute(roi_cnn_tc3_kernel<true, kSlots, ST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      roi_cnn_tc3_kernel<true, kSlots, ST, false><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride,
-                                                                                 counter, nullptr);
-    }
-  } else if (!ssb_k2_single_pass_v4_()) {
-    return ssb_roi_cnn_fwd_v3_(R, lengths, B, T, weights, standardize, out, out_stride, stream);   // roi_cnn_v3.cu
-  } else {
-    constexpr int kSlots = 4, ST = 128;
-    constexpr size_t smem = smem_total<false, kSlots>();
-    static_assert(smem <= 232448, "fp16-mode smem budget");
-    const int64_t want = (frames + kSlots - 1) / kSlots;
-    const int grid = (int)(want < kSMs ? want : kSMs);
-    SSB_CUDA(cudaFuncSetAttribute(roi_cnn_tc3_kernel<false, kSlots, ST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    roi_cnn_tc3_kernel<false, kSlots, ST, false><<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride, counter, nullptr);
+  if (passes == 3) {                                   // both operands split: fp32-parity grade, the training mode
+    return saved ? launch_k2<true, true, 2, 256, true>(R, lengths, B, T, gw, standardize, out, out_stride, counter, saved, st)
+                 : launch_k2<true, true, 2, 256, false>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
   }
-  SSB_LAUNCH_CHECK();
-  return SSB_OK;
+  if (passes == 2) {                                   // split weights, activations rounded to fp16 once
+    // four narrow slots: 10.5 ms per 4096 clips against 12.1 ms for two wide ones (B200, r2)
+    if (ssb_k2_tc2_slots_() == 2) return launch_k2<true, false, 2, 256, false>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
+    return launch_k2<true, false, 4, 128, false>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
+  }
+  if (!ssb_k2_single_pass_v4_()) return ssb_roi_cnn_fwd_v3_(R, lengths, B, T, weights, standardize, out, out_stride, stream);   // roi_cnn_v3.cu
+  return launch_k2<false, false, 4, 128, false>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
 }

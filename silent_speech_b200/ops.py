@@ -74,6 +74,7 @@ def roi_cnn_fwd(R: torch.Tensor, lengths: Optional[torch.Tensor], weights: Seque
                 standardize: bool = True, out: Optional[torch.Tensor] = None, out_col: int = 0,
                 passes: int = 0, saved: Optional[torch.Tensor] = None) -> torch.Tensor:
     """R u8 [B,T,48,96] -> embedding f32 [B,T,32] (or written into out[..., out_col:out_col+32]).
+    passes: 0 fp32 CUDA cores; 1 single fp16 pass; 2 split weights x fp16 activations; 3 both operands split (hi + lo).
     saved (passes = 3): uint8 [B*T, roi_cnn_saved_bytes()] receiving the activations roi_cnn_bwd needs."""
     _need(R, torch.uint8, "R")
     B, T, Hh, Ww = R.shape

@@ -100,7 +100,7 @@ class StreamScheduler:
             emb = None
             if self.de:
                 Rs = R if all_found else R[torch.from_numpy(sel).to(R.device)]
-                passes = F_ssb._passes(self.model)[0]
+                passes = F_ssb.cnn_passes(self.model)
                 emb = ops.roi_cnn_fwd(Rs.view(a.size, 1, *Rs.shape[1:]).contiguous(), None, self.model.roi_cnn.tensors(),
                                       standardize=self.model.standardize_roi, passes=passes).view(a.size, self.de)
             ops.ring_push(self.ring, self._i32(a), self._i32(pos), Xs.contiguous().float(), emb)
