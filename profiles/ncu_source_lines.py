@@ -1,5 +1,5 @@
 """Per-source-line summary of an .ncu-rep captured with --import-source on (kernels built with -lineinfo):
-    python profiles/ncu_source_lines.py rep [top_n]
+    python profiles/ncu_source_lines.py rep [top_n] [all_lines.csv]
 Prints, per CUDA source line, stall samples, executed instructions, shared-memory wavefronts (LSU) and the excessive
 (bank-conflict) ones, sorted by samples."""
 import csv, subprocess, sys
@@ -23,7 +23,14 @@ for r in rows:
                   num("L1 Wavefronts Shared"), num("L1 Wavefronts Shared Excessive")))
 tot = [sum(l[i] for l in lines) for i in (3, 4, 5, 6)]
 print(f"totals: samples {tot[0]:.0f}  inst {tot[1]:.0f}  smem wavefronts {tot[2]:.0f}  excessive {tot[3]:.0f}")
-for key, name in ((3, "stall samples"), (5, "shared wavefronts"), (6, "excessive (bank-conflict) wavefronts")):
+if len(sys.argv) > 3:                      # every line in file order (file, line, samples, instructions, wavefronts, source)
+    with open(sys.argv[3], "w", newline="") as fh:
+        w = csv.writer(fh)
+        w.writerow(["file", "line", "samples", "inst", "smem_wavefronts", "source"])
+        for l in lines:
+            if l[3] or l[4]:
+                w.writerow([l[0], l[1], int(l[3]), int(l[4]), int(l[5]), l[2]])
+for key, name in ((3, "stall samples"), (4, "instructions executed"), (5, "shared wavefronts"), (6, "excessive (bank-conflict) wavefronts")):
     print(f"\n== top lines by {name}")
     for l in sorted(lines, key=lambda l: -l[key])[:top]:
         if l[key] <= 0: break

@@ -67,7 +67,8 @@ gemm_tc_kernel(const float* __restrict__ A1, int64_t lda1, int K1, const float* 
                const int64_t* __restrict__ lengths, int T) {
   extern __shared__ __align__(1024) uint8_t smem[];
   Tail& tail = *reinterpret_cast<Tail*>(smem + STAGES * STAGE_BYTES);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // known warp-uniform (MMA descriptors stay in uniform registers)
   const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
 
   if (lengths) {          // tiles made only of padded frames are never read downstream
@@ -83,7 +84,7 @@ gemm_tc_kernel(const float* __restrict__ A1, int64_t lda1, int K1, const float* 
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
-  const uint32_t tmem = tail.tmem_base;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, tail.tmem_base, 0);
   constexpr uint32_t idesc = tc::make_idesc_f16(BM, BN);
 
   const int chunks1 = (K1 + BK - 1) / BK, chunks2 = A2 ? (K2 + BK - 1) / BK : 0;
@@ -104,7 +105,7 @@ gemm_tc_kernel(const float* __restrict__ A1, int64_t lda1, int K1, const float* 
     stage_operand<BN, kSplit>(w_src, ldw, N - n0, k_valid, b_hi, b_lo, tid);
     tc::fence_async_smem();
     __syncthreads();
-    if (tid == 0) {
+    if (warp == 0 && tc::elect_one()) {
       tc::fence_after_sync();
       const int ksteps = (k_valid + 15) / 16;
       for (int j = 0; j < ksteps; ++j) {

@@ -96,7 +96,8 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
   float* bias_s = tile_s + EPI_WARPS * 32 * TILE_LD;              // nnt * 128 floats
   uint8_t* live_s = reinterpret_cast<uint8_t*>(bias_s + nnt * BN);         // 128 bytes
   Ctl& ctl = *reinterpret_cast<Ctl*>(live_s + BM);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // known warp-uniform: role branches and MMA descriptors go uniform
 
   for (int i = tid; i < nnt * BN; i += THREADS) bias_s[i] = (a.bias && i < a.N) ? a.bias[i] : 0.f;
   if (warp == 0) tc::tmem_alloc<TMEM_COLS>(&ctl.tmem_base);
@@ -108,7 +109,7 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
-  const uint32_t tmem = ctl.tmem_base;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, ctl.tmem_base, 0);
   const uint32_t a_u = tc::smem_u32(a_s), w_u = tc::smem_u32(w_s);
   constexpr uint32_t idesc = tc::make_idesc_f16(BM, BN);
   uint32_t w_it = 0, acc_it = 0;                             // running weight-block / accumulator counters (ring phases)
@@ -178,7 +179,7 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
       w_it = __shfl_sync(0xffffffffu, w_it, 0);
     } else if (warp == EPI_WARPS + 1) {
       // =============================== MMA issuer ===============================
-      if (lane == 0) {
+      if (tc::elect_one()) {
         for (int nt = 0; nt < nnt; ++nt, ++acc_it) {
           const uint32_t buf = acc_it & 1;
           tc::mbar_wait_bounded(&ctl.accempty[buf], ((acc_it >> 1) & 1) ^ 1);
@@ -296,7 +297,8 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
   float* bias_s = reinterpret_cast<float*>(w_s + SSTAGES * 2 * W_BLOCK);   // nnt * 128 floats
   uint8_t* live_s = reinterpret_cast<uint8_t*>(bias_s + nnt * BN);         // 64 bytes
   Ctl& ctl = *reinterpret_cast<Ctl*>(live_s + SBM);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // known warp-uniform: role branches and MMA descriptors go uniform
 
   for (int i = tid; i < nnt * BN; i += THREADS) bias_s[i] = (a.bias && i < a.N) ? a.bias[i] : 0.f;
   if (warp == 0) tc::tmem_alloc<STMEM_COLS>(&ctl.tmem_base);
@@ -308,7 +310,7 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
-  const uint32_t tmem = ctl.tmem_base;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, ctl.tmem_base, 0);
   const uint32_t ah_u = tc::smem_u32(act_hi), al_u = tc::smem_u32(act_lo), w_u = tc::smem_u32(w_s);
   constexpr uint32_t idesc = tc::make_idesc_f16(BN, SBM);     // M = 128 weight rows, N = 64 activation rows
   uint32_t w_it = 0, acc_it = 0;
@@ -383,7 +385,7 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
       w_it = __shfl_sync(0xffffffffu, w_it, 0);
     } else if (warp == EPI_WARPS + 1) {
       // =============================== MMA issuer ===============================
-      if (lane == 0) {
+      if (tc::elect_one()) {
         for (int nt = 0; nt < nnt; ++nt, ++acc_it) {
           const uint32_t buf = acc_it & 1;
           tc::mbar_wait_bounded(&ctl.accempty[buf], ((acc_it >> 1) & 1) ^ 1);

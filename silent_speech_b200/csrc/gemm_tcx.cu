@@ -114,7 +114,8 @@ gemm_tcx_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
                 const int64_t* __restrict__ lengths, int T, const float* __restrict__ a_amax) {
   extern __shared__ __align__(1024) uint8_t smem[];
   Tail& tail = *reinterpret_cast<Tail*>(smem + STAGES * STAGE_BYTES);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // known warp-uniform (MMA descriptors stay in uniform registers)
   const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
   const int kbeg = blockIdx.z * k_per_split, kend = min(K, kbeg + k_per_split);
 
@@ -131,7 +132,7 @@ gemm_tcx_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
-  const uint32_t tmem = tail.tmem_base;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, tail.tmem_base, 0);
   constexpr uint32_t idesc = tc::make_idesc_f16(BM, BN);
   float a_scale = 1.f, c_scale = 1.f;                   // power of two that lifts max|A| into [2048, 4096), and its inverse
   if (a_amax) {
@@ -163,7 +164,7 @@ gemm_tcx_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
     lb.store(b_hi, b_lo, 1.f, tid);
     tc::fence_async_smem();
     __syncthreads();
-    if (tid == 0) {
+    if (warp == 0 && tc::elect_one()) {
       tc::fence_after_sync();
       const int ksteps = (k_valid + 15) / 16;
       for (int j = 0; j < ksteps; ++j) {

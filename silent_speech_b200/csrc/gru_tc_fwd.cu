@@ -146,7 +146,8 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   float* gstage = reinterpret_cast<float*>(smem + (kSplit ? 2 : 1) * (A_BYTES + B_BYTES));     // !kSplit only
   Ctl& ctl = *reinterpret_cast<Ctl*>(smem + (kSplit ? 2 : 1) * (A_BYTES + B_BYTES) + (kSplit ? 0 : GI_STAGE_BYTES));
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // known warp-uniform: role branch and MMA descriptors go uniform
   const uint32_t rank = tc::cluster_ctarank();
   const int dir = blockIdx.y;
   const int b0 = (blockIdx.x / CL) * rows;       // rows <= BM clips per cluster: the tile's first `rows` rows are real
@@ -202,7 +203,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
   __syncthreads();
   tc::fence_after_sync();
   const int maxlen = ctl.maxlen;
-  const uint32_t tmem = ctl.tmem_base;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, ctl.tmem_base, 0);
   tc::cluster_sync_all();                        // every CTA's barriers exist before any remote operation
 
   constexpr uint32_t idesc = tc::make_idesc_f16(BM, NG);
@@ -228,7 +229,7 @@ gru_tc_fwd_kernel(const float* __restrict__ gi, int64_t gi_ld,
       }
       tc::mbar_wait_bounded(&ctl.full, (s - 1) & 1);            // all four h slices of step s-1 are in place
       tc::fence_after_sync();
-      if (lane == 0) {
+      if (tc::elect_one()) {
 #pragma unroll 1
         for (int j = 0; j < H / 16; ++j) {
           const uint64_t dah = tc::make_desc(tc::smem_u32(a_hi) + j * 2 * A_LBO, A_LBO, 128);

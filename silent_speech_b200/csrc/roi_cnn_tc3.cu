@@ -208,7 +208,10 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   uint8_t* w3op = w2op + L::P * W2_BYTES;
   SlotMisc* smz = reinterpret_cast<SlotMisc*>(w3op + L::W3_BYTES);
   Shared& sh = *reinterpret_cast<Shared*>(smz + kSlots);
-  const int slot = threadIdx.x / ST, tid = threadIdx.x % ST, warp = tid >> 5, lane = tid & 31;
+  // slot and warp index through a shuffle: the compiler then knows they are warp-uniform (uniform registers and branches
+  // for everything derived from them, in particular the MMA descriptors)
+  const int slot = __shfl_sync(0xffffffffu, (int)(threadIdx.x / ST), 0), tid = threadIdx.x % ST, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   uint8_t* ring = smem + slot * L::SLOT_BYTES;         // raw u8 frame (bulk-copy destination)
   uint8_t* r0 = ring + RING_BYTES;                     // conv1 patches, later a2
   uint8_t* a1 = r0 + L::R0_BYTES;
@@ -249,7 +252,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
-  const uint32_t tmem = sh.tmem_base + slot * TMEM_PER_SLOT;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, sh.tmem_base, 0) + slot * TMEM_PER_SLOT;
   const uint32_t r0_u = tc::smem_u32(r0), a1_u = tc::smem_u32(a1), ring_u = tc::smem_u32(ring);
   const uint32_t w1_u = tc::smem_u32(w1op), w2_u = tc::smem_u32(w2op), w3_u = tc::smem_u32(w3op);
   constexpr uint32_t idesc1 = tc::make_idesc_f16(128, 32), idesc2 = tc::make_idesc_f16(128, 64);
@@ -380,7 +383,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     build(0);
     tc::fence_async_smem();
     slot_sync<ST>(slot);
-    if (tid == 0) { tc::fence_after_sync(); conv1_issue(0); }
+    if (warp == 0 && tc::elect_one()) { tc::fence_after_sync(); conv1_issue(0); }
     float mean_u = 0.f, inv_s = 1.0f / 255.0f;
     if (standardize) {
       uint32_t t1 = 0, t2 = 0;
@@ -489,7 +492,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       tc::fence_before_sync();
       tc::fence_async_smem();
       slot_sync<ST>(slot);                              // patches of round r+1 complete; round r's TMEM columns and patch buffer free
-      if (tid == 0 && r + 1 < C1_ROUNDS) { tc::fence_after_sync(); conv1_issue(r + 1); }
+      if (warp == 0 && r + 1 < C1_ROUNDS && tc::elect_one()) { tc::fence_after_sync(); conv1_issue(r + 1); }
       if (warp == 1) {
         if (r == 0) {
           // hand-out, split in two so that neither global round trip is waited for: the atomic was issued at the top of
@@ -609,7 +612,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     {
       // two tiles of TMEM columns: tiles 0 and 1 in flight, tile 2 re-uses tile 0's columns once its epilogue is
       // done; every tile has its own commit, so an epilogue overlaps the next tile's MMAs
-      if (tid == 0) {
+      if (warp == 0 && tc::elect_one()) {
         tc::fence_after_sync();
         conv2_issue(0, 0);
         tc::mma_commit(&mz.bar[0]);
@@ -621,7 +624,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       conv2_epilogue(0, 0);
       tc::fence_before_sync();
       slot_sync<ST>(slot);
-      if (tid == 0) {
+      if (warp == 0 && tc::elect_one()) {
         tc::fence_after_sync();
         conv2_issue(2, 0);
         tc::mma_commit(&mz.bar[0]);
@@ -640,7 +643,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     // ================= conv3 + ReLU + mean: 3 tiles of 16 rows x 8 columns (12 rows real), 9 taps
     // every tile has its own commit (bar[0..2]): the channel sums of tile i are taken while tiles i+1.. are still in the
     // tensor core
-    if (tid == 0) {
+    if (warp == 0 && tc::elect_one()) {
       tc::fence_after_sync();
 #pragma unroll
       for (int tx = 0; tx < 3; ++tx) {

@@ -161,7 +161,9 @@ roi_cnn_v3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
   uint8_t* w3op = w2op + L::P * W2_BYTES;
   SlotMisc* smz = reinterpret_cast<SlotMisc*>(w3op + L::W3_BYTES);
   Shared& sh = *reinterpret_cast<Shared*>(smz + kSlots);
-  const int slot = threadIdx.x / ST, tid = threadIdx.x % ST, warp = tid >> 5, lane = tid & 31;
+  // slot and warp index through a shuffle: known warp-uniform to the compiler (MMA descriptors stay in uniform registers)
+  const int slot = __shfl_sync(0xffffffffu, (int)(threadIdx.x / ST), 0), tid = threadIdx.x % ST, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   uint8_t* r0 = smem + slot * L::SLOT_BYTES;           // pix / patches, later a2
   uint8_t* a1 = r0 + L::R0_BYTES;
   SlotMisc& mz = smz[slot];
@@ -180,7 +182,7 @@ roi_cnn_v3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
-  const uint32_t tmem = sh.tmem_base + slot * TMEM_PER_SLOT;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, sh.tmem_base, 0) + slot * TMEM_PER_SLOT;
   const uint32_t r0_u = tc::smem_u32(r0), a1_u = tc::smem_u32(a1);
   const uint32_t w1_u = tc::smem_u32(w1op), w2_u = tc::smem_u32(w2op), w3_u = tc::smem_u32(w3op);
   constexpr uint32_t idesc1 = tc::make_idesc_f16(128, 32), idesc2 = tc::make_idesc_f16(128, 64);
@@ -385,7 +387,7 @@ roi_cnn_v3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
       }
       tc::fence_async_smem();
       slot_sync<ST>(slot);
-      if (tid == 0) {
+      if (warp == 0 && tc::elect_one()) {
         tc::fence_after_sync();
         for (int tl = 0; tl < ntiles; ++tl) {
           const uint64_t ah = tc::make_desc(r0_u + L::OFF_PATCH + tl * 2048, L::PATCH_CHUNK, 128);
@@ -552,7 +554,7 @@ roi_cnn_v3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
     {
       // two tiles of TMEM columns: tiles 0 and 1 in flight, tile 2 re-uses tile 0's columns once its epilogue is
       // done; every tile has its own commit, so an epilogue overlaps the next tile's MMAs
-      if (tid == 0) {
+      if (warp == 0 && tc::elect_one()) {
         tc::fence_after_sync();
         conv2_issue(0, 0);
         tc::mma_commit(&mz.bar[0]);
@@ -564,7 +566,7 @@ roi_cnn_v3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
       conv2_epilogue(0, 0);
       tc::fence_before_sync();
       slot_sync<ST>(slot);
-      if (tid == 0) {
+      if (warp == 0 && tc::elect_one()) {
         tc::fence_after_sync();
         conv2_issue(2, 0);
         tc::mma_commit(&mz.bar[0]);
@@ -583,7 +585,7 @@ roi_cnn_v3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ len
     // ================= conv3 + ReLU + mean: 3 tiles of 16 rows x 8 columns (12 rows real), 9 taps
     // every tile has its own commit (bar[0..2]): the channel sums of tile i are taken while tiles i+1.. are still in the
     // tensor core
-    if (tid == 0) {
+    if (warp == 0 && tc::elect_one()) {
       tc::fence_after_sync();
 #pragma unroll
       for (int tx = 0; tx < 3; ++tx) {
