@@ -185,20 +185,26 @@ __device__ __forceinline__ float eff_weight(float w) {
   return hi + lh;
 }
 
-template <bool kSplit, bool kALo, int kSlots, int ST, bool kSave>
+template <bool kSplit, bool kALo, int kSlots, int ST, bool kSave, bool kStack = kSplit && ST == 256>
 __global__ void __launch_bounds__(ST * kSlots, 1)
 roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ lengths, int B, int T,
                    Weights gw, int standardize, float* __restrict__ out, int64_t out_stride,
                    unsigned int* __restrict__ counter, uint8_t* __restrict__ saved) {
-  constexpr bool kWide = ST == 256, kStack = kSplit && kWide;
-  static_assert(ST == 128 || kStack, "256-thread slots exist in split mode only");
+  // kStack: the hi and lo weight parts sit side by side along N of ONE MMA (conv2: N = 128, conv3: N = 64) -- an MMA with
+  // M = 128, K = 16 costs about 32 + N/4 cycles of the tensor pipe (the 4 KB A operand is fetched per instruction:
+  // profiles/microbench/r2_tc_micro3.txt), so one N = 128 MMA (64) is cheaper than two N = 64 MMAs (96).  A narrow slot's
+  // 128 TMEM columns then hold one conv2 tile (tiles run one after the other) or two conv3 tiles.
+  constexpr bool kWide = ST == 256;
+  static_assert(!kStack || kSplit, "only split weights are stacked");
+  static_assert(ST == 128 || kStack, "256-thread slots exist in the stacked split mode only");
   static_assert(!kSave || kALo, "saved activations come from the full split mode");
   using L = Lay<kSplit, kALo, kWide>;
   constexpr int NWG = ST / 128;                        // warps per TMEM lane quarter
   constexpr int C1_TPR = L::TPR, C1_LAST = L::LAST_TILES, PATCH_CHUNK = L::PATCH_CHUNK, PATCH_BUF = L::PATCH_BUF;
   constexpr int TMEM_PER_SLOT = 512 / kSlots;
   constexpr int C1W = 32, C2W = kStack ? 128 : 64;     // TMEM columns per conv1 / conv2 tile
-  static_assert(TMEM_PER_SLOT >= 2 * C2W && TMEM_PER_SLOT < 3 * C2W, "conv2 runs two tiles of TMEM columns, committed tile by tile");
+  constexpr int C2_FLY = TMEM_PER_SLOT / C2W;          // conv2 tiles in flight: 2 (tile 2 re-uses tile 0's columns) or 1
+  static_assert(C2_FLY == 1 || C2_FLY == 2, "conv2 runs one or two tiles of TMEM columns, committed tile by tile");
   constexpr int E1 = C1_TPR / NWG;                     // conv1 epilogue tiles per thread and round: 4 (ST=128) or 2 (ST=256)
   constexpr int NB1 = L::NBUF1;
   static_assert(C1_TPR % NWG == 0 && ST >= 64, "conv1 round / slot shape");
@@ -260,6 +266,8 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
   static_assert(NB1 * C1_TPR * C1W <= TMEM_PER_SLOT, "conv1 rounds do not fit the slot's TMEM columns");
   constexpr uint32_t idesc3_hi = tc::make_idesc_f16(128, kStack ? 64 : 32), idesc3_lo = tc::make_idesc_f16(128, 32);
   constexpr int COLS3 = kStack ? 64 : 32;
+  constexpr int C3_FLY = TMEM_PER_SLOT / COLS3 >= 3 ? 3 : 2;           // conv3 tiles in flight
+  static_assert(TMEM_PER_SLOT >= 2 * COLS3, "conv3 needs two tiles of TMEM columns");
   // base descriptors, built once: the issuing thread only adds compile-time offsets to them
   const uint64_t d_patch = tc::make_desc(r0_u, PATCH_CHUNK, 128), d_w1 = tc::make_desc(w1_u, L::W1_CHUNK, 128);
   const uint64_t d_a1 = tc::make_desc(a1_u, P1_PLANE, 128), d_w2 = tc::make_desc(w2_u, L::P * W2_CHUNK, 128);
@@ -548,7 +556,33 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         }
     };
     auto conv2_epilogue = [&](int tl, uint32_t dcol) {
-      if (kStack) {
+      if (kStack && !kWide) {
+        // 128-thread slot, stacked tile: columns [0,64) = A.B_hi, [64,128) = A.B_lo, 16 channels x 4 sub-positions each;
+        // two sub-positions per pass keep the live registers at 64 + 16
+        float m4[16];
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          float a[32], b[32];
+          tc::tmem_ld32(tq + dcol + half * 32, a);
+          tc::tmem_ld32(tq + dcol + 64 + half * 32, b);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int co = 0; co < 16; ++co) {
+            const float x = fmaxf(a[co] + b[co], a[16 + co] + b[16 + co]);
+            m4[co] = half ? fmaxf(m4[co], x) : x;
+          }
+        }
+        if (a2off[tl] >= 0) {
+          float hi[16], bb[16];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) *reinterpret_cast<float4*>(bb + 4 * i) = *reinterpret_cast<const float4*>(sh.b2 + 4 * i);
+#pragma unroll
+          for (int co = 0; co < 16; ++co) hi[co] = fmaxf(m4[co] + bb[co], 0.f);
+          const uint32_t off = (uint32_t)a2off[tl];
+          *reinterpret_cast<uint4*>(r0 + off) = pack8(hi);
+          *reinterpret_cast<uint4*>(r0 + PLANE2 + off) = pack8(hi + 8);
+        }
+      } else if (kStack) {
         // 256-thread slots: warpgroup wg owns output channels 8wg..8wg+7 (= channel plane wg of a2); per sub-position
         // it adds the A_hi.B_lo half (columns 64..) to the main half, then max / bias / ReLU / hi-lo split
         float m4[8];
@@ -609,7 +643,7 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         }
       }
     };
-    {
+    if (C2_FLY == 2) {
       // two tiles of TMEM columns: tiles 0 and 1 in flight, tile 2 re-uses tile 0's columns once its epilogue is
       // done; every tile has its own commit, so an epilogue overlaps the next tile's MMAs
       if (warp == 0 && tc::elect_one()) {
@@ -635,6 +669,21 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1;
       tc::fence_after_sync();
       conv2_epilogue(2, 0);
+    } else {
+      // one stacked tile fills the slot's TMEM columns: the three tiles run one after the other (the other slots' MMAs
+      // fill the tensor pipe meanwhile)
+#pragma unroll
+      for (int tl = 0; tl < 3; ++tl) {
+        if (warp == 0 && tc::elect_one()) {
+          tc::fence_after_sync();
+          conv2_issue(tl, 0);
+          tc::mma_commit(&mz.bar[0]);
+        }
+        tc::mbar_wait_bounded(&mz.bar[0], ph0); ph0 ^= 1;
+        tc::fence_after_sync();
+        conv2_epilogue(tl, 0);
+        if (tl < 2) { tc::fence_before_sync(); slot_sync<ST>(slot); }
+      }
     }
     tc::fence_async_smem();
     tc::fence_before_sync();
@@ -643,21 +692,22 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
     // ================= conv3 + ReLU + mean: 3 tiles of 16 rows x 8 columns (12 rows real), 9 taps
     // every tile has its own commit (bar[0..2]): the channel sums of tile i are taken while tiles i+1.. are still in the
     // tensor core
+    auto conv3_issue = [&](int tx, uint32_t col) {
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {
+        const int dy = tap / 3, dx = tap % 3;
+        const uint32_t a_off = (dy * PITCH2 + tx * 8 + dx) * 16;
+        const uint64_t db = tc::desc_add(d_w3, 2 * tap * L::W3_CHUNK);
+        tc::mma_f16(tmem + col, tc::desc_add(d_a2, a_off), db, idesc3_hi, tap > 0);
+        if (kALo) tc::mma_f16(tmem + col, tc::desc_add(d_a2, A2_BYTES + a_off), db, idesc3_lo, true);
+        if (kSplit && !kStack) tc::mma_f16(tmem + col, tc::desc_add(d_a2, a_off), tc::desc_add(db, 32 * 16), idesc3_lo, true);
+      }
+      tc::mma_commit(&mz.bar[tx]);
+    };
     if (warp == 0 && tc::elect_one()) {
       tc::fence_after_sync();
 #pragma unroll
-      for (int tx = 0; tx < 3; ++tx) {
-#pragma unroll
-        for (int tap = 0; tap < 9; ++tap) {
-          const int dy = tap / 3, dx = tap % 3;
-          const uint32_t a_off = (dy * PITCH2 + tx * 8 + dx) * 16;
-          const uint64_t db = tc::desc_add(d_w3, 2 * tap * L::W3_CHUNK);
-          tc::mma_f16(tmem + tx * COLS3, tc::desc_add(d_a2, a_off), db, idesc3_hi, tap > 0);
-          if (kALo) tc::mma_f16(tmem + tx * COLS3, tc::desc_add(d_a2, A2_BYTES + a_off), db, idesc3_lo, true);
-          if (kSplit && !kStack) tc::mma_f16(tmem + tx * COLS3, tc::desc_add(d_a2, a_off), tc::desc_add(db, 32 * 16), idesc3_lo, true);
-        }
-        tc::mma_commit(&mz.bar[tx]);
-      }
+      for (int tx = 0; tx < C3_FLY; ++tx) conv3_issue(tx, tx * COLS3);
     }
     float acc[C3P];
 #pragma unroll
@@ -669,12 +719,13 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
       if (tx == 1) { tc::mbar_wait_bounded(&mz.bar[1], ph1); ph1 ^= 1; }
       if (tx == 2) { tc::mbar_wait_bounded(&mz.bar[2], ph2); ph2 ^= 1; }
       tc::fence_after_sync();
+      const uint32_t col3 = (tx % C3_FLY) * COLS3;         // tile 2 re-uses tile 0's columns when only two fit
       if (q < 3 && tx % NWG == wg) {
         float v[32];
-        tc::tmem_ld32(tq + tx * COLS3, v);
+        tc::tmem_ld32(tq + col3, v);
         if (kStack) {
           float w[32];
-          tc::tmem_ld32(tq + tx * COLS3 + 32, w);
+          tc::tmem_ld32(tq + col3 + 32, w);
           tc::tmem_ld_wait();
 #pragma unroll
           for (int c = 0; c < C3; ++c) v[c] += w[c];
@@ -694,6 +745,11 @@ roi_cnn_tc3_kernel(const uint8_t* __restrict__ R, const int64_t* __restrict__ le
         }
         if (kSave)                                                       // tile tx: image rows row/8, columns 8 tx + row%8
           reinterpret_cast<uint32_t*>(saved + f * SV_BYTES + SV_MASK3)[(row >> 3) * W2 + tx * 8 + (row & 7)] = on;
+      }
+      if (C3_FLY == 2 && tx == 0) {                      // tile 0's columns have been read: tile 2 goes into them
+        tc::fence_before_sync();
+        slot_sync<ST>(slot);
+        if (warp == 0 && tc::elect_one()) { tc::fence_after_sync(); conv3_issue(2, 0); }
       }
     }
     if (q < 3) {
@@ -757,7 +813,7 @@ static int ssb_k2_tc2_slots_() {
   return n;
 }
 namespace ssb { namespace cnn3 {
-template <bool kSplit, bool kALo, int kSlots, int ST, bool kSave>
+template <bool kSplit, bool kALo, int kSlots, int ST, bool kSave, bool kStack>
 static int launch_k2(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T, const Weights& gw, int32_t standardize,
                      float* out, int64_t out_stride, unsigned int* counter, void* saved, cudaStream_t st) {
   constexpr size_t smem = smem_total<kSplit, kALo, kSlots>();
@@ -765,7 +821,7 @@ static int launch_k2(const uint8_t* R, const int64_t* lengths, int64_t B, int64_
   static_assert((kSlots == 2) == (ST == 256), "two wide or four narrow slots");
   const int64_t want = (B * T + kSlots - 1) / kSlots;
   const int grid = (int)(want < kSMs ? want : kSMs);
-  auto kern = roi_cnn_tc3_kernel<kSplit, kALo, kSlots, ST, kSave>;
+  auto kern = roi_cnn_tc3_kernel<kSplit, kALo, kSlots, ST, kSave, kStack>;
   SSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<grid, ST * kSlots, smem, st>>>(R, lengths, (int)B, (int)T, gw, standardize, out, out_stride, counter,
                                         reinterpret_cast<uint8_t*>(saved));
@@ -791,14 +847,15 @@ extern "C" int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int
   unsigned int* counter = nullptr;
   if (int rc = ssb_scratch_counter_(st, &counter)) return rc;
   if (passes == 3) {                                   // both operands split: fp32-parity grade, the training mode
-    return saved ? launch_k2<true, true, 2, 256, true>(R, lengths, B, T, gw, standardize, out, out_stride, counter, saved, st)
-                 : launch_k2<true, true, 2, 256, false>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
+    return saved ? launch_k2<true, true, 2, 256, true, true>(R, lengths, B, T, gw, standardize, out, out_stride, counter, saved, st)
+                 : launch_k2<true, true, 2, 256, false, true>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
   }
   if (passes == 2) {                                   // split weights, activations rounded to fp16 once
-    // four narrow slots: 10.5 ms per 4096 clips against 12.1 ms for two wide ones (B200, r2)
-    if (ssb_k2_tc2_slots_() == 2) return launch_k2<true, false, 2, 256, false>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
-    return launch_k2<true, false, 4, 128, false>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
+    // four narrow slots (A/B: SSB_K2_TC2_SLOTS=2 two wide slots, =4 four narrow slots with hi / lo as separate MMAs)
+    if (ssb_k2_tc2_slots_() == 2) return launch_k2<true, false, 2, 256, false, true>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
+    if (ssb_k2_tc2_slots_() == 4) return launch_k2<true, false, 4, 128, false, false>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
+    return launch_k2<true, false, 4, 128, false, true>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
   }
   if (!ssb_k2_single_pass_v4_()) return ssb_roi_cnn_fwd_v3_(R, lengths, B, T, weights, standardize, out, out_stride, stream);   // roi_cnn_v3.cu
-  return launch_k2<false, false, 4, 128, false>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
+  return launch_k2<false, false, 4, 128, false, false>(R, lengths, B, T, gw, standardize, out, out_stride, counter, nullptr, st);
 }
