@@ -205,6 +205,12 @@ int ssb_proj_prepack_split(const float* W_a, const float* W_b, int64_t ldw, int6
 int ssb_proj_gemm_split(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
                         const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
                         const int64_t* lengths, int64_t T, void* stream);
+/* Inference form of the split projection (same call sites, train_model_official.py:261-267 under torch.no_grad):
+ * the packed weights of ssb_proj_prepack_split, activations rounded to fp16 once, D += W_hi.A + W_lo.A on 128-row tiles
+ * (two N = 128 MMAs per k-step instead of three N = 64 ones per 64 rows).  Same arguments as ssb_proj_gemm_split. */
+int ssb_proj_gemm_wsplit(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                         const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
+                         const int64_t* lengths, int64_t T, void* stream);
 
 /* K3a v2 without any allocation: ssb_proj_prepack + ssb_proj_gemm in one call, the packed-weight workspace being a
  * file-scope static device array of the library instead of caller-owned memory.  NO COUNTERPART IN THE REFERENCE: added

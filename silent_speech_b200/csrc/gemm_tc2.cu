@@ -283,17 +283,25 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
 // rate and the accumulator comes out TRANSPOSED: TMEM lane = output column n, TMEM column = tile row m.  The epilogue
 // therefore needs no shared-memory transpose: a warp's 32 lanes hold 32 consecutive n of one row, i.e. every store
 // instruction writes one full 128-byte row segment of C.
-constexpr int SBM = 64;                                  // activation rows per tile
-constexpr int SCHUNK = SBM * 16;                         // one k-chunk (8 k) of 64 rows
+//
+// kALo = false ("weights split", the inference form): the activations are rounded to fp16 ONCE and D += W_hi.A + W_lo.A.
+// Without the lo copy a 128-row tile fits (the same 96 KB), so each of the two MMAs per k-step has N = 128: per 128 rows
+// 2 x 64 tensor-pipe cycles instead of 6 x 48 (an M = 128, K = 16 MMA costs about 32 + N/4 cycles), and the activation
+// conversion is half the work.  Logits stay within 1e-4 of the CPU reference (bench.py's parity block); training keeps kALo.
 constexpr int SSTAGES = 3;
-constexpr int STMEM_COLS = 128;                          // two 64-column accumulators
 
+template <bool kALo>
 __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
+  constexpr int SBM = kALo ? 64 : 128;                     // activation rows per tile
+  constexpr int SCHUNK = SBM * 16;                         // one k-chunk (8 k) of one part of the tile
+  constexpr int ACH = 2048;                                // one k-chunk of the whole tile: 128 rows, or 64 hi rows | 64 lo rows
+  constexpr int ACC = 128;                                 // TMEM columns per accumulator
+  constexpr int STMEM_COLS = 2 * ACC;                      // two accumulators
+  constexpr int RG = SBM / 8;                              // 8-row groups per tile
   extern __shared__ __align__(1024) uint8_t smem[];
   const int K1p = round_up(a.K1, 8), Kp = kp_of(a.K1, a.K2), nkb = Kp / KB, nnt = (a.N + BN - 1) / BN;
   uint8_t* act_hi = smem;                                    // Kp/8 chunks x 1024 B
-  uint8_t* act_lo = act_hi + (Kp / 8) * SCHUNK;
-  uint8_t* w_s = act_lo + (Kp / 8) * SCHUNK;                 // SSTAGES x (16 KB hi + 16 KB lo)
+  uint8_t* w_s = act_hi + (Kp / 8) * ACH;                    // SSTAGES x (16 KB hi + 16 KB lo)
   float* bias_s = reinterpret_cast<float*>(w_s + SSTAGES * 2 * W_BLOCK);   // nnt * 128 floats
   uint8_t* live_s = reinterpret_cast<uint8_t*>(bias_s + nnt * BN);         // 64 bytes
   Ctl& ctl = *reinterpret_cast<Ctl*>(live_s + SBM);
@@ -311,8 +319,10 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = __shfl_sync(0xffffffffu, ctl.tmem_base, 0);
-  const uint32_t ah_u = tc::smem_u32(act_hi), al_u = tc::smem_u32(act_lo), w_u = tc::smem_u32(w_s);
-  constexpr uint32_t idesc = tc::make_idesc_f16(BN, SBM);     // M = 128 weight rows, N = 64 activation rows
+  const uint32_t ah_u = tc::smem_u32(act_hi), w_u = tc::smem_u32(w_s);
+  // M = 128 weight rows; N = the tile's 128 operand rows (kALo: 64 hi rows | 64 lo rows side by side, so W_hi.[A_hi | A_lo]
+  // is ONE MMA -- an M = 128, K = 16 MMA costs about 32 + N/4 cycles, the weight operand being fetched per instruction)
+  constexpr uint32_t idesc = tc::make_idesc_f16(BN, 128), idesc_lo = tc::make_idesc_f16(BN, SBM);
   uint32_t w_it = 0, acc_it = 0;
 
   const int m_tiles = (a.M + SBM - 1) / SBM;
@@ -336,10 +346,10 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
 #pragma unroll
         for (int u = 0; u < NB; ++u) {
           const int idx = base + u * THREADS;
-          const int r8 = idx & 7, c4 = (idx >> 3) & 3, rest = idx >> 5, rg = rest & 7, cg = rest >> 3;
+          const int r8 = idx & 7, c4 = (idx >> 3) & 3, rest = idx >> 5, rg = rest % RG, cg = rest / RG;
           const int row = rg * 8 + r8, chunk = cg * 4 + c4, kk = chunk * 8;
           v0[u] = make_float4(0.f, 0.f, 0.f, 0.f); v1[u] = v0[u];
-          dst[u] = idx < items ? (uint32_t)(chunk * SCHUNK + rg * 128 + r8 * 16) : 0xffffffffu;
+          dst[u] = idx < items ? (uint32_t)(chunk * ACH + rg * 128 + r8 * 16) : 0xffffffffu;
           if (idx < items && m0 + row < a.M) {
             if (kk < K1p) {
               const float* g = a.A1 + (int64_t)(m0 + row) * a.lda1 + kk;
@@ -357,12 +367,15 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
         for (int u = 0; u < NB; ++u)
           if (dst[u] != 0xffffffffu) {
             float x[8] = {v0[u].x, v0[u].y, v0[u].z, v0[u].w, v1[u].x, v1[u].y, v1[u].z, v1[u].w}, l[8];
+            uint8_t* act_lo = act_hi + SCHUNK;               // kALo: the lo rows follow the hi rows inside every k-chunk
 #pragma unroll
-            for (int j = 0; j < 8; ++j) tc::split_f16(x[j], x[j], l[j]);
+            for (int j = 0; j < 8; ++j)
+              if (kALo) tc::split_f16(x[j], x[j], l[j]);     // otherwise pack_f16 rounds once
             *reinterpret_cast<uint4*>(act_hi + dst[u]) = make_uint4(tc::pack_f16(x[0], x[1]), tc::pack_f16(x[2], x[3]),
                                                                     tc::pack_f16(x[4], x[5]), tc::pack_f16(x[6], x[7]));
-            *reinterpret_cast<uint4*>(act_lo + dst[u]) = make_uint4(tc::pack_f16(l[0], l[1]), tc::pack_f16(l[2], l[3]),
-                                                                    tc::pack_f16(l[4], l[5]), tc::pack_f16(l[6], l[7]));
+            if (kALo)
+              *reinterpret_cast<uint4*>(act_lo + dst[u]) = make_uint4(tc::pack_f16(l[0], l[1]), tc::pack_f16(l[2], l[3]),
+                                                                      tc::pack_f16(l[4], l[5]), tc::pack_f16(l[6], l[7]));
           }
       }
     }
@@ -396,14 +409,13 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
             tc::fence_after_sync();
 #pragma unroll
             for (int j = 0; j < KB / 16; ++j) {
-              const uint32_t koff = (kb * (KB / 8) + 2 * j) * SCHUNK;
+              const uint32_t koff = (kb * (KB / 8) + 2 * j) * ACH;
               const uint64_t dwh = tc::make_desc(w_u + s * 2 * W_BLOCK + 2 * j * CHUNK, CHUNK, 128);
               const uint64_t dwl = tc::make_desc(w_u + s * 2 * W_BLOCK + W_BLOCK + 2 * j * CHUNK, CHUNK, 128);
-              const uint64_t dah = tc::make_desc(ah_u + koff, SCHUNK, 128);
-              const uint64_t dal = tc::make_desc(al_u + koff, SCHUNK, 128);
-              tc::mma_f16(tmem + buf * SBM, dwh, dah, idesc, (kb | j) != 0);
-              tc::mma_f16(tmem + buf * SBM, dwl, dah, idesc, true);
-              tc::mma_f16(tmem + buf * SBM, dwh, dal, idesc, true);
+              const uint64_t dact = tc::make_desc(ah_u + koff, ACH, 128);
+              // columns [0, SBM): W_hi.A_hi + W_lo.A_hi; kALo: columns [64, 128): W_hi.A_lo (added in the epilogue)
+              tc::mma_f16(tmem + buf * ACC, dwh, dact, idesc, (kb | j) != 0);
+              tc::mma_f16(tmem + buf * ACC, dwl, dact, idesc_lo, true);
             }
             tc::mma_commit(&ctl.empty[s]);
           }
@@ -418,16 +430,23 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
       // =============================== epilogue warps ===============================
       // warp w reads TMEM lanes 32 (w % 4) .. (= output columns nt*128 + 32 (w % 4) + lane) and the 32 accumulator columns
       // (= tile rows) 32 (w / 4) ..; one store instruction per row: 32 lanes x 4 B = one 128-byte segment of C
+      // (a 128-row tile: two such column blocks per warp)
+      constexpr int CB = 2;                                    // 32-column blocks per warp: two row blocks, or hi part + lo part
       const int q = warp & 3, half = warp >> 2;
       const uint32_t tlane = tmem + ((uint32_t)(q * 32) << 16);
-      uint32_t live_mask = 0;
-      for (int r = 0; r < 32; ++r) live_mask |= (live_s[half * 32 + r] != 0 ? 1u : 0u) << r;
+      uint32_t live_mask[CB];
+#pragma unroll
+      for (int cb = 0; cb < CB; ++cb) {
+        live_mask[cb] = 0;
+        for (int r = 0; r < 32; ++r) live_mask[cb] |= (live_s[(kALo ? half : half * CB + cb) * 32 + r] != 0 ? 1u : 0u) << r;
+      }
       for (int nt = 0; nt < nnt; ++nt, ++acc_it) {
         const uint32_t buf = acc_it & 1;
         tc::mbar_wait_bounded(&ctl.accfull[buf], (acc_it >> 1) & 1);
         tc::fence_after_sync();
-        float v[32];
-        tc::tmem_ld32(tlane + buf * SBM + half * 32, v);
+        float v[CB][32];
+#pragma unroll
+        for (int cb = 0; cb < CB; ++cb) tc::tmem_ld32(tlane + buf * ACC + (kALo ? cb * 64 + half * 32 : (half * CB + cb) * 32), v[cb]);
         tc::tmem_ld_wait();
         tc::fence_before_sync();
         __syncwarp();
@@ -435,10 +454,13 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
         const int n = nt * BN + q * 32 + lane;
         if (n < a.N) {
           const float bv = bias_s[n];
-          float* c = a.C + (int64_t)(m0 + half * 32) * a.ldc + n;
 #pragma unroll
-          for (int r = 0; r < 32; ++r)
-            if ((live_mask >> r) & 1u) c[(int64_t)r * a.ldc] = v[r] + bv;
+          for (int cb = 0; cb < (kALo ? 1 : CB); ++cb) {
+            float* c = a.C + (int64_t)(m0 + (kALo ? half : half * CB + cb) * 32) * a.ldc + n;
+#pragma unroll
+            for (int r = 0; r < 32; ++r)
+              if ((live_mask[cb] >> r) & 1u) c[(int64_t)r * a.ldc] = (kALo ? v[0][r] + v[1][r] : v[cb][r]) + bv;
+          }
         }
       }
     }
@@ -448,8 +470,8 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
   if (warp == 0) tc::tmem_dealloc<STMEM_COLS>(tmem);
 }
 
-inline size_t smem_bytes_split(int Kp, int nnt) {
-  return (size_t)2 * (Kp / 8) * SCHUNK + SSTAGES * 2 * W_BLOCK + (size_t)nnt * BN * 4 + SBM + sizeof(Ctl);
+inline size_t smem_bytes_split(int Kp, int nnt) {          // both forms: 2 x 64 rows or 1 x 128 rows of fp16 activations
+  return (size_t)(Kp / 8) * 2048 + SSTAGES * 2 * W_BLOCK + (size_t)nnt * BN * 4 + 128 + sizeof(Ctl);
 }
 
 inline size_t smem_bytes(int Kp, int nnt) {
@@ -533,9 +555,9 @@ extern "C" int ssb_proj_gemm(const float* A1, int64_t lda1, int64_t K1, const fl
 // C[M, N] = [A1 | A2] . W^T + bias at fp32-parity grade (fp16 hi/lo split of both operands, three products, fp32 accumulation
 // in TMEM): the input projection of the split-mode recurrence for both directions in one persistent launch.  packed comes
 // from ssb_proj_prepack_split.  Same alignment rules as ssb_proj_gemm; C is fp32.
-extern "C" int ssb_proj_gemm_split(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
-                                   const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
-                                   const int64_t* lengths, int64_t T, void* stream) {
+static int proj_gemm_split_impl(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                                const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
+                                const int64_t* lengths, int64_t T, bool act_lo, void* stream) {
   using namespace ssb;
   using namespace ssb::gemm2;
   SSB_REQUIRE(A1 && packed && C, "null pointer");
@@ -553,11 +575,29 @@ extern "C" int ssb_proj_gemm_split(const float* A1, int64_t lda1, int64_t K1, co
   const int nnt = cdiv(N, BN);
   const size_t smem = smem_bytes_split(Kp, nnt);
   SSB_REQUIRE(smem <= 232448, "shared-memory budget");
-  const int m_tiles = cdiv(M, SBM);
-  SSB_CUDA(cudaFuncSetAttribute(proj_gemm_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  proj_gemm_split_kernel<<<m_tiles < kSMs ? m_tiles : kSMs, THREADS, smem, (cudaStream_t)stream>>>(a);
+  const int m_tiles = cdiv(M, act_lo ? 64 : 128);
+  const int grid = m_tiles < kSMs ? m_tiles : kSMs;
+  if (act_lo) {
+    SSB_CUDA(cudaFuncSetAttribute(proj_gemm_split_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    proj_gemm_split_kernel<true><<<grid, THREADS, smem, (cudaStream_t)stream>>>(a);
+  } else {
+    SSB_CUDA(cudaFuncSetAttribute(proj_gemm_split_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    proj_gemm_split_kernel<false><<<grid, THREADS, smem, (cudaStream_t)stream>>>(a);
+  }
   SSB_LAUNCH_CHECK();
   return SSB_OK;
+}
+extern "C" int ssb_proj_gemm_split(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                                   const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
+                                   const int64_t* lengths, int64_t T, void* stream) {
+  return proj_gemm_split_impl(A1, lda1, K1, A2, lda2, K2, packed, bias, C, ldc, M, N, lengths, T, true, stream);
+}
+// The inference form of the split projection: the same packed weights (ssb_proj_prepack_split), activations rounded to
+// fp16 once, D += W_hi.A + W_lo.A on 128-row tiles.
+extern "C" int ssb_proj_gemm_wsplit(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
+                                    const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,
+                                    const int64_t* lengths, int64_t T, void* stream) {
+  return proj_gemm_split_impl(A1, lda1, K1, A2, lda2, K2, packed, bias, C, ldc, M, N, lengths, T, false, stream);
 }
 
 // ------------------------------------------------------------------------------------------------- no-allocation variant

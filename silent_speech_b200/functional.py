@@ -23,6 +23,14 @@ def _passes(model):
     return {"fp32": (0, 0), "tc3": (3, 3), "fp16": (1, 1), "cnn16": (1, 3), "gru16": (3, 1)}[getattr(model, "precision", "fp32")]
 
 
+# Inference projections: splitting the activations too is the default.  Rounding them to fp16 once (ssb_proj_gemm_wsplit:
+# 128-row tiles, two MMAs per k-step; model.proj_full_split = False or a tuple of the layers that keep the full split) makes
+# the two projections 0.7 ms faster per 4096 clips but costs about 1e-4 of max |logit| PER LAYER (tools/proj_probe.py:
+# 1.6e-4 .. 2.5e-4 with both) -- the recurrence carries a gi error through 90 steps, unlike the ROI CNN, whose activations
+# can be rounded for free (cnn_passes).  That misses the 1e-4 bar of the tc3 mode, so it stays opt-in.
+PROJ_FULL_SPLIT_DEFAULT = True
+
+
 def cnn_passes(model, save: bool = False) -> int:
     """`passes` of the ROI-CNN kernel for this call.  In the fp32-parity mode (tc3) the training forward (save) runs the full
     split (3: weights and activations as fp16 hi + lo; the saved activations are fp32); inference runs 2: split weights,
@@ -84,7 +92,7 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
     if passes and B > 128:      # homogeneous 128-clip tiles: each cluster runs max(len in tile) steps
         order = torch.argsort(lengths, descending=True).to(torch.int32)
 
-    def layer(pl, A2d, extra, gates):
+    def layer(pl, A2d, extra, gates, idx):
         if not passes:
             _project(A2d, pl["weight_ih"], pl["bias_ih"], gi2d, lengths, T, extra=extra)
             return ops.gru_layer_fwd(gi, lengths, pl["weight_hh"][0], pl["bias_hh"][0], pl["weight_hh"][1],
@@ -106,19 +114,25 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
         # split mode (fp32-parity grade): the same persistent GEMM with hi/lo operands, both directions in one launch
         packed = ops.proj_prepack(pl["weight_ih"][0], pl["weight_ih"][1], A2d.shape[1], 0 if extra is None else extra.shape[1],
                                   split=True)
-        ops.proj_gemm(A2d, packed, fold, gi2d, 2 * G3, A2=extra, lengths=lengths, T=T, split=True)
+        # training (gates saved) always splits the activations; inference follows model.proj_full_split (see above)
+        full = getattr(model, "proj_full_split", None)       # None: default policy; True / False / tuple of layer indices
+        if full is None:
+            full = PROJ_FULL_SPLIT_DEFAULT
+        full = (idx in full) if isinstance(full, (tuple, list, set)) else bool(full)
+        ops.proj_gemm(A2d, packed, fold, gi2d, 2 * G3, A2=extra, lengths=lengths, T=T, split=True,
+                      act_split=gates is not None or full)
         return ops.gru_layer_fwd_tc(gi, lengths, pl["weight_hh"][0], pl["bias_hh"][0], pl["weight_hh"][1],
                                     pl["bias_hh"][1], passes=passes, order=order, gates=gates)
 
     gates0 = torch.empty(B, T, 2, 4, H, device=dev, dtype=torch.float32) if save else None
-    seq0 = layer(p0, X.view(B * T, x_dim), None if emb is None else emb.view(B * T, -1), gates0)
+    seq0 = layer(p0, X.view(B * T, x_dim), None if emb is None else emb.view(B * T, -1), gates0, 0)
     seq0_in = seq0
     drop_seed = 0
     if training and model.gru_dropout > 0:
         drop_seed = model._next_seed()
         seq0_in = ops.dropout(seq0, model.gru_dropout, drop_seed)
     gates1 = torch.empty(B, T, 2, 4, H, device=dev, dtype=torch.float32) if save else None
-    seq1 = layer(p1, seq0_in.view(B * T, 2 * H), None, gates1)
+    seq1 = layer(p1, seq0_in.view(B * T, 2 * H), None, gates1, 1)
     saved = None
     if save:
         saved = [torch.empty(B, T, device=dev), torch.empty(B, 2 * H, device=dev), torch.empty(B, 2 * H, device=dev),

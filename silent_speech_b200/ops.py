@@ -297,16 +297,18 @@ def proj_prepack(W_a: torch.Tensor, W_b: Optional[torch.Tensor], K1: int, K2: in
 
 
 def proj_gemm(A1: torch.Tensor, packed: torch.Tensor, bias, C2d: torch.Tensor, N: int, A2: Optional[torch.Tensor] = None,
-              lengths=None, T: int = 0, split: bool = False):
+              lengths=None, T: int = 0, split: bool = False, act_split: bool = True):
     # C2d may be float32 or float16 (fp16 gi for the single-pass recurrence)
     """C[:, :N] = [A1 | A2] @ packed^T + bias: both directions' input projections in one persistent tcgen05 GEMM.
-    split: fp32-parity grade (hi/lo split of both operands; packed from proj_prepack(..., split=True); C fp32)."""
+    split: fp32-parity grade (hi/lo split of both operands; packed from proj_prepack(..., split=True); C fp32);
+    act_split=False: the inference form (weights split, activations rounded to fp16 once, 128-row tiles)."""
     M, K1 = A1.shape
     K2 = 0 if A2 is None else A2.shape[1]
     if split:
         if not (C2d.is_cuda and C2d.dtype == torch.float32 and C2d.stride(1) == 1):
             raise _lib.SsbError("split projection: C must be a CUDA float32 matrix with unit column stride")
-        check(_lib.lib().ssb_proj_gemm_split(ptr(A1), i64(A1.stride(0)), i64(K1), ptr(A2), i64(0 if A2 is None else A2.stride(0)),
+        fn = _lib.lib().ssb_proj_gemm_split if act_split else _lib.lib().ssb_proj_gemm_wsplit
+        check(fn(ptr(A1), i64(A1.stride(0)), i64(K1), ptr(A2), i64(0 if A2 is None else A2.stride(0)),
                                              i64(K2), ptr(packed), ptr(bias), ptr(C2d), i64(C2d.stride(0)), i64(M), i64(N),
                                              ptr(lengths), i64(T), stream_ptr()))
         return C2d

@@ -239,10 +239,13 @@ def test_proj_gemm_vs_fp64(M, n_each, K1, K2, T):
 
 @pytest.mark.parametrize("M,n_each,K1,K2,T", [(64, 576, 180, 32, 0), (1000, 576, 384, 0, 10), (77, 576, 180, 0, 0),
                                               (39960, 576, 180, 32, 90), (300, 200, 64, 0, 0), (130, 576, 384, 0, 0)])
-def test_proj_gemm_split_vs_fp64(M, n_each, K1, K2, T):
+@pytest.mark.parametrize("act_split", [True, False])
+def test_proj_gemm_split_vs_fp64(M, n_each, K1, K2, T, act_split):
     """The fp32-parity projection GEMM (hi/lo split of both operands, weights as the M = 128 operand, transposed
     accumulator): within 2e-6 of the fp64 product of the raw fp32 operands (tolerance of the 1e-4 parity budget),
-    rows of padded frames and the columns past N untouched."""
+    rows of padded frames and the columns past N untouched.  act_split=False is the inference form (activations rounded
+    to fp16 once: 128-row tiles, two MMAs per k-step): within 3e-4 of fp64 at the GEMM (the activations' rounding, 2^-12
+    per element, averaged over K), and it is the model-level tests and bench.py's parity block that hold the logits to 1e-4."""
     dev = _cuda()
     from silent_speech_b200 import ops
     g = torch.Generator().manual_seed(M + K1 + 1)
@@ -261,7 +264,8 @@ def test_proj_gemm_split_vs_fp64(M, n_each, K1, K2, T):
         Lh[0] = T
         L = Lh.to(dev)
     packed = ops.proj_prepack(Wa.to(dev), Wb.to(dev), K1, K2, split=True)
-    ops.proj_gemm(A1.to(dev), packed, b.to(dev), C[:, :N], N, A2=None if A2 is None else A2.to(dev), lengths=L, T=T, split=True)
+    ops.proj_gemm(A1.to(dev), packed, b.to(dev), C[:, :N], N, A2=None if A2 is None else A2.to(dev), lengths=L, T=T, split=True,
+                  act_split=act_split)
     torch.cuda.synchronize()
     out = C.cpu()
     assert torch.all(out[:, N:] == -7.0)
@@ -272,11 +276,12 @@ def test_proj_gemm_split_vs_fp64(M, n_each, K1, K2, T):
         live[:Mr] = (torch.arange(T)[None, :] < Lh[:, None]).reshape(-1)
         assert torch.all(out[~live][:, :N] == -7.0)
     e = rel_err(out[live][:, :N], ref[live])
-    print(f"proj split M={M} K={K1}+{K2}: rel err {e:.2e}")
-    assert e < 2e-6
+    print(f"proj split M={M} K={K1}+{K2} act_split={act_split}: rel err {e:.2e}")
+    assert e < (2e-6 if act_split else 3e-4)
     # repeated launches are bit-identical (ring phases, accumulator hand-over)
     C2 = torch.full((M, N + 4), -7.0, device=dev)
-    ops.proj_gemm(A1.to(dev), packed, b.to(dev), C2[:, :N], N, A2=None if A2 is None else A2.to(dev), lengths=L, T=T, split=True)
+    ops.proj_gemm(A1.to(dev), packed, b.to(dev), C2[:, :N], N, A2=None if A2 is None else A2.to(dev), lengths=L, T=T, split=True,
+                  act_split=act_split)
     assert torch.equal(C2.cpu(), out)
 
 

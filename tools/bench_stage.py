@@ -78,7 +78,7 @@ elif a.stage == "proj":
         fn = lambda: ops.proj_gemm(A1, packed, bias, gi, 2 * G3, A2=A2, lengths=L, T=T)
     else:
         packed = ops.proj_prepack(Wa, Wb, K1, K2, split=True)
-        fn = lambda: ops.proj_gemm(A1, packed, bias, gi, 2 * G3, A2=A2, lengths=L, T=T, split=True)
+        fn = lambda: ops.proj_gemm(A1, packed, bias, gi, 2 * G3, A2=A2, lengths=L, T=T, split=True, act_split=(a.precision != 'tc2'))
     best, mean = timeit(fn)
     by = B * T * (2 * G3 + K1 + K2) * 4
     print(f"proj layer {a.layer} {a.precision} B={B}: best {best:.3f} ms mean {mean:.3f} ms  {by / best / 1e6:.0f} GB/s algorithmic (A read + C write)")
