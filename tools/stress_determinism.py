@@ -83,7 +83,7 @@ names = ["roi_cnn.net.0.weight", "roi_cnn.net.0.bias", "roi_cnn.net.3.weight", "
 wc = [pr[n] for n in names]
 dr = synth.clip_batch(200, 90, mode="uniform", seed=4)
 Rd, Ld = torch.from_numpy(dr["R"]).to(dev), torch.from_numpy(dr["lengths"]).to(dev)
-for passes in (3, 1):
+for passes in (3, 2, 1):      # 2: the tc3 inference form (four narrow slots, hi|lo stacked, conv2 tiles one after the other)
     first, bad = None, 0
     for it in range(reps):
         junk = torch.randn(1 << 20, device=dev) * 1e3
@@ -99,19 +99,19 @@ for passes in (3, 1):
 A = torch.randn(260 * 64, 384, device=dev)
 Wa, Wb = pr["gru.weight_ih_l1"], pr["gru.weight_ih_l1_reverse"]
 bias = torch.randn(2 * G3, device=dev)
-for split in (True, False):
+for split, act_split in ((True, True), (True, False), (False, True)):
     packed = ops.proj_prepack(Wa, Wb, 384, 0, split=split)
     first, bad = None, 0
     for it in range(reps):
         junk = torch.randn(1 << 20, device=dev) * 1e3
         c = torch.full((260 * 64, 2 * G3), float("nan"), device=dev)
-        ops.proj_gemm(A, packed, bias, c, 2 * G3, lengths=L, T=T, split=split)
+        ops.proj_gemm(A, packed, bias, c, 2 * G3, lengths=L, T=T, split=split, act_split=act_split)
         c = torch.where(mask.reshape(-1, 1), c, torch.zeros_like(c))
         if first is None:
             first = c.clone()
         elif not torch.equal(c, first):
             bad += 1
-            print(f"proj_gemm split={split} it={it}: differs")
+            print(f"proj_gemm split={split} act_split={act_split} it={it}: differs")
         del junk
     torch.cuda.synchronize()
-    print(f"proj_gemm split={split}: {reps} reps, mismatches {bad}")
+    print(f"proj_gemm split={split} act_split={act_split}: {reps} reps, mismatches {bad}")
