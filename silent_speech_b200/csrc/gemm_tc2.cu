@@ -15,6 +15,8 @@
 //     4-stage weight ring and two 128-column TMEM accumulators, so the epilogue (TMEM -> +bias -> global)
 //     of tile n overlaps the MMAs of tile n+1.
 // K is laid out as [A1 padded to 8 | A2 padded to 8 | zeros to a multiple of 64] on both operands.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -24,14 +26,14 @@ namespace gemm2 {
 constexpr int BM = 128, BN = 128, KB = 64;
 constexpr int CHUNK = 2048;                              // one k-chunk (8 k) of 128 rows: 16 groups x 128 B
 constexpr int W_BLOCK = (KB / 8) * CHUNK;                // 16,384 B
-constexpr int STAGES = 4;
+constexpr int STAGES = 4, MAX_STAGES = 4;
 constexpr int EPI_WARPS = 8, THREADS = (EPI_WARPS + 2) * 32;   // two epilogue warps per TMEM lane quarter
 constexpr int TILE_LD = 36;                              // floats per row of an epilogue transpose tile (conflict-free 16-byte accesses)
 constexpr int TMEM_COLS = 256;
 constexpr int MAX_KP = 384, MAX_N = 1152;
 
 struct Ctl {
-  uint64_t full[STAGES], empty[STAGES], accfull[2], accempty[2];
+  uint64_t full[MAX_STAGES], empty[MAX_STAGES], accfull[2], accempty[2];
   uint32_t tmem_base;
 };
 
@@ -288,27 +290,30 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_kernel(Args a) {
 // Without the lo copy a 128-row tile fits (the same 96 KB), so each of the two MMAs per k-step has N = 128: per 128 rows
 // 2 x 64 tensor-pipe cycles instead of 6 x 48 (an M = 128, K = 16 MMA costs about 32 + N/4 cycles), and the activation
 // conversion is half the work.  Logits stay within 1e-4 of the CPU reference (bench.py's parity block); training keeps kALo.
-constexpr int SSTAGES = 3;
-
-template <bool kALo>
+//
+// Tile height SBM and ring depth SSTAGES, measured on B200 (layer 0, 4096 clips): 64 rows with 2 / 3 / 4 stages of 32 KB:
+// 0.94 / 0.84 / 0.77 ms; 96 or 128 rows (hi | lo as N = 192 / 256, 2 stages): 1.08 / 0.85 ms.  Taller tiles do not pay:
+// the shared-memory pipe is the bound -- the MMAs read 128 B per cycle of operands (both K-major from shared memory) while
+// the ring takes in another 70 B per cycle -- so the shared memory goes to the deepest ring that fits beside a 64-row tile
+// (four stages; the bias is read from global memory to make room at K = 384).
+template <bool kALo, int SBM, int SSTAGES>
 __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
-  constexpr int SBM = kALo ? 64 : 128;                     // activation rows per tile
   constexpr int SCHUNK = SBM * 16;                         // one k-chunk (8 k) of one part of the tile
-  constexpr int ACH = 2048;                                // one k-chunk of the whole tile: 128 rows, or 64 hi rows | 64 lo rows
-  constexpr int ACC = 128;                                 // TMEM columns per accumulator
-  constexpr int STMEM_COLS = 2 * ACC;                      // two accumulators
+  constexpr int NROW = (kALo ? 2 : 1) * SBM;               // operand rows per k-chunk: SBM rows, or SBM hi rows | SBM lo rows
+  constexpr int ACH = NROW * 16;                           // one k-chunk of the whole tile
+  constexpr int ACC = NROW;                                // TMEM columns per accumulator
+  constexpr int STMEM_COLS = 2 * ACC <= 256 ? 256 : 512;   // two accumulators
   constexpr int RG = SBM / 8;                              // 8-row groups per tile
+  static_assert(SBM % 32 == 0 && NROW % 16 == 0 && NROW <= 256 && SSTAGES <= MAX_STAGES, "tile shape");
   extern __shared__ __align__(1024) uint8_t smem[];
   const int K1p = round_up(a.K1, 8), Kp = kp_of(a.K1, a.K2), nkb = Kp / KB, nnt = (a.N + BN - 1) / BN;
   uint8_t* act_hi = smem;                                    // Kp/8 chunks x 1024 B
   uint8_t* w_s = act_hi + (Kp / 8) * ACH;                    // SSTAGES x (16 KB hi + 16 KB lo)
-  float* bias_s = reinterpret_cast<float*>(w_s + SSTAGES * 2 * W_BLOCK);   // nnt * 128 floats
-  uint8_t* live_s = reinterpret_cast<uint8_t*>(bias_s + nnt * BN);         // 64 bytes
-  Ctl& ctl = *reinterpret_cast<Ctl*>(live_s + SBM);
+  uint8_t* live_s = w_s + SSTAGES * 2 * W_BLOCK;             // SBM bytes
+  Ctl& ctl = *reinterpret_cast<Ctl*>(live_s + 128);
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // known warp-uniform: role branches and MMA descriptors go uniform
 
-  for (int i = tid; i < nnt * BN; i += THREADS) bias_s[i] = (a.bias && i < a.N) ? a.bias[i] : 0.f;
   if (warp == 0) tc::tmem_alloc<STMEM_COLS>(&ctl.tmem_base);
   if (tid == 32) {
     for (int s = 0; s < SSTAGES; ++s) { tc::mbar_init(&ctl.full[s], 1); tc::mbar_init(&ctl.empty[s], 1); }
@@ -320,9 +325,9 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
   tc::fence_after_sync();
   const uint32_t tmem = __shfl_sync(0xffffffffu, ctl.tmem_base, 0);
   const uint32_t ah_u = tc::smem_u32(act_hi), w_u = tc::smem_u32(w_s);
-  // M = 128 weight rows; N = the tile's 128 operand rows (kALo: 64 hi rows | 64 lo rows side by side, so W_hi.[A_hi | A_lo]
+  // M = 128 weight rows; N = the tile's operand rows (kALo: SBM hi rows | SBM lo rows side by side, so W_hi.[A_hi | A_lo]
   // is ONE MMA -- an M = 128, K = 16 MMA costs about 32 + N/4 cycles, the weight operand being fetched per instruction)
-  constexpr uint32_t idesc = tc::make_idesc_f16(BN, 128), idesc_lo = tc::make_idesc_f16(BN, SBM);
+  constexpr uint32_t idesc = tc::make_idesc_f16(BN, NROW), idesc_lo = tc::make_idesc_f16(BN, SBM);
   uint32_t w_it = 0, acc_it = 0;
 
   const int m_tiles = (a.M + SBM - 1) / SBM;
@@ -413,7 +418,7 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
               const uint64_t dwh = tc::make_desc(w_u + s * 2 * W_BLOCK + 2 * j * CHUNK, CHUNK, 128);
               const uint64_t dwl = tc::make_desc(w_u + s * 2 * W_BLOCK + W_BLOCK + 2 * j * CHUNK, CHUNK, 128);
               const uint64_t dact = tc::make_desc(ah_u + koff, ACH, 128);
-              // columns [0, SBM): W_hi.A_hi + W_lo.A_hi; kALo: columns [64, 128): W_hi.A_lo (added in the epilogue)
+              // columns [0, SBM): W_hi.A_hi + W_lo.A_hi; kALo: columns [SBM, 2 SBM): W_hi.A_lo (added in the epilogue)
               tc::mma_f16(tmem + buf * ACC, dwh, dact, idesc, (kb | j) != 0);
               tc::mma_f16(tmem + buf * ACC, dwl, dact, idesc_lo, true);
             }
@@ -429,37 +434,50 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
     } else {
       // =============================== epilogue warps ===============================
       // warp w reads TMEM lanes 32 (w % 4) .. (= output columns nt*128 + 32 (w % 4) + lane) and the 32 accumulator columns
-      // (= tile rows) 32 (w / 4) ..; one store instruction per row: 32 lanes x 4 B = one 128-byte segment of C
-      // (a 128-row tile: two such column blocks per warp)
-      constexpr int CB = 2;                                    // 32-column blocks per warp: two row blocks, or hi part + lo part
+      // (= tile rows) of every other 32-row block; one store instruction per row: 32 lanes x 4 B = one 128-byte segment of C
+      constexpr int RB = SBM / 32, MYB = (RB + 1) / 2;         // row blocks of the tile; blocks per warp (half, half + 2, ..)
       const int q = warp & 3, half = warp >> 2;
       const uint32_t tlane = tmem + ((uint32_t)(q * 32) << 16);
-      uint32_t live_mask[CB];
+      uint32_t live_mask[MYB];
 #pragma unroll
-      for (int cb = 0; cb < CB; ++cb) {
-        live_mask[cb] = 0;
-        for (int r = 0; r < 32; ++r) live_mask[cb] |= (live_s[(kALo ? half : half * CB + cb) * 32 + r] != 0 ? 1u : 0u) << r;
+      for (int k = 0; k < MYB; ++k) {
+        live_mask[k] = 0;
+        const int rb = half + 2 * k;
+        if (rb < RB)
+          for (int r = 0; r < 32; ++r) live_mask[k] |= (live_s[rb * 32 + r] != 0 ? 1u : 0u) << r;
       }
       for (int nt = 0; nt < nnt; ++nt, ++acc_it) {
         const uint32_t buf = acc_it & 1;
         tc::mbar_wait_bounded(&ctl.accfull[buf], (acc_it >> 1) & 1);
         tc::fence_after_sync();
-        float v[CB][32];
-#pragma unroll
-        for (int cb = 0; cb < CB; ++cb) tc::tmem_ld32(tlane + buf * ACC + (kALo ? cb * 64 + half * 32 : (half * CB + cb) * 32), v[cb]);
-        tc::tmem_ld_wait();
-        tc::fence_before_sync();
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&ctl.accempty[buf]);     // the values are in registers: the accumulator may be reused
         const int n = nt * BN + q * 32 + lane;
-        if (n < a.N) {
-          const float bv = bias_s[n];
+        const float bv = (a.bias && n < a.N) ? __ldg(a.bias + n) : 0.f;
 #pragma unroll
-          for (int cb = 0; cb < (kALo ? 1 : CB); ++cb) {
-            float* c = a.C + (int64_t)(m0 + (kALo ? half : half * CB + cb) * 32) * a.ldc + n;
+        for (int k = 0; k < MYB; ++k) {
+          const int rb = half + 2 * k;                         // warp-uniform
+          float v[32];
+          if (rb < RB) {
+            tc::tmem_ld32(tlane + buf * ACC + rb * 32, v);
+            if (kALo) {
+              float w[32];
+              tc::tmem_ld32(tlane + buf * ACC + SBM + rb * 32, w);
+              tc::tmem_ld_wait();
+#pragma unroll
+              for (int r = 0; r < 32; ++r) v[r] += w[r];
+            } else {
+              tc::tmem_ld_wait();
+            }
+          }
+          if (k == MYB - 1) {                                  // this warp's last read of the accumulator: it may be reused
+            tc::fence_before_sync();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&ctl.accempty[buf]);
+          }
+          if (rb < RB && n < a.N) {
+            float* c = a.C + (int64_t)(m0 + rb * 32) * a.ldc + n;
 #pragma unroll
             for (int r = 0; r < 32; ++r)
-              if ((live_mask[cb] >> r) & 1u) c[(int64_t)r * a.ldc] = (kALo ? v[0][r] + v[1][r] : v[cb][r]) + bv;
+              if ((live_mask[k] >> r) & 1u) c[(int64_t)r * a.ldc] = v[r] + bv;
           }
         }
       }
@@ -470,8 +488,20 @@ __global__ void __launch_bounds__(THREADS, 1) proj_gemm_split_kernel(Args a) {
   if (warp == 0) tc::tmem_dealloc<STMEM_COLS>(tmem);
 }
 
-inline size_t smem_bytes_split(int Kp, int nnt) {          // both forms: 2 x 64 rows or 1 x 128 rows of fp16 activations
-  return (size_t)(Kp / 8) * 2048 + SSTAGES * 2 * W_BLOCK + (size_t)nnt * BN * 4 + 128 + sizeof(Ctl);
+inline size_t smem_bytes_split(int Kp, int nnt, int nrow, int stages) {     // nrow = operand rows per k-chunk (hi + lo)
+  return (size_t)(Kp / 8) * nrow * 16 + (size_t)stages * 2 * W_BLOCK + 128 + sizeof(Ctl);
+}
+
+template <bool kALo, int SBM, int SSTAGES>
+int launch_proj_split(const Args& a, int Kp, int nnt, cudaStream_t st) {
+  const size_t smem = smem_bytes_split(Kp, nnt, (kALo ? 2 : 1) * SBM, SSTAGES);
+  SSB_REQUIRE(smem <= 232448, "shared-memory budget");
+  const int m_tiles = cdiv(a.M, SBM);
+  auto kern = proj_gemm_split_kernel<kALo, SBM, SSTAGES>;
+  SSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<m_tiles < kSMs ? m_tiles : kSMs, THREADS, smem, st>>>(a);
+  SSB_LAUNCH_CHECK();
+  return SSB_OK;
 }
 
 inline size_t smem_bytes(int Kp, int nnt) {
@@ -573,19 +603,13 @@ static int proj_gemm_split_impl(const float* A1, int64_t lda1, int64_t K1, const
   if (M == 0) return SSB_OK;
   Args a{A1, lda1, (int)K1, A2, lda2, (int)K2, reinterpret_cast<const uint8_t*>(packed), bias, C, ldc, (int)M, (int)N, 0, lengths, (int)T};
   const int nnt = cdiv(N, BN);
-  const size_t smem = smem_bytes_split(Kp, nnt);
-  SSB_REQUIRE(smem <= 232448, "shared-memory budget");
-  const int m_tiles = cdiv(M, act_lo ? 64 : 128);
-  const int grid = m_tiles < kSMs ? m_tiles : kSMs;
-  if (act_lo) {
-    SSB_CUDA(cudaFuncSetAttribute(proj_gemm_split_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    proj_gemm_split_kernel<true><<<grid, THREADS, smem, (cudaStream_t)stream>>>(a);
-  } else {
-    SSB_CUDA(cudaFuncSetAttribute(proj_gemm_split_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    proj_gemm_split_kernel<false><<<grid, THREADS, smem, (cudaStream_t)stream>>>(a);
-  }
-  SSB_LAUNCH_CHECK();
-  return SSB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!act_lo) return launch_proj_split<false, 128, 4>(a, Kp, nnt, st);
+  // SSB_PROJ_STAGES = 2 | 3 forces a shallower weight ring (A/B runs; read once)
+  static const int nst = [] { const char* e = getenv("SSB_PROJ_STAGES"); return e ? atoi(e) : 0; }();
+  if (nst == 2) return launch_proj_split<true, 64, 2>(a, Kp, nnt, st);
+  if (nst == 3) return launch_proj_split<true, 64, 3>(a, Kp, nnt, st);
+  return launch_proj_split<true, 64, 4>(a, Kp, nnt, st);
 }
 extern "C" int ssb_proj_gemm_split(const float* A1, int64_t lda1, int64_t K1, const float* A2, int64_t lda2, int64_t K2,
                                    const void* packed, const float* bias, float* C, int64_t ldc, int64_t M, int64_t N,

@@ -26,3 +26,18 @@ for use_roi, B, T, seed in ((True, 150, 90, 7), (False, 260, 64, 7), (True, 64, 
             with torch.no_grad():
                 lg = m(X.to(dev), L.to(dev), None if R is None else R.to(dev))
             print(f"roi={use_roi} seed={seed} proj_full={full} cnn_full={cnn_full}: rel_err {rel_err(lg, ref):.3e}")
+
+# the ROI CNN alone in single-pass fp16 (weights rounded too) under split projections / recurrences ("cnn16")
+for use_roi, B, T, seed in ((True, 150, 90, 7), (True, 64, 90, 42), (True, 96, 90, 3)):
+    p = ref_model.synth_params(seed, use_roi=use_roi)
+    d = synth.clip_batch(B, T, mode="uniform", seed=9, use_roi=use_roi)
+    X, L, R = torch.from_numpy(d["X"]), torch.from_numpy(d["lengths"]), torch.from_numpy(d["R"])
+    with torch.no_grad():
+        ref = ref_model.forward(p, X, L, R)
+        emb_ref = ref_model.roi_cnn(p, ref_model.roi_prepare(R, True))
+    for prec in ("tc3", "cnn16", "fp16"):
+        m = BiGRUClassifier(180, 10, use_roi=True, precision=prec)
+        m.load_state_dict(p); m = m.to(dev).eval()
+        with torch.no_grad():
+            lg = m(X.to(dev), L.to(dev), R.to(dev))
+        print(f"seed={seed} precision={prec}: logit rel_err {rel_err(lg, ref):.3e}  (|emb| max {float(emb_ref.abs().max()):.2f}, |logit| max {float(ref.abs().max()):.2f})")
