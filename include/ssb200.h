@@ -167,10 +167,14 @@ int ssb_gru_layer_fwd_tc(const void* gi, int64_t gi_ld, const int64_t* lengths, 
                          const float* whh_f, const float* bhh_f, const float* whh_r, const float* bhh_r,
                          float* out, float* gates, int32_t passes, int32_t gi_layout, void* stream);
 
-/* K2 on the tensor cores: same contract as ssb_roi_cnn_fwd plus `passes` (1 = single fp16 pass, 3 = hi/lo split,
- * fp32-parity grade).  All three convolutions are tcgen05 GEMMs with the 2x2 max-pools folded into N; passes = 1 runs
- * four 128-thread frame slots per CTA with one MMA issuer each; frames are handed out by an atomic counter, the next
- * frame is prefetched, conv2 tiles are committed one by one.  (Third generation of this kernel) */
+/* K2 on the tensor cores: same contract as ssb_roi_cnn_fwd (train_model_official.py:286-294, 209-229) plus `passes`:
+ *   1 = single fp16 pass (stated tolerance 1e-3 on the logits);
+ *   2 = weights split hi + lo, activations rounded to fp16 once (x.W_hi + x.W_lo; conv1's raw-pixel input is exact):
+ *       the inference form of the fp32-parity mode -- embedding within 3e-5, logits unchanged at the 1e-6 level;
+ *   3 = both operands split (fp32-parity grade everywhere; the training forward, the only mode that fills `saved`).
+ * All three convolutions are tcgen05 GEMMs with the 2x2 max-pools folded into N; frames are staged by one bulk async copy
+ * each, handed out by an atomic counter; four 128-thread frame slots per CTA (passes 1, 2) or two 256-thread slots
+ * (passes 3) with one MMA issuer each; hi | lo weights stacked along N.   */
 int ssb_roi_cnn_fwd_tc3(const uint8_t* R, const int64_t* lengths, int64_t B, int64_t T,
                         int32_t roi_h, int32_t roi_w, const float* const* weights_host, int32_t standardize,
                         float* out, int64_t out_stride, int32_t passes, void* saved, void* stream);
