@@ -25,7 +25,7 @@ def _passes(model):
 
 # Inference projections: splitting the activations too is the default.  Rounding them to fp16 once (ssb_proj_gemm_wsplit:
 # 128-row tiles, two MMAs per k-step; model.proj_full_split = False or a tuple of the layers that keep the full split) makes
-# the two projections 0.7 ms faster per 4096 clips but costs about 1e-4 of max |logit| PER LAYER (tools/proj_probe.py:
+# the two projections 0.7 ms faster per 4096 clips but costs about 1e-4 of max |logit| PER LAYER (tests/probes/proj_probe.py:
 # 1.6e-4 .. 2.5e-4 with both) -- the recurrence carries a gi error through 90 steps, unlike the ROI CNN, whose activations
 # can be rounded for free (cnn_passes).  That misses the 1e-4 bar of the tc3 mode, so it stays opt-in.
 PROJ_FULL_SPLIT_DEFAULT = True
@@ -106,7 +106,7 @@ def forward_impl(model, X, lengths, R, training: bool, save: bool, k_top: int = 
             g = gi
             if blk and getattr(model, "gi_half", False):
                 # opt-in (model.gi_half = True): gi stored as fp16 -- projection GEMM -13 %, recurrence -2 %, logit error
-                # 2.6e-4 -> 4.4e-4 of max|logit| (tools/gi16_probe.py); off by default, the step gains only 2 %
+                # 2.6e-4 -> 4.4e-4 of max|logit| (tests/probes/gi16_probe.py); off by default, the step gains only 2 %
                 g = torch.empty(B, T, 2 * G3, device=dev, dtype=torch.float16)
             ops.proj_gemm(A2d, packed, fold, g.view(B * T, 2 * G3), 2 * G3, A2=extra, lengths=lengths, T=T)
             return ops.gru_layer_fwd_tc(g, lengths, pl["weight_hh"][0], pl["bias_hh"][0], pl["weight_hh"][1],

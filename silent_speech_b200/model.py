@@ -108,7 +108,7 @@ class BiGRUClassifier(nn.Module):
         if precision not in ("fp32", "tc3", "fp16", "cnn16", "gru16"):
             raise ValueError("precision must be 'fp32' (CUDA-core FMA), 'tc3' (tensor cores, split-fp16, "
                              "fp32-parity grade), 'fp16' (tensor cores, single fp16 pass) or one of the diagnostic "
-                             "mixes 'cnn16' / 'gru16' (only that stage single-pass; tools/precision_modes.py)")
+                             "mixes 'cnn16' / 'gru16' (only that stage single-pass; tests/probes/precision_modes.py)")
         self.precision = precision
         if hidden != HIDDEN or roi_emb != ROI_EMB or gru_layers != 2:
             raise ValueError("libssb200 kernels are specialised for hidden=192, roi_emb=32, 2 GRU layers "

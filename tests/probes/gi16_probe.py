@@ -1,6 +1,6 @@
 """What would fp16 storage of gi cost in logit error?  Rounds gi through fp16 between the projection GEMM and the recurrence."""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 from oracle import ref_model
 from silent_speech_b200 import BiGRUClassifier, synth, ops

@@ -1,8 +1,8 @@
 """Logit error of the tc3 inference mode as a function of which stages round their ACTIVATIONS to fp16 once instead of
 splitting them (weights are always split): the two GRU input projections (ssb_proj_gemm_wsplit) and the ROI CNN (K2 passes=2).
-    python tools/proj_probe.py        (B200; the oracle is the checker)"""
+    python tests/probes/proj_probe.py        (B200; the oracle is the checker)"""
 import os, sys, torch
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from oracle import ref_model
 from silent_speech_b200 import BiGRUClassifier, synth
 torch.set_num_threads(os.cpu_count() or 1)

@@ -3,7 +3,6 @@
 import argparse, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from oracle import ref_model
 from silent_speech_b200 import ops, synth
 
 ap = argparse.ArgumentParser()
@@ -19,7 +18,7 @@ a = ap.parse_args()
 dev = torch.device("cuda")
 B, T, G3, H = a.batch, 90, 576, 192
 passes = {"fp16": 1, "tc2": 2, "tc3": 3}[a.precision]   # tc2: K2 only (split weights, fp16 activations)
-p = {k: v.to(dev).contiguous() for k, v in ref_model.synth_params(42).items()}
+p = {k: v.to(dev).contiguous() for k, v in synth.synth_params(42).items()}
 L = torch.from_numpy(synth.lengths(B, T, a.lengths)).to(dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
