@@ -82,22 +82,52 @@ def ncu_traffic(kernel_key, clips, lengths):
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled while the timed region runs."""
+    """SM clock + throttle reasons sampled while the timed region runs.  NVML in-process (nvidia_ml_py: a few microseconds
+    per query, initialised once, outside any timed region); falls back to polling nvidia-smi when the module is missing.
+    (Spawning nvidia-smi from every rank at the start of a timed region cost a straggler at 8 GPUs: the train step's
+    launch-bound ranks then waited for it inside the all-reduce.)"""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    _nvml = None          # (module, ok) once tried
 
     def __init__(self, index):
         self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+        if ClockSampler._nvml is None:
+            try:
+                import pynvml
+                pynvml.nvmlInit()
+                ClockSampler._nvml = (pynvml, True)
+            except Exception:
+                ClockSampler._nvml = (None, False)
+        self._h = None
+        if ClockSampler._nvml[1]:
+            try:
+                self._h = ClockSampler._nvml[0].nvmlDeviceGetHandleByIndex(index)
+            except Exception:
+                self._h = None
+
+    def _sample_nvml(self):
+        nv = ClockSampler._nvml[0]
+        sm = nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)
+        mx = nv.nvmlDeviceGetMaxClockInfo(self._h, nv.NVML_CLOCK_SM)
+        get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        r = int(get(self._h))
+        bits = [0x8, 0x40, 0x20, 0x4]      # HwSlowdown, HwThermalSlowdown, SwThermalSlowdown, SwPowerCap
+        return [str(sm), str(mx)] + ["Active" if r & b else "Not Active" for b in bits]
 
     def _run(self):
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([c.strip() for c in out.strip().split(",")])
+                if self._h is not None:
+                    self.rows.append(self._sample_nvml())
+                else:
+                    out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                    self.rows.append([c.strip() for c in out.strip().split(",")])
             except Exception:
                 pass
-            self._stop.wait(0.15)
+            self._stop.wait(0.02 if self._h is not None else 0.15)
 
     def __enter__(self):
         self._stop.clear()
@@ -112,10 +142,9 @@ class ClockSampler:
     def summary(self):
         sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
         mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i].lower().startswith("active") for r in self.rows)]
+        reasons = [n for i, n in enumerate(self.NAMES) if any(len(r) >= 6 and r[2 + i].lower().startswith("active") for r in self.rows)]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": "nvml" if self._h is not None else "nvidia-smi"}
 
 
 def make_batch(B, T, mode, use_roi=True, unique=64, seed=42):
